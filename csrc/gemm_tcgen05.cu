@@ -1,0 +1,448 @@
+// Persistent, warp-specialised bf16 GEMM for sm_100a: TMA -> 128B-swizzled smem ring -> tcgen05.mma with fp32
+// accumulators in TMEM (double buffered) -> tcgen05.ld epilogue (bias / residual / dtype cast) -> global.
+//
+//   D[M,N] = A[M,K] * B[N,K]^T  (+ bias[N]) (+ residual[M,N])
+//
+// Both operands may be K-major (reduction dim contiguous) or MN-major (output dim contiguous), which gives the
+// three shapes a linear layer needs without ever transposing in memory:
+//   forward  y  = x  W^T : A = x  (K-major),  B = W  (K-major)
+//   dgrad    dx = dy W   : A = dy (K-major),  B = W  (MN-major: W is [N_red, K_out] row-major)
+//   wgrad    dW = dy^T x : A = dy (MN-major), B = x  (MN-major), reduction over tokens, split-K over the SMs
+//
+// Replaces the cuBLAS calls behind F.linear in the reference (models/layers.py:49,93 and their autograd).
+#include "common.cuh"
+#include "dpfs_b200.h"
+
+#include <cudaTypedefs.h>
+#include <stdio.h>
+
+namespace dpfs {
+
+constexpr int BM = 128;
+constexpr int BK = 64;
+constexpr int kGemmThreads = 192;  // warp 0: TMA producer, warp 1: MMA issuer + TMEM owner, warps 2-5: epilogue
+
+struct GemmArgs {
+  int M, N, K;
+  int splits;        // split-K factor
+  int kb_per_split;  // K blocks (of BK) per split
+  void* out;         // OutT [splits][M][ldo]
+  long long ldo;
+  long long split_stride;  // elements between split slabs
+  const float* bias;       // [N] or nullptr
+  const float* residual;   // fp32 [M][ldr] or nullptr
+  long long ldr;
+};
+
+template <int BN>
+struct GemmSmem {
+  static constexpr int kABytes = BM * BK * 2;
+  static constexpr int kBBytes = BN * BK * 2;
+  static constexpr int kStageBytes = kABytes + kBBytes;
+  static constexpr int kStages = (BN == 256) ? 4 : 6;
+  static constexpr int kBarrierBytes = 256;
+  static constexpr int kTotal = kStages * kStageBytes + kBarrierBytes + 1024;  // + alignment slack
+};
+
+template <typename OutT>
+__device__ __forceinline__ void store_chunk32(OutT* dst, const float (&v)[32], int ncols_valid);
+
+template <>
+__device__ __forceinline__ void store_chunk32<float>(float* dst, const float (&v)[32], int ncols_valid) {
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    if (j * 4 + 4 <= ncols_valid) {
+      float4 o = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+      *reinterpret_cast<float4*>(dst + 4 * j) = o;
+    }
+  }
+}
+template <>
+__device__ __forceinline__ void store_chunk32<__nv_bfloat16>(__nv_bfloat16* dst, const float (&v)[32],
+                                                             int ncols_valid) {
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    if (j * 8 + 8 <= ncols_valid) {
+      uint4 o;
+      o.x = pack_bf16(v[8 * j + 0], v[8 * j + 1]);
+      o.y = pack_bf16(v[8 * j + 2], v[8 * j + 3]);
+      o.z = pack_bf16(v[8 * j + 4], v[8 * j + 5]);
+      o.w = pack_bf16(v[8 * j + 6], v[8 * j + 7]);
+      *reinterpret_cast<uint4*>(dst + 8 * j) = o;
+    }
+  }
+}
+
+template <int BN, bool A_MN, bool B_MN, typename OutT>
+__global__ void __launch_bounds__(kGemmThreads, 1)
+gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                 const GemmArgs args) {
+  using S = GemmSmem<BN>;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* sA = smem;
+  uint8_t* sB = smem + S::kStages * S::kABytes;
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + S::kStages * S::kStageBytes);
+  uint64_t* empty_bar = full_bar + S::kStages;
+  uint64_t* tmem_full = empty_bar + S::kStages;
+  uint64_t* tmem_empty = tmem_full + 2;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty + 2);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+
+  const int tiles_m = (args.M + BM - 1) / BM;
+  const int tiles_n = (args.N + BN - 1) / BN;
+  const int tiles_mn = tiles_m * tiles_n;
+  const int num_work = tiles_mn * args.splits;
+  const int kb_total = (args.K + BK - 1) / BK;
+
+  if (threadIdx.x == 0) {
+    prefetch_tmap(&tmA);
+    prefetch_tmap(&tmB);
+    for (int i = 0; i < S::kStages; ++i) {
+      mbar_init(&full_bar[i], 1);
+      mbar_init(&empty_bar[i], 1);
+    }
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(&tmem_full[i], 1);
+      mbar_init(&tmem_empty[i], 4);
+    }
+    fence_mbar_init();
+  }
+  if (warp == 1) {
+    tmem_alloc(tmem_slot, 2 * BN);
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    // ------------------------------------------------------------------ TMA producer
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int w = blockIdx.x; w < num_work; w += gridDim.x) {
+        const int split = w / tiles_mn;
+        const int t = w - split * tiles_mn;
+        const int m0 = (t / tiles_n) * BM;
+        const int n0 = (t % tiles_n) * BN;
+        const int kb0 = split * args.kb_per_split;
+        const int kb1 = min(kb_total, kb0 + args.kb_per_split);
+        for (int kb = kb0; kb < kb1; ++kb) {
+          mbar_wait(&empty_bar[stage], phase ^ 1);
+          mbar_expect_tx(&full_bar[stage], S::kStageBytes);
+          uint8_t* a_dst = sA + stage * S::kABytes;
+          uint8_t* b_dst = sB + stage * S::kBBytes;
+          if constexpr (!A_MN) {
+            tma_load_2d(a_dst, &tmA, &full_bar[stage], kb * BK, m0);
+          } else {
+#pragma unroll
+            for (int b = 0; b < BM / 64; ++b)
+              tma_load_2d(a_dst + b * (BK * 128), &tmA, &full_bar[stage], m0 + 64 * b, kb * BK);
+          }
+          if constexpr (!B_MN) {
+            tma_load_2d(b_dst, &tmB, &full_bar[stage], kb * BK, n0);
+          } else {
+#pragma unroll
+            for (int b = 0; b < BN / 64; ++b)
+              tma_load_2d(b_dst + b * (BK * 128), &tmB, &full_bar[stage], n0 + 64 * b, kb * BK);
+          }
+          if (++stage == S::kStages) {
+            stage = 0;
+            phase ^= 1;
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ------------------------------------------------------------------ MMA issuer (single thread)
+    if (lane == 0) {
+      constexpr uint32_t idesc = make_idesc_bf16(BM, BN, A_MN, B_MN);
+      int stage = 0;
+      uint32_t phase = 0;
+      int as = 0;
+      uint32_t aphase = 0;
+      for (int w = blockIdx.x; w < num_work; w += gridDim.x) {
+        const int split = w / tiles_mn;
+        const int kb0 = split * args.kb_per_split;
+        const int kb1 = min(kb_total, kb0 + args.kb_per_split);
+        mbar_wait(&tmem_empty[as], aphase ^ 1);
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + as * BN;
+        for (int kb = kb0; kb < kb1; ++kb) {
+          mbar_wait(&full_bar[stage], phase);
+          tc_fence_after();
+          const uint32_t a_base = smem_u32(sA + stage * S::kABytes);
+          const uint32_t b_base = smem_u32(sB + stage * S::kBBytes);
+#pragma unroll
+          for (int k = 0; k < BK / 16; ++k) {
+            // K-major: one 128B swizzle atom spans BK; step 16 elements (32 B) inside the atom; 8-row groups are
+            // 1024 B apart.  MN-major: rows are k, 128 B each; 64-wide MN atoms are BK*128 B apart (LBO), 8-row k
+            // groups are 1024 B apart (SBO); step 16 k-rows = 2048 B.
+            const uint64_t adesc = A_MN ? make_smem_desc_sw128(a_base + k * 2048, BK * 128, 1024)
+                                        : make_smem_desc_sw128(a_base + k * 32, 0, 1024);
+            const uint64_t bdesc = B_MN ? make_smem_desc_sw128(b_base + k * 2048, BK * 128, 1024)
+                                        : make_smem_desc_sw128(b_base + k * 32, 0, 1024);
+            umma_bf16_ss(d_tmem, adesc, bdesc, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
+          }
+          umma_commit(&empty_bar[stage]);  // frees the smem slot once these MMAs have read it
+          if (++stage == S::kStages) {
+            stage = 0;
+            phase ^= 1;
+          }
+        }
+        umma_commit(&tmem_full[as]);  // accumulator complete -> epilogue
+        if (++as == 2) {
+          as = 0;
+          aphase ^= 1;
+        }
+      }
+    }
+  } else {
+    // ------------------------------------------------------------------ epilogue warps (TMEM -> regs -> global)
+    const int q = warp & 3;  // TMEM lane quarter this warp may access
+    int as = 0;
+    uint32_t aphase = 0;
+    OutT* out = reinterpret_cast<OutT*>(args.out);
+    for (int w = blockIdx.x; w < num_work; w += gridDim.x) {
+      const int split = w / tiles_mn;
+      const int t = w - split * tiles_mn;
+      const int m0 = (t / tiles_n) * BM;
+      const int n0 = (t % tiles_n) * BN;
+      const int row = m0 + q * 32 + lane;
+      mbar_wait(&tmem_full[as], aphase);
+      tc_fence_after();
+      const uint32_t t_addr = tmem_base + as * BN + (static_cast<uint32_t>(q * 32) << 16);
+      OutT* orow = out + split * args.split_stride + static_cast<long long>(row) * args.ldo + n0;
+      const float* rrow = args.residual ? args.residual + static_cast<long long>(row) * args.ldr + n0 : nullptr;
+#pragma unroll 1
+      for (int c = 0; c < BN / 32; ++c) {
+        uint32_t r[32];
+        tmem_ld32(t_addr + c * 32, r);
+        tmem_ld_wait();
+        const int ncols_valid = args.N - (n0 + c * 32);
+        if (row < args.M && ncols_valid > 0) {
+          float v[32];
+#pragma unroll
+          for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
+          if (args.bias) {
+#pragma unroll
+            for (int j = 0; j < 32; ++j)
+              if (j < ncols_valid) v[j] += __ldg(args.bias + n0 + c * 32 + j);
+          }
+          if (rrow) {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+              if (j * 4 + 4 <= ncols_valid) {
+                const float4 rv = *reinterpret_cast<const float4*>(rrow + c * 32 + 4 * j);
+                v[4 * j] += rv.x;
+                v[4 * j + 1] += rv.y;
+                v[4 * j + 2] += rv.z;
+                v[4 * j + 3] += rv.w;
+              }
+            }
+          }
+          store_chunk32<OutT>(orow + c * 32, v, ncols_valid);
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&tmem_empty[as]);
+      if (++as == 2) {
+        as = 0;
+        aphase ^= 1;
+      }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, 2 * BN);
+  }
+}
+
+// Sum split-K partial slabs (fp32) and write the final result; optional bias and dtype cast.
+template <typename OutT>
+__global__ void splitk_reduce_kernel(const float* __restrict__ ws, OutT* __restrict__ out, long long ldo,
+                                     const float* __restrict__ bias, int M, int N, int splits) {
+  const long long total4 = static_cast<long long>(M) * N / 4;
+  const long long slab = static_cast<long long>(M) * N;
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total4;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    float4 acc = *reinterpret_cast<const float4*>(ws + i * 4);
+    for (int s = 1; s < splits; ++s) {
+      const float4 p = *reinterpret_cast<const float4*>(ws + s * slab + i * 4);
+      acc.x += p.x;
+      acc.y += p.y;
+      acc.z += p.z;
+      acc.w += p.w;
+    }
+    const long long e = i * 4;
+    const int r = static_cast<int>(e / N);
+    const int c = static_cast<int>(e % N);
+    if (bias) {
+      acc.x += bias[c];
+      acc.y += bias[c + 1];
+      acc.z += bias[c + 2];
+      acc.w += bias[c + 3];
+    }
+    OutT* o = out + static_cast<long long>(r) * ldo + c;
+    if constexpr (sizeof(OutT) == 4) {
+      *reinterpret_cast<float4*>(o) = acc;
+    } else {
+      uint2 pk;
+      pk.x = pack_bf16(acc.x, acc.y);
+      pk.y = pack_bf16(acc.z, acc.w);
+      *reinterpret_cast<uint2*>(o) = pk;
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// host side
+// ---------------------------------------------------------------------------------------------------------
+static PFN_cuTensorMapEncodeTiled_v12000 get_encode_fn() {
+  static PFN_cuTensorMapEncodeTiled_v12000 fn = nullptr;
+  if (!fn) {
+    cudaDriverEntryPointQueryResult q;
+    void* p = nullptr;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) != cudaSuccess ||
+        q != cudaDriverEntryPointSuccess)
+      return nullptr;
+    fn = reinterpret_cast<PFN_cuTensorMapEncodeTiled_v12000>(p);
+  }
+  return fn;
+}
+
+// 2-D bf16 tensor map over a row-major [outer][ld] array whose logical inner extent is `inner`;
+// box = 64 (inner, 128 B, 128B swizzle) x box_outer.
+int make_tmap_bf16_2d(CUtensorMap* tm, const void* ptr, uint64_t inner, uint64_t outer, uint64_t ld_elems,
+                      uint32_t box_inner, uint32_t box_outer) {
+  auto fn = get_encode_fn();
+  if (!fn) return -1;
+  cuuint64_t dims[2] = {inner, outer};
+  cuuint64_t strides[1] = {ld_elems * 2};
+  cuuint32_t box[2] = {box_inner, box_outer};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = fn(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(ptr), dims, strides, box, estr,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  return r == CUDA_SUCCESS ? 0 : -2;
+}
+
+int num_sms() {
+  static int n = 0;
+  if (!n) {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
+  }
+  return n;
+}
+
+template <int BN, bool A_MN, bool B_MN, typename OutT>
+static int launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmArgs& args, cudaStream_t stream) {
+  using S = GemmSmem<BN>;
+  auto kfn = gemm_bf16_kernel<BN, A_MN, B_MN, OutT>;
+  static bool configured = false;
+  if (!configured) {
+    cudaError_t e = cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, S::kTotal);
+    if (e != cudaSuccess) return static_cast<int>(e);
+    configured = true;
+  }
+  const int tiles = ((args.M + BM - 1) / BM) * ((args.N + BN - 1) / BN) * args.splits;
+  const int grid = tiles < num_sms() ? tiles : num_sms();
+  kfn<<<grid, kGemmThreads, S::kTotal, stream>>>(tmA, tmB, args);
+  return static_cast<int>(cudaGetLastError());
+}
+
+template <int BN, typename OutT>
+static int dispatch_major(bool a_mn, bool b_mn, const CUtensorMap& tmA, const CUtensorMap& tmB,
+                          const GemmArgs& args, cudaStream_t stream) {
+  if (!a_mn && !b_mn) return launch_gemm<BN, false, false, OutT>(tmA, tmB, args, stream);
+  if (!a_mn && b_mn) return launch_gemm<BN, false, true, OutT>(tmA, tmB, args, stream);
+  if (a_mn && b_mn) return launch_gemm<BN, true, true, OutT>(tmA, tmB, args, stream);
+  return launch_gemm<BN, true, false, OutT>(tmA, tmB, args, stream);
+}
+
+}  // namespace dpfs
+
+using namespace dpfs;
+
+extern "C" int dpfs_gemm_bf16(const void* A, long long lda, int a_mn_major, const void* B, long long ldb,
+                              int b_mn_major, void* out, long long ldo, int out_fp32, const float* bias,
+                              const float* residual, long long ldr, int M, int N, int K, int splits,
+                              float* workspace, int bn, cudaStream_t stream) {
+  if (M <= 0 || N <= 0 || K <= 0) return 0;
+  if ((N % 8) != 0 || (lda % 8) != 0 || (ldb % 8) != 0 || (ldo % (out_fp32 ? 4 : 8)) != 0) return -10;
+  if (splits < 1) splits = 1;
+  const int kb_total = (K + BK - 1) / BK;
+  if (splits > kb_total) splits = kb_total;
+  int kb_per_split = (kb_total + splits - 1) / splits;
+  splits = (kb_total + kb_per_split - 1) / kb_per_split;
+  if (splits > 1 && workspace == nullptr) return -11;
+  if (bn != 256) bn = 128;
+
+  CUtensorMap tmA, tmB;
+  int rc;
+  if (!a_mn_major)
+    rc = make_tmap_bf16_2d(&tmA, A, K, M, lda, 64, BM);
+  else
+    rc = make_tmap_bf16_2d(&tmA, A, M, K, lda, 64, BK);
+  if (rc) return rc;
+  if (!b_mn_major)
+    rc = make_tmap_bf16_2d(&tmB, B, K, N, ldb, 64, bn);
+  else
+    rc = make_tmap_bf16_2d(&tmB, B, N, K, ldb, 64, BK);
+  if (rc) return rc;
+
+  GemmArgs args;
+  args.M = M;
+  args.N = N;
+  args.K = K;
+  args.splits = splits;
+  args.kb_per_split = kb_per_split;
+  args.bias = bias;
+  args.residual = residual;
+  args.ldr = ldr;
+  const bool direct = (splits == 1);
+  if (direct) {
+    args.out = out;
+    args.ldo = ldo;
+    args.split_stride = 0;
+  } else {
+    args.out = workspace;
+    args.ldo = N;
+    args.split_stride = static_cast<long long>(M) * N;
+    args.bias = nullptr;
+    args.residual = nullptr;
+  }
+  const bool kernel_fp32 = direct ? (out_fp32 != 0) : true;
+  if (bn == 256) {
+    rc = kernel_fp32 ? dispatch_major<256, float>(a_mn_major, b_mn_major, tmA, tmB, args, stream)
+                     : dispatch_major<256, __nv_bfloat16>(a_mn_major, b_mn_major, tmA, tmB, args, stream);
+  } else {
+    rc = kernel_fp32 ? dispatch_major<128, float>(a_mn_major, b_mn_major, tmA, tmB, args, stream)
+                     : dispatch_major<128, __nv_bfloat16>(a_mn_major, b_mn_major, tmA, tmB, args, stream);
+  }
+  if (rc) return rc;
+  if (!direct) {
+    if (residual) return -12;  // residual is only fused on the direct path
+    const long long total4 = static_cast<long long>(M) * N / 4;
+    int blocks = static_cast<int>((total4 + 255) / 256);
+    if (blocks > num_sms() * 8) blocks = num_sms() * 8;
+    if (out_fp32)
+      splitk_reduce_kernel<float><<<blocks, 256, 0, stream>>>(workspace, reinterpret_cast<float*>(out), ldo, bias,
+                                                             M, N, splits);
+    else
+      splitk_reduce_kernel<__nv_bfloat16><<<blocks, 256, 0, stream>>>(
+          workspace, reinterpret_cast<__nv_bfloat16*>(out), ldo, bias, M, N, splits);
+    rc = static_cast<int>(cudaGetLastError());
+  }
+  return rc;
+}

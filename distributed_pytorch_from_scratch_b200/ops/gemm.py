@@ -1,0 +1,75 @@
+"""bf16 GEMM on tcgen05 tensor cores (csrc/gemm_tcgen05.cu).
+
+``gemm_nt`` computes ``out[M,N] = A[M,K] @ B[N,K]^T`` where each operand may be given K-major (reduction dim
+contiguous) or MN-major (stored transposed, output dim contiguous) — the three cases a linear layer needs
+(forward, dgrad, wgrad) without materialising a transpose.  Replaces the cuBLAS GEMMs behind ``F.linear`` in the
+reference (models/layers.py:49,93).
+"""
+from __future__ import annotations
+
+from typing import Optional
+
+import torch
+
+from . import _lib
+
+_WS = {}
+
+
+def _workspace(device, nfloats: int) -> torch.Tensor:
+    ws = _WS.get(device)
+    if ws is None or ws.numel() < nfloats:
+        ws = torch.empty(max(nfloats, 1 << 22), dtype=torch.float32, device=device)
+        _WS[device] = ws
+    return ws
+
+
+def auto_splits(M: int, N: int, K: int, bn: int = 128) -> int:
+    """Split-K factor that fills the 148 SMs when the output has few tiles (wgrad: tiny M x N, huge K)."""
+    tiles = ((M + 127) // 128) * ((N + bn - 1) // bn)
+    kb = (K + 63) // 64
+    if tiles >= 120 or kb < 8:
+        return 1
+    s = max(1, min(kb // 4, (148 * 2) // tiles))
+    return s
+
+
+def gemm_nt(a: torch.Tensor, b: torch.Tensor, *, a_mn_major: bool = False, b_mn_major: bool = False,
+            out: Optional[torch.Tensor] = None, out_dtype: torch.dtype = torch.bfloat16,
+            bias: Optional[torch.Tensor] = None, residual: Optional[torch.Tensor] = None,
+            splits: int = 0, bn: int = 0) -> torch.Tensor:
+    """out[M,N] = A[M,K] @ B[N,K]^T (+bias) (+residual).
+
+    a: [M,K] (K-major) or [K,M] (``a_mn_major``); b: [N,K] or [K,N] (``b_mn_major``); 2-D, bf16, last dim
+    contiguous (row stride may exceed the row length).
+    """
+    assert a.dim() == 2 and b.dim() == 2 and a.dtype == torch.bfloat16 and b.dtype == torch.bfloat16
+    assert a.stride(1) == 1 and b.stride(1) == 1
+    if a_mn_major:
+        K, M = a.shape
+    else:
+        M, K = a.shape
+    if b_mn_major:
+        Kb, N = b.shape
+    else:
+        N, Kb = b.shape
+    assert K == Kb, f"reduction dims differ: {K} vs {Kb}"
+    if out is None:
+        out = torch.empty((M, N), dtype=out_dtype, device=a.device)
+    else:
+        assert out.shape == (M, N) and out.stride(1) == 1
+    out_fp32 = out.dtype == torch.float32
+    assert out_fp32 or out.dtype == torch.bfloat16
+    if bias is not None:
+        assert bias.dtype == torch.float32 and bias.numel() == N and bias.is_contiguous()
+    if residual is not None:
+        assert residual.dtype == torch.float32 and residual.shape == (M, N) and residual.stride(1) == 1
+    if splits == 0:
+        splits = auto_splits(M, N, K, bn or 128) if residual is None else 1
+    ws = _workspace(a.device, splits * M * N) if splits > 1 else None
+    rc = _lib.lib().dpfs_gemm_bf16(
+        a.data_ptr(), a.stride(0), int(a_mn_major), b.data_ptr(), b.stride(0), int(b_mn_major),
+        out.data_ptr(), out.stride(0), int(out_fp32), _lib.ptr(bias), _lib.ptr(residual),
+        residual.stride(0) if residual is not None else 0, M, N, K, splits, _lib.ptr(ws), bn, _lib.stream())
+    _lib.check(rc, "dpfs_gemm_bf16")
+    return out
