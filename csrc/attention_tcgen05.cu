@@ -1,0 +1,660 @@
+// Causal flash attention forward / backward on tcgen05 tensor cores (sm_100a).
+//
+// Replaces the materialised attention of the reference (models/model.py:68-78: QK^T / sqrt(hd), a per-call
+// fp32 [b,1,t,t] triu mask, masked_fill(-10000), softmax, PV, plus two einops head rearranges): scores and
+// probabilities never leave the SM (S and dP live in TMEM, P and dS in shared memory), the causal mask is implicit
+// (tiles above the diagonal are skipped), and the head split / merge is folded into the TMA tensor maps over the
+// packed [b*t, 3*Dl] QKV buffer — no transposes, no [b,H,t,t] tensors.
+//
+// Layouts
+//   qkv : bf16 [b*t][3*Dl]   q | k | v segments, each H heads of hd (RoPE already applied to q and k)
+//   out : bf16 [b*t][Dl]
+//   lse : fp32 [b][H][t]     log-sum-exp of the scaled scores (natural log)
+//   dqkv: bf16 [b*t][3*Dl]   (backward; dq is accumulated in fp32 [b*t][Dl] across kv tiles and converted after)
+//
+// Forward CTA  = one (batch, head, 128-row q tile); loops over kv tiles up to the diagonal.
+// Backward CTA = one (batch, head, 128-row kv tile); loops over q tiles from the diagonal down.
+// Warp roles (192 threads): warp 0 TMA producer, warp 1 tcgen05.mma issuer (+ TMEM owner), warps 2-5 softmax /
+// gradient math, one thread per tile row (TMEM lane).
+#include "common.cuh"
+#include "dpfs_b200.h"
+
+#include <cudaTypedefs.h>
+
+namespace dpfs {
+
+int num_sms();
+
+constexpr int kAttnThreads = 192;
+constexpr int kTile = 128;  // q rows and kv rows per tile
+constexpr float kLog2e = 1.4426950408889634f;
+constexpr float kLn2 = 0.6931471805599453f;
+
+__device__ __forceinline__ float fast_exp2(float x) {
+  float y;
+  asm volatile("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+
+// K-major SW128 operand [rows][cols] made of 64-column atoms (each atom = rows x 128 B, atoms `atom_bytes` apart):
+// descriptor for the 16-wide K slice kk.
+__device__ __forceinline__ uint64_t desc_kmajor(uint32_t base, int kk, uint32_t atom_bytes) {
+  return make_smem_desc_sw128(base + (kk >> 2) * atom_bytes + (kk & 3) * 32, 0, 1024);
+}
+// MN-major SW128 operand stored as [k rows][MN cols] in 64-column atoms: descriptor for k rows [16*kk, 16*kk+16).
+__device__ __forceinline__ uint64_t desc_mnmajor(uint32_t base, int kk, uint32_t atom_bytes) {
+  return make_smem_desc_sw128(base + kk * 2048, atom_bytes, 1024);
+}
+
+// write 32 consecutive bf16 (columns [c0, c0+32) of row r) into a K-major SW128 [128][128] tile (two 64-col atoms)
+__device__ __forceinline__ void st_tile_row32(uint8_t* tile, int r, int c0, const uint32_t (&packed)[16]) {
+  uint8_t* atom = tile + (c0 >> 6) * (kTile * 128) + r * 128;
+  const int cc0 = (c0 & 63) >> 3;  // first 16-byte chunk inside the atom row
+#pragma unroll
+  for (int q = 0; q < 4; ++q) {
+    const int phys = (cc0 + q) ^ (r & 7);
+    *reinterpret_cast<uint4*>(atom + (phys << 4)) =
+        make_uint4(packed[4 * q], packed[4 * q + 1], packed[4 * q + 2], packed[4 * q + 3]);
+  }
+}
+
+// ================================================================================================= forward
+template <int HD>
+struct FwdCfg {
+  static constexpr int kStages = 2;
+  static constexpr int kQBytes = kTile * HD * 2;
+  static constexpr int kKVBytes = kTile * HD * 2;  // one K or V tile
+  static constexpr int kPBytes = kTile * kTile * 2;
+  static constexpr int kSmem = kQBytes + kStages * 2 * kKVBytes + kPBytes + 256 + 1024;
+  static constexpr int kTmemCols = 512;  // S0: [0,128), S1: [128,256), O: [256, 256+HD)
+};
+
+template <int HD>
+__global__ void __launch_bounds__(kAttnThreads, 1)
+attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, __nv_bfloat16* __restrict__ out,
+                float* __restrict__ lse, int T, int H, int Dl, float scale_log2) {
+  using C = FwdCfg<HD>;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* sQ = smem;
+  uint8_t* sK = sQ + C::kQBytes;                    // [stage]
+  uint8_t* sV = sK + C::kStages * C::kKVBytes;      // [stage]
+  uint8_t* sP = sV + C::kStages * C::kKVBytes;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sP + C::kPBytes);
+  uint64_t* q_full = bars;
+  uint64_t* k_full = bars + 1;                       // [2]
+  uint64_t* v_full = bars + 3;                       // [2]
+  uint64_t* kv_empty = bars + 5;                     // [2]
+  uint64_t* s_full = bars + 7;                       // [2] (S is double buffered in TMEM)
+  uint64_t* p_full = bars + 9;
+  uint64_t* o_done = bars + 10;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 11);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int nq = (T + kTile - 1) / kTile;
+  const int qt = nq - 1 - blockIdx.x;  // heavy tiles first
+  const int h = blockIdx.y, b = blockIdx.z;
+  const int q0 = qt * kTile;
+  const int n_kv = qt + 1;
+
+  if (threadIdx.x == 0) {
+    prefetch_tmap(&tm_qkv);
+    mbar_init(q_full, 1);
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(&k_full[i], 1);
+      mbar_init(&v_full[i], 1);
+      mbar_init(&kv_empty[i], 1);
+    }
+    mbar_init(&s_full[0], 1);
+    mbar_init(&s_full[1], 1);
+    mbar_init(p_full, 4);
+    mbar_init(o_done, 1);
+    fence_mbar_init();
+  }
+  if (warp == 1) {
+    tmem_alloc(tmem_slot, C::kTmemCols);
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  const uint32_t tS = tmem_base, tO = tmem_base + 256;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      mbar_expect_tx(q_full, C::kQBytes);
+#pragma unroll
+      for (int a = 0; a < HD / 64; ++a) tma_load_3d(sQ + a * (kTile * 128), &tm_qkv, q_full, h * HD + a * 64, q0, b);
+      for (int j = 0; j < n_kv; ++j) {
+        const int st = j & 1;
+        mbar_wait(&kv_empty[st], ((j >> 1) & 1) ^ 1);
+        mbar_expect_tx(&k_full[st], C::kKVBytes);
+#pragma unroll
+        for (int a = 0; a < HD / 64; ++a)
+          tma_load_3d(sK + st * C::kKVBytes + a * (kTile * 128), &tm_qkv, &k_full[st], Dl + h * HD + a * 64,
+                      j * kTile, b);
+        mbar_expect_tx(&v_full[st], C::kKVBytes);
+#pragma unroll
+        for (int a = 0; a < HD / 64; ++a)
+          tma_load_3d(sV + st * C::kKVBytes + a * (kTile * 128), &tm_qkv, &v_full[st], 2 * Dl + h * HD + a * 64,
+                      j * kTile, b);
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      constexpr uint32_t idesc_s = make_idesc_bf16(kTile, kTile, false, false);
+      constexpr uint32_t idesc_o = make_idesc_bf16(kTile, HD, false, true);
+      const uint32_t q_base = smem_u32(sQ), p_base = smem_u32(sP);
+      mbar_wait(q_full, 0);
+      // S(0); afterwards S(j+1) is issued before PV(j) so that QK^T overlaps the softmax of tile j
+      mbar_wait(&k_full[0], 0);
+      tc_fence_after();
+#pragma unroll
+      for (int kk = 0; kk < HD / 16; ++kk)
+        umma_bf16_ss(tS, desc_kmajor(q_base, kk, kTile * 128), desc_kmajor(smem_u32(sK), kk, kTile * 128), idesc_s,
+                     kk > 0);
+      umma_commit(&s_full[0]);
+      for (int j = 0; j < n_kv; ++j) {
+        const int st = j & 1;
+        if (j + 1 < n_kv) {
+          // S buffer (j+1)&1 was last read by the softmax of tile j-1, which finished before p_full(j-1)
+          const int sn = (j + 1) & 1;
+          mbar_wait(&k_full[sn], ((j + 1) >> 1) & 1);
+          tc_fence_after();
+          const uint32_t k_base = smem_u32(sK + sn * C::kKVBytes);
+#pragma unroll
+          for (int kk = 0; kk < HD / 16; ++kk)
+            umma_bf16_ss(tS + sn * 128, desc_kmajor(q_base, kk, kTile * 128), desc_kmajor(k_base, kk, kTile * 128),
+                         idesc_s, kk > 0);
+          umma_commit(&s_full[sn]);
+        }
+        mbar_wait(p_full, j & 1);
+        mbar_wait(&v_full[st], (j >> 1) & 1);
+        tc_fence_after();
+        const uint32_t v_base = smem_u32(sV + st * C::kKVBytes);
+#pragma unroll
+        for (int kk = 0; kk < kTile / 16; ++kk)
+          umma_bf16_ss(tO, desc_kmajor(p_base, kk, kTile * 128), desc_mnmajor(v_base, kk, kTile * 128), idesc_o,
+                       (j > 0 || kk > 0) ? 1u : 0u);
+        umma_commit(o_done);
+        umma_commit(&kv_empty[st]);
+      }
+    }
+  } else {
+    // ------------------------------------------------------------------ softmax warps: one thread per q row
+    const int q = warp & 3;
+    const int r = q * 32 + lane;  // row inside the tile == TMEM lane
+    const uint32_t lane_off = static_cast<uint32_t>(q * 32) << 16;
+    float m_run = -INFINITY, l_run = 0.f;
+    for (int j = 0; j < n_kv; ++j) {
+      mbar_wait(&s_full[j & 1], (j >> 1) & 1);
+      tc_fence_after();
+      float s[kTile];
+#pragma unroll
+      for (int c = 0; c < 4; ++c) {
+        uint32_t tmp[32];
+        tmem_ld32(tS + (j & 1) * 128 + lane_off + c * 32, tmp);
+        tmem_ld_wait();
+#pragma unroll
+        for (int i = 0; i < 32; ++i) s[c * 32 + i] = __uint_as_float(tmp[i]) * scale_log2;
+      }
+      if (j == qt) {  // diagonal tile: mask kv > q
+#pragma unroll
+        for (int i = 0; i < kTile; ++i)
+          if (i > r) s[i] = -INFINITY;
+      }
+      float mx = m_run;
+#pragma unroll
+      for (int i = 0; i < kTile; ++i) mx = fmaxf(mx, s[i]);
+      const float alpha = fast_exp2(m_run - mx);
+      m_run = mx;
+      float sum = 0.f;
+      uint32_t packed[kTile / 2];
+#pragma unroll
+      for (int i = 0; i < kTile; i += 2) {
+        const float p0 = fast_exp2(s[i] - mx), p1 = fast_exp2(s[i + 1] - mx);
+        sum += p0 + p1;
+        packed[i >> 1] = pack_bf16(p0, p1);
+      }
+      l_run = l_run * alpha + sum;
+      if (j > 0) {
+        // previous PV must be complete before O is rescaled and P is overwritten
+        mbar_wait(o_done, (j - 1) & 1);
+        tc_fence_after();
+        if (__any_sync(0xffffffffu, alpha != 1.f)) {
+#pragma unroll
+          for (int c = 0; c < HD / 32; ++c) {
+            uint32_t o[32];
+            tmem_ld32(tO + lane_off + c * 32, o);
+            tmem_ld_wait();
+#pragma unroll
+            for (int i = 0; i < 32; ++i) o[i] = __float_as_uint(__uint_as_float(o[i]) * alpha);
+            tmem_st32(tO + lane_off + c * 32, o);
+          }
+          tmem_st_wait();
+        }
+      }
+#pragma unroll
+      for (int c = 0; c < 4; ++c) {
+        uint32_t chunk[16];
+#pragma unroll
+        for (int i = 0; i < 16; ++i) chunk[i] = packed[c * 16 + i];
+        st_tile_row32(sP, r, c * 32, chunk);
+      }
+      fence_proxy_async_smem();
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(p_full);
+    }
+    // epilogue: O / l -> bf16, lse
+    mbar_wait(o_done, (n_kv - 1) & 1);
+    tc_fence_after();
+    const float inv_l = 1.f / l_run;
+    const bool valid = (q0 + r) < T;
+    __nv_bfloat16* orow = out + (static_cast<long long>(b) * T + q0 + r) * Dl + h * HD;
+#pragma unroll
+    for (int c = 0; c < HD / 32; ++c) {
+      uint32_t o[32];
+      tmem_ld32(tO + lane_off + c * 32, o);
+      tmem_ld_wait();
+      if (valid) {
+#pragma unroll
+        for (int v8 = 0; v8 < 4; ++v8) {
+          uint4 w;
+          w.x = pack_bf16(__uint_as_float(o[8 * v8 + 0]) * inv_l, __uint_as_float(o[8 * v8 + 1]) * inv_l);
+          w.y = pack_bf16(__uint_as_float(o[8 * v8 + 2]) * inv_l, __uint_as_float(o[8 * v8 + 3]) * inv_l);
+          w.z = pack_bf16(__uint_as_float(o[8 * v8 + 4]) * inv_l, __uint_as_float(o[8 * v8 + 5]) * inv_l);
+          w.w = pack_bf16(__uint_as_float(o[8 * v8 + 6]) * inv_l, __uint_as_float(o[8 * v8 + 7]) * inv_l);
+          *reinterpret_cast<uint4*>(orow + c * 32 + v8 * 8) = w;
+        }
+      }
+    }
+    if (valid && lse) lse[(static_cast<long long>(b) * H + h) * T + q0 + r] = (m_run + log2f(l_run)) * kLn2;
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, C::kTmemCols);
+  }
+}
+
+// ================================================================================================= backward
+// delta[b][h][i] = sum_c dO[i][c] * O[i][c]   (one warp per (row, head))
+__global__ void attn_delta_kernel(const __nv_bfloat16* __restrict__ o, const __nv_bfloat16* __restrict__ d_o,
+                                  float* __restrict__ delta, int B, int T, int H, int HD) {
+  const int warps = (blockDim.x >> 5) * gridDim.x;
+  const int lane = threadIdx.x & 31;
+  const long long total = static_cast<long long>(B) * T * H;
+  const int Dl = H * HD;
+  for (long long w = static_cast<long long>(blockIdx.x) * (blockDim.x >> 5) + (threadIdx.x >> 5); w < total;
+       w += warps) {
+    const long long row = w / H;
+    const int h = static_cast<int>(w % H);
+    const __nv_bfloat16* po = o + row * Dl + h * HD;
+    const __nv_bfloat16* pd = d_o + row * Dl + h * HD;
+    float acc = 0.f;
+    for (int c = lane * 2; c < HD; c += 64) {
+      const float2 a = unpack_bf16(*reinterpret_cast<const uint32_t*>(po + c));
+      const float2 g = unpack_bf16(*reinterpret_cast<const uint32_t*>(pd + c));
+      acc += a.x * g.x + a.y * g.y;
+    }
+    acc = warp_sum(acc);
+    if (lane == 0) {
+      const long long bb = row / T, tt = row % T;
+      delta[(bb * H + h) * T + tt] = acc;
+    }
+  }
+}
+
+// dq fp32 [M][Dl] -> bf16 into dqkv[:, 0:Dl]
+__global__ void attn_dq_convert_kernel(const float* __restrict__ dq, __nv_bfloat16* __restrict__ dqkv, long long M,
+                                       int Dl) {
+  const int vec = Dl / 4;
+  const long long total = M * vec;
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const long long row = i / vec;
+    const int c = static_cast<int>(i % vec) * 4;
+    const float4 v = *reinterpret_cast<const float4*>(dq + row * Dl + c);
+    uint2 o;
+    o.x = pack_bf16(v.x, v.y);
+    o.y = pack_bf16(v.z, v.w);
+    *reinterpret_cast<uint2*>(dqkv + row * 3 * Dl + c) = o;
+  }
+}
+
+template <int HD>
+struct BwdCfg {
+  static constexpr int kStages = (HD == 64) ? 2 : 1;
+  static constexpr int kTileBytes = kTile * HD * 2;  // K, V, Q or dO tile
+  static constexpr int kPBytes = kTile * kTile * 2;
+  static constexpr int kSmem = 2 * kTileBytes + kStages * 2 * kTileBytes + 2 * kPBytes + 256 + 1024;
+  static constexpr int kTmemCols = 512;  // S/dQ [0,128), dP [128,256), dV [256,256+HD), dK [256+HD, 256+2HD)
+};
+
+__device__ __forceinline__ void red_add_v4(float* addr, float a, float b, float c, float d) {
+  asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(a), "f"(b), "f"(c), "f"(d)
+               : "memory");
+}
+
+template <int HD>
+__global__ void __launch_bounds__(kAttnThreads, 1)
+attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constant__ CUtensorMap tm_do,
+                const float* __restrict__ lse, const float* __restrict__ delta, float* __restrict__ dq_acc,
+                __nv_bfloat16* __restrict__ dqkv, int T, int H, int Dl, float scale, float scale_log2) {
+  using C = BwdCfg<HD>;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* sK = smem;
+  uint8_t* sV = sK + C::kTileBytes;
+  uint8_t* sQ = sV + C::kTileBytes;                  // [stage]
+  uint8_t* sDO = sQ + C::kStages * C::kTileBytes;    // [stage]
+  uint8_t* sP = sDO + C::kStages * C::kTileBytes;
+  uint8_t* sDS = sP + C::kPBytes;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sDS + C::kPBytes);
+  uint64_t* kv_full = bars;
+  uint64_t* qdo_full = bars + 1;   // [2]
+  uint64_t* qdo_empty = bars + 3;  // [2]
+  uint64_t* sdp_full = bars + 5;
+  uint64_t* pds_full = bars + 6;
+  uint64_t* dq_full = bars + 7;
+  uint64_t* s_free = bars + 8;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 9);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int nq = (T + kTile - 1) / kTile;
+  const int jt = blockIdx.x;  // kv tile; tile 0 has the most q tiles -> scheduled first
+  const int h = blockIdx.y, b = blockIdx.z;
+  const int kv0 = jt * kTile;
+  const int n_it = nq - jt;
+
+  if (threadIdx.x == 0) {
+    prefetch_tmap(&tm_qkv);
+    prefetch_tmap(&tm_do);
+    mbar_init(kv_full, 1);
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(&qdo_full[i], 1);
+      mbar_init(&qdo_empty[i], 1);
+    }
+    mbar_init(sdp_full, 1);
+    mbar_init(pds_full, 4);
+    mbar_init(dq_full, 1);
+    mbar_init(s_free, 4);
+    fence_mbar_init();
+  }
+  if (warp == 1) {
+    tmem_alloc(tmem_slot, C::kTmemCols);
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  const uint32_t tS = tmem_base, tDP = tmem_base + 128, tDV = tmem_base + 256, tDK = tmem_base + 256 + HD;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      mbar_expect_tx(kv_full, 2 * C::kTileBytes);
+#pragma unroll
+      for (int a = 0; a < HD / 64; ++a) {
+        tma_load_3d(sK + a * (kTile * 128), &tm_qkv, kv_full, Dl + h * HD + a * 64, kv0, b);
+        tma_load_3d(sV + a * (kTile * 128), &tm_qkv, kv_full, 2 * Dl + h * HD + a * 64, kv0, b);
+      }
+      for (int it = 0; it < n_it; ++it) {
+        const int st = it % C::kStages;
+        const int q0 = (jt + it) * kTile;
+        mbar_wait(&qdo_empty[st], ((it / C::kStages) & 1) ^ 1);
+        mbar_expect_tx(&qdo_full[st], 2 * C::kTileBytes);
+#pragma unroll
+        for (int a = 0; a < HD / 64; ++a) {
+          tma_load_3d(sQ + st * C::kTileBytes + a * (kTile * 128), &tm_qkv, &qdo_full[st], h * HD + a * 64, q0, b);
+          tma_load_3d(sDO + st * C::kTileBytes + a * (kTile * 128), &tm_do, &qdo_full[st], h * HD + a * 64, q0, b);
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      constexpr uint32_t idesc_s = make_idesc_bf16(kTile, kTile, false, false);   // S, dP
+      constexpr uint32_t idesc_kv = make_idesc_bf16(kTile, HD, true, true);       // dV, dK
+      constexpr uint32_t idesc_q = make_idesc_bf16(kTile, HD, false, true);       // dQ
+      const uint32_t k_base = smem_u32(sK), v_base = smem_u32(sV), p_base = smem_u32(sP), ds_base = smem_u32(sDS);
+      constexpr uint32_t kAtom = kTile * 128;
+      mbar_wait(kv_full, 0);
+      for (int it = 0; it < n_it; ++it) {
+        const int st = it % C::kStages;
+        const uint32_t q_base = smem_u32(sQ + st * C::kTileBytes), do_base = smem_u32(sDO + st * C::kTileBytes);
+        mbar_wait(&qdo_full[st], (it / C::kStages) & 1);
+        if (it > 0) mbar_wait(s_free, (it - 1) & 1);
+        tc_fence_after();
+#pragma unroll
+        for (int kk = 0; kk < HD / 16; ++kk)
+          umma_bf16_ss(tS, desc_kmajor(q_base, kk, kAtom), desc_kmajor(k_base, kk, kAtom), idesc_s, kk > 0);
+#pragma unroll
+        for (int kk = 0; kk < HD / 16; ++kk)
+          umma_bf16_ss(tDP, desc_kmajor(do_base, kk, kAtom), desc_kmajor(v_base, kk, kAtom), idesc_s, kk > 0);
+        umma_commit(sdp_full);
+        mbar_wait(pds_full, it & 1);
+        tc_fence_after();
+#pragma unroll
+        for (int kk = 0; kk < kTile / 16; ++kk)  // dV += P^T dO   (reduction over the 128 q rows)
+          umma_bf16_ss(tDV, desc_mnmajor(p_base, kk, kAtom), desc_mnmajor(do_base, kk, kAtom), idesc_kv,
+                       (it > 0 || kk > 0) ? 1u : 0u);
+#pragma unroll
+        for (int kk = 0; kk < kTile / 16; ++kk)  // dK += dS^T Q
+          umma_bf16_ss(tDK, desc_mnmajor(ds_base, kk, kAtom), desc_mnmajor(q_base, kk, kAtom), idesc_kv,
+                       (it > 0 || kk > 0) ? 1u : 0u);
+        umma_commit(&qdo_empty[st]);
+#pragma unroll
+        for (int kk = 0; kk < kTile / 16; ++kk)  // dQ = dS K   (reduction over the 128 kv rows)
+          umma_bf16_ss(tS, desc_kmajor(ds_base, kk, kAtom), desc_mnmajor(k_base, kk, kAtom), idesc_q, kk > 0);
+        umma_commit(dq_full);
+      }
+    }
+  } else {
+    const int q = warp & 3;
+    const int r = q * 32 + lane;
+    const uint32_t lane_off = static_cast<uint32_t>(q * 32) << 16;
+    for (int it = 0; it < n_it; ++it) {
+      const int q0 = (jt + it) * kTile;
+      const bool row_valid = (q0 + r) < T;
+      const long long stat_idx = (static_cast<long long>(b) * H + h) * T + q0 + r;
+      const float lse2 = row_valid ? lse[stat_idx] * kLog2e : 0.f;
+      const float dlt = row_valid ? delta[stat_idx] : 0.f;
+      mbar_wait(sdp_full, it & 1);
+      tc_fence_after();
+#pragma unroll 1
+      for (int c = 0; c < 4; ++c) {
+        uint32_t sv[32], dv[32];
+        tmem_ld32(tS + lane_off + c * 32, sv);
+        tmem_ld32(tDP + lane_off + c * 32, dv);
+        tmem_ld_wait();
+        uint32_t pp[16], dd[16];
+#pragma unroll
+        for (int i = 0; i < 32; i += 2) {
+          float p0 = fast_exp2(__uint_as_float(sv[i]) * scale_log2 - lse2);
+          float p1 = fast_exp2(__uint_as_float(sv[i + 1]) * scale_log2 - lse2);
+          const int col = c * 32 + i;
+          if (!row_valid || (it == 0 && col > r)) p0 = 0.f;
+          if (!row_valid || (it == 0 && col + 1 > r)) p1 = 0.f;
+          const float d0 = p0 * (__uint_as_float(dv[i]) - dlt) * scale;
+          const float d1 = p1 * (__uint_as_float(dv[i + 1]) - dlt) * scale;
+          pp[i >> 1] = pack_bf16(p0, p1);
+          dd[i >> 1] = pack_bf16(d0, d1);
+        }
+        st_tile_row32(sP, r, c * 32, pp);
+        st_tile_row32(sDS, r, c * 32, dd);
+      }
+      fence_proxy_async_smem();
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(pds_full);
+      // dQ tile -> fp32 atomics
+      mbar_wait(dq_full, it & 1);
+      tc_fence_after();
+      float* dq_row = dq_acc + (static_cast<long long>(b) * T + q0 + r) * Dl + h * HD;
+#pragma unroll 1
+      for (int c = 0; c < HD / 32; ++c) {
+        uint32_t v[32];
+        tmem_ld32(tS + lane_off + c * 32, v);
+        tmem_ld_wait();
+        if (row_valid) {
+#pragma unroll
+          for (int i = 0; i < 32; i += 4)
+            red_add_v4(dq_row + c * 32 + i, __uint_as_float(v[i]), __uint_as_float(v[i + 1]),
+                       __uint_as_float(v[i + 2]), __uint_as_float(v[i + 3]));
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(s_free);
+    }
+    // all MMAs (incl. the last dV / dK updates) completed before the last dq_full fired
+    const bool kv_valid = (kv0 + r) < T;
+    __nv_bfloat16* drow = dqkv + (static_cast<long long>(b) * T + kv0 + r) * 3 * Dl + h * HD;
+#pragma unroll 1
+    for (int which = 0; which < 2; ++which) {  // 0: dK -> segment 1, 1: dV -> segment 2
+      const uint32_t tsrc = which == 0 ? tDK : tDV;
+      __nv_bfloat16* dst = drow + (which + 1) * Dl;
+#pragma unroll 1
+      for (int c = 0; c < HD / 32; ++c) {
+        uint32_t v[32];
+        tmem_ld32(tsrc + lane_off + c * 32, v);
+        tmem_ld_wait();
+        if (kv_valid) {
+#pragma unroll
+          for (int v8 = 0; v8 < 4; ++v8) {
+            uint4 w;
+            w.x = pack_bf16(__uint_as_float(v[8 * v8 + 0]), __uint_as_float(v[8 * v8 + 1]));
+            w.y = pack_bf16(__uint_as_float(v[8 * v8 + 2]), __uint_as_float(v[8 * v8 + 3]));
+            w.z = pack_bf16(__uint_as_float(v[8 * v8 + 4]), __uint_as_float(v[8 * v8 + 5]));
+            w.w = pack_bf16(__uint_as_float(v[8 * v8 + 6]), __uint_as_float(v[8 * v8 + 7]));
+            *reinterpret_cast<uint4*>(dst + c * 32 + v8 * 8) = w;
+          }
+        }
+      }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, C::kTmemCols);
+  }
+}
+
+// ------------------------------------------------------------------------------------------------- host
+static PFN_cuTensorMapEncodeTiled_v12000 encode_fn() {
+  static PFN_cuTensorMapEncodeTiled_v12000 fn = nullptr;
+  if (!fn) {
+    cudaDriverEntryPointQueryResult q;
+    void* p = nullptr;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) != cudaSuccess ||
+        q != cudaDriverEntryPointSuccess)
+      return nullptr;
+    fn = reinterpret_cast<PFN_cuTensorMapEncodeTiled_v12000>(p);
+  }
+  return fn;
+}
+
+// 3-D bf16 map over [B][T][ld] (row-major rows of `cols` valid columns): box = 64 cols x 128 rows x 1 batch.
+static int make_tmap_rows3d(CUtensorMap* tm, const void* ptr, int cols, int T, int B, long long ld) {
+  auto fn = encode_fn();
+  if (!fn) return -1;
+  cuuint64_t dims[3] = {static_cast<cuuint64_t>(cols), static_cast<cuuint64_t>(T), static_cast<cuuint64_t>(B)};
+  cuuint64_t strides[2] = {static_cast<cuuint64_t>(ld) * 2, static_cast<cuuint64_t>(ld) * 2 * T};
+  cuuint32_t box[3] = {64, kTile, 1};
+  cuuint32_t estr[3] = {1, 1, 1};
+  CUresult r = fn(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<void*>(ptr), dims, strides, box, estr,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  return r == CUDA_SUCCESS ? 0 : -2;
+}
+
+template <int HD>
+static int launch_fwd(const CUtensorMap& tm, void* out, float* lse, int B, int T, int H, float scale,
+                      cudaStream_t stream) {
+  using C = FwdCfg<HD>;
+  auto kfn = attn_fwd_kernel<HD>;
+  static bool configured = false;
+  if (!configured) {
+    cudaError_t e = cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmem);
+    if (e != cudaSuccess) return static_cast<int>(e);
+    configured = true;
+  }
+  dim3 grid((T + kTile - 1) / kTile, H, B);
+  kfn<<<grid, kAttnThreads, C::kSmem, stream>>>(tm, reinterpret_cast<__nv_bfloat16*>(out), lse, T, H, H * HD,
+                                               scale * kLog2e);
+  return static_cast<int>(cudaGetLastError());
+}
+
+template <int HD>
+static int launch_bwd(const CUtensorMap& tm_qkv, const CUtensorMap& tm_do, const float* lse, const float* delta,
+                      float* dq_acc, void* dqkv, int B, int T, int H, float scale, cudaStream_t stream) {
+  using C = BwdCfg<HD>;
+  auto kfn = attn_bwd_kernel<HD>;
+  static bool configured = false;
+  if (!configured) {
+    cudaError_t e = cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmem);
+    if (e != cudaSuccess) return static_cast<int>(e);
+    configured = true;
+  }
+  dim3 grid((T + kTile - 1) / kTile, H, B);
+  kfn<<<grid, kAttnThreads, C::kSmem, stream>>>(tm_qkv, tm_do, lse, delta, dq_acc,
+                                               reinterpret_cast<__nv_bfloat16*>(dqkv), T, H, H * HD, scale,
+                                               scale * kLog2e);
+  return static_cast<int>(cudaGetLastError());
+}
+
+}  // namespace dpfs
+
+using namespace dpfs;
+
+extern "C" int dpfs_attn_fwd(const void* qkv, void* out, float* lse, int B, int T, int H, int HD, float scale,
+                             cudaStream_t stream) {
+  if (HD != 64 && HD != 128) return -40;
+  if (B <= 0 || T <= 0 || H <= 0) return 0;
+  CUtensorMap tm;
+  int rc = make_tmap_rows3d(&tm, qkv, 3 * H * HD, T, B, 3LL * H * HD);
+  if (rc) return rc;
+  return HD == 64 ? launch_fwd<64>(tm, out, lse, B, T, H, scale, stream)
+                  : launch_fwd<128>(tm, out, lse, B, T, H, scale, stream);
+}
+
+// dq_acc: fp32 [B*T][H*HD] scratch (zeroed here); delta: fp32 [B][H][T] scratch.
+extern "C" int dpfs_attn_bwd(const void* qkv, const void* out, const void* d_out, const float* lse, float* delta,
+                             float* dq_acc, void* dqkv, int B, int T, int H, int HD, float scale,
+                             cudaStream_t stream) {
+  if (HD != 64 && HD != 128) return -40;
+  if (B <= 0 || T <= 0 || H <= 0) return 0;
+  const int Dl = H * HD;
+  const long long M = static_cast<long long>(B) * T;
+  CUtensorMap tm_qkv, tm_do;
+  int rc = make_tmap_rows3d(&tm_qkv, qkv, 3 * Dl, T, B, 3LL * Dl);
+  if (rc) return rc;
+  rc = make_tmap_rows3d(&tm_do, d_out, Dl, T, B, Dl);
+  if (rc) return rc;
+  cudaMemsetAsync(dq_acc, 0, sizeof(float) * M * Dl, stream);
+  {
+    const long long warps = M * H;
+    long long blocks = (warps + 7) / 8;
+    if (blocks > num_sms() * 16LL) blocks = num_sms() * 16LL;
+    attn_delta_kernel<<<static_cast<int>(blocks), 256, 0, stream>>>(
+        reinterpret_cast<const __nv_bfloat16*>(out), reinterpret_cast<const __nv_bfloat16*>(d_out), delta, B, T, H,
+        HD);
+  }
+  rc = HD == 64 ? launch_bwd<64>(tm_qkv, tm_do, lse, delta, dq_acc, dqkv, B, T, H, scale, stream)
+                : launch_bwd<128>(tm_qkv, tm_do, lse, delta, dq_acc, dqkv, B, T, H, scale, stream);
+  if (rc) return rc;
+  {
+    const long long total = M * (Dl / 4);
+    long long blocks = (total + 255) / 256;
+    if (blocks > num_sms() * 16LL) blocks = num_sms() * 16LL;
+    attn_dq_convert_kernel<<<static_cast<int>(blocks), 256, 0, stream>>>(
+        dq_acc, reinterpret_cast<__nv_bfloat16*>(dqkv), M, Dl);
+  }
+  return static_cast<int>(cudaGetLastError());
+}

@@ -1,0 +1,708 @@
+// Fused memory-bound kernels of the training step: RMSNorm / LayerNorm fwd+bwd, SwiGLU / GELU fwd+bwd, RoPE,
+// column sums (bias grads), dtype casts.  Each replaces a chain of ATen elementwise kernels in the reference
+// (models/layers.py:151-155, models/model.py:17-31,95) with a single pass over HBM.
+#include "common.cuh"
+#include "dpfs_b200.h"
+
+namespace dpfs {
+
+// --------------------------------------------------------------------------------------------- helpers
+struct alignas(16) F4 {
+  float x, y, z, w;
+};
+
+template <typename T>
+__device__ __forceinline__ void load4(const T* p, float (&v)[4]);
+template <>
+__device__ __forceinline__ void load4<float>(const float* p, float (&v)[4]) {
+  const float4 t = *reinterpret_cast<const float4*>(p);
+  v[0] = t.x;
+  v[1] = t.y;
+  v[2] = t.z;
+  v[3] = t.w;
+}
+template <>
+__device__ __forceinline__ void load4<__nv_bfloat16>(const __nv_bfloat16* p, float (&v)[4]) {
+  const uint2 t = *reinterpret_cast<const uint2*>(p);
+  const float2 a = unpack_bf16(t.x), b = unpack_bf16(t.y);
+  v[0] = a.x;
+  v[1] = a.y;
+  v[2] = b.x;
+  v[3] = b.y;
+}
+template <typename T>
+__device__ __forceinline__ void store4(T* p, const float (&v)[4]);
+template <>
+__device__ __forceinline__ void store4<float>(float* p, const float (&v)[4]) {
+  *reinterpret_cast<float4*>(p) = make_float4(v[0], v[1], v[2], v[3]);
+}
+template <>
+__device__ __forceinline__ void store4<__nv_bfloat16>(__nv_bfloat16* p, const float (&v)[4]) {
+  uint2 t;
+  t.x = pack_bf16(v[0], v[1]);
+  t.y = pack_bf16(v[2], v[3]);
+  *reinterpret_cast<uint2*>(p) = t;
+}
+
+constexpr int kNormThreads = 256;  // 8 warps, one row per warp at a time
+constexpr int kMaxNV = 16;         // float4 per lane -> D <= 2048 per warp-row
+
+// --------------------------------------------------------------------------------------------- RMSNorm fwd
+// y = scale * x * rsqrt(mean(x^2) + eps); statistics in fp32 (reference models/layers.py:151-155).
+template <typename XT, typename YT, int NV>
+__global__ void __launch_bounds__(kNormThreads) rmsnorm_fwd_kernel(const XT* __restrict__ x,
+                                                                   const float* __restrict__ scale,
+                                                                   YT* __restrict__ y, float* __restrict__ rstd_out,
+                                                                   int M, int D, float eps) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int wpb = kNormThreads / 32;
+  float sc[NV][4];
+#pragma unroll
+  for (int i = 0; i < NV; ++i) {
+    const int c = (i * 32 + lane) * 4;
+    if (c < D) load4<float>(scale + c, sc[i]);
+  }
+  for (int row = blockIdx.x * wpb + warp; row < M; row += gridDim.x * wpb) {
+    const XT* xr = x + static_cast<long long>(row) * D;
+    float v[NV][4];
+    float ss = 0.f;
+#pragma unroll
+    for (int i = 0; i < NV; ++i) {
+      const int c = (i * 32 + lane) * 4;
+      if (c < D) {
+        load4<XT>(xr + c, v[i]);
+        ss += v[i][0] * v[i][0] + v[i][1] * v[i][1] + v[i][2] * v[i][2] + v[i][3] * v[i][3];
+      }
+    }
+    ss = warp_sum(ss);
+    const float rstd = rsqrtf(ss / D + eps);
+    if (lane == 0 && rstd_out) rstd_out[row] = rstd;
+    YT* yr = y + static_cast<long long>(row) * D;
+#pragma unroll
+    for (int i = 0; i < NV; ++i) {
+      const int c = (i * 32 + lane) * 4;
+      if (c < D) {
+        float o[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) o[j] = v[i][j] * rstd * sc[i][j];
+        store4<YT>(yr + c, o);
+      }
+    }
+  }
+}
+
+// --------------------------------------------------------------------------------------------- RMSNorm bwd
+// dx = dres + rstd * (g - xhat * mean(g * xhat)),  g = dy * scale, xhat = x * rstd;  dscale = sum_rows dy * xhat.
+// Each block writes one row of per-block dscale partials into `scratch` [gridDim.x][D]; a second kernel sums them
+// in a fixed order (deterministic).
+template <typename XT, typename GT, int NV>
+__global__ void __launch_bounds__(kNormThreads) rmsnorm_bwd_kernel(
+    const GT* __restrict__ dy, const XT* __restrict__ x, const float* __restrict__ rstd_in,
+    const float* __restrict__ scale, const float* __restrict__ dres, float* __restrict__ dx,
+    __nv_bfloat16* __restrict__ dx_bf16, float* __restrict__ scratch, int M, int D) {
+  __shared__ float red[kNormThreads / 32][32 * 4];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int wpb = kNormThreads / 32;
+  float sc[NV][4], ds[NV][4];
+#pragma unroll
+  for (int i = 0; i < NV; ++i) {
+    const int c = (i * 32 + lane) * 4;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) ds[i][j] = 0.f;
+    if (c < D) load4<float>(scale + c, sc[i]);
+  }
+  for (int row = blockIdx.x * wpb + warp; row < M; row += gridDim.x * wpb) {
+    const long long off = static_cast<long long>(row) * D;
+    const float rstd = rstd_in[row];
+    float xh[NV][4], g[NV][4];
+    float dot = 0.f;
+#pragma unroll
+    for (int i = 0; i < NV; ++i) {
+      const int c = (i * 32 + lane) * 4;
+      if (c < D) {
+        float xv[4], dv[4];
+        load4<XT>(x + off + c, xv);
+        load4<GT>(dy + off + c, dv);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          xh[i][j] = xv[j] * rstd;
+          g[i][j] = dv[j] * sc[i][j];
+          ds[i][j] += dv[j] * xh[i][j];
+          dot += g[i][j] * xh[i][j];
+        }
+      }
+    }
+    dot = warp_sum(dot) / D;
+#pragma unroll
+    for (int i = 0; i < NV; ++i) {
+      const int c = (i * 32 + lane) * 4;
+      if (c < D) {
+        float o[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) o[j] = rstd * (g[i][j] - xh[i][j] * dot);
+        if (dres) {
+          float r[4];
+          load4<float>(dres + off + c, r);
+#pragma unroll
+          for (int j = 0; j < 4; ++j) o[j] += r[j];
+        }
+        if (dx) store4<float>(dx + off + c, o);
+        if (dx_bf16) store4<__nv_bfloat16>(dx_bf16 + off + c, o);
+      }
+    }
+  }
+  // block-level reduction of the dscale partials: warps -> smem -> warp 0 sums in fixed order
+#pragma unroll
+  for (int i = 0; i < NV; ++i) {
+    __syncthreads();
+#pragma unroll
+    for (int j = 0; j < 4; ++j) red[warp][lane * 4 + j] = ds[i][j];
+    __syncthreads();
+    if (warp == 0) {
+      const int c = (i * 32 + lane) * 4;
+      if (c < D) {
+        float o[4] = {0.f, 0.f, 0.f, 0.f};
+        for (int w = 0; w < wpb; ++w)
+#pragma unroll
+          for (int j = 0; j < 4; ++j) o[j] += red[w][lane * 4 + j];
+        store4<float>(scratch + static_cast<long long>(blockIdx.x) * D + c, o);
+      }
+    }
+  }
+}
+
+// out[c] = sum_b partial[b][c]
+__global__ void reduce_partials_kernel(const float* __restrict__ partial, float* __restrict__ out, int nblocks,
+                                       int D, int accumulate) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= D) return;
+  float s = 0.f;
+  for (int b = 0; b < nblocks; ++b) s += partial[static_cast<long long>(b) * D + c];
+  out[c] = accumulate ? out[c] + s : s;
+}
+
+// --------------------------------------------------------------------------------------------- LayerNorm
+// y = (x - mean) * rstd * gamma + beta.  (The reference only has RMSNorm; LayerNorm is provided because the
+// north-star names it.)  One warp per row, fp32 statistics.
+template <typename XT, typename YT, int NV>
+__global__ void __launch_bounds__(kNormThreads) layernorm_fwd_kernel(const XT* __restrict__ x,
+                                                                     const float* __restrict__ gamma,
+                                                                     const float* __restrict__ beta,
+                                                                     YT* __restrict__ y, float* __restrict__ mean_out,
+                                                                     float* __restrict__ rstd_out, int M, int D,
+                                                                     float eps) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int wpb = kNormThreads / 32;
+  for (int row = blockIdx.x * wpb + warp; row < M; row += gridDim.x * wpb) {
+    const XT* xr = x + static_cast<long long>(row) * D;
+    float v[NV][4];
+    float s = 0.f;
+#pragma unroll
+    for (int i = 0; i < NV; ++i) {
+      const int c = (i * 32 + lane) * 4;
+      if (c < D) {
+        load4<XT>(xr + c, v[i]);
+        s += v[i][0] + v[i][1] + v[i][2] + v[i][3];
+      }
+    }
+    const float mean = warp_sum(s) / D;
+    float ss = 0.f;
+#pragma unroll
+    for (int i = 0; i < NV; ++i) {
+      const int c = (i * 32 + lane) * 4;
+      if (c < D) {
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const float d = v[i][j] - mean;
+          ss += d * d;
+        }
+      }
+    }
+    const float rstd = rsqrtf(warp_sum(ss) / D + eps);
+    if (lane == 0) {
+      if (mean_out) mean_out[row] = mean;
+      if (rstd_out) rstd_out[row] = rstd;
+    }
+    YT* yr = y + static_cast<long long>(row) * D;
+#pragma unroll
+    for (int i = 0; i < NV; ++i) {
+      const int c = (i * 32 + lane) * 4;
+      if (c < D) {
+        float gm[4], bt[4] = {0.f, 0.f, 0.f, 0.f}, o[4];
+        load4<float>(gamma + c, gm);
+        if (beta) load4<float>(beta + c, bt);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) o[j] = (v[i][j] - mean) * rstd * gm[j] + bt[j];
+        store4<YT>(yr + c, o);
+      }
+    }
+  }
+}
+
+// dx = rstd * (g - mean(g) - xhat * mean(g*xhat)), g = dy*gamma; dgamma = sum dy*xhat; dbeta = sum dy.
+// scratch: [gridDim.x][2*D] (dgamma partials then dbeta partials).
+template <typename XT, typename GT, int NV>
+__global__ void __launch_bounds__(kNormThreads) layernorm_bwd_kernel(
+    const GT* __restrict__ dy, const XT* __restrict__ x, const float* __restrict__ mean_in,
+    const float* __restrict__ rstd_in, const float* __restrict__ gamma, float* __restrict__ dx,
+    float* __restrict__ scratch, int M, int D) {
+  __shared__ float red[kNormThreads / 32][32 * 4];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int wpb = kNormThreads / 32;
+  float dg[NV][4], db[NV][4];
+#pragma unroll
+  for (int i = 0; i < NV; ++i)
+#pragma unroll
+    for (int j = 0; j < 4; ++j) dg[i][j] = db[i][j] = 0.f;
+  for (int row = blockIdx.x * wpb + warp; row < M; row += gridDim.x * wpb) {
+    const long long off = static_cast<long long>(row) * D;
+    const float mean = mean_in[row], rstd = rstd_in[row];
+    float xh[NV][4], g[NV][4];
+    float s1 = 0.f, s2 = 0.f;
+#pragma unroll
+    for (int i = 0; i < NV; ++i) {
+      const int c = (i * 32 + lane) * 4;
+      if (c < D) {
+        float xv[4], dv[4], gm[4];
+        load4<XT>(x + off + c, xv);
+        load4<GT>(dy + off + c, dv);
+        load4<float>(gamma + c, gm);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          xh[i][j] = (xv[j] - mean) * rstd;
+          g[i][j] = dv[j] * gm[j];
+          dg[i][j] += dv[j] * xh[i][j];
+          db[i][j] += dv[j];
+          s1 += g[i][j];
+          s2 += g[i][j] * xh[i][j];
+        }
+      }
+    }
+    s1 = warp_sum(s1) / D;
+    s2 = warp_sum(s2) / D;
+#pragma unroll
+    for (int i = 0; i < NV; ++i) {
+      const int c = (i * 32 + lane) * 4;
+      if (c < D) {
+        float o[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) o[j] = rstd * (g[i][j] - s1 - xh[i][j] * s2);
+        store4<float>(dx + off + c, o);
+      }
+    }
+  }
+#pragma unroll
+  for (int pass = 0; pass < 2; ++pass) {
+#pragma unroll
+    for (int i = 0; i < NV; ++i) {
+      __syncthreads();
+#pragma unroll
+      for (int j = 0; j < 4; ++j) red[warp][lane * 4 + j] = pass == 0 ? dg[i][j] : db[i][j];
+      __syncthreads();
+      if (warp == 0) {
+        const int c = (i * 32 + lane) * 4;
+        if (c < D) {
+          float o[4] = {0.f, 0.f, 0.f, 0.f};
+          for (int w = 0; w < wpb; ++w)
+#pragma unroll
+            for (int j = 0; j < 4; ++j) o[j] += red[w][lane * 4 + j];
+          store4<float>(scratch + static_cast<long long>(blockIdx.x) * 2 * D + pass * D + c, o);
+        }
+      }
+    }
+  }
+}
+
+// --------------------------------------------------------------------------------------------- SwiGLU / GELU
+// gu: [M][2F] bf16 with the gate in columns [0,F) and the up projection in [F,2F) (concatenated weights);
+// act = silu(gate) * up   (reference models/model.py:95).
+__global__ void swiglu_fwd_kernel(const __nv_bfloat16* __restrict__ gu, __nv_bfloat16* __restrict__ act, int M,
+                                  int F) {
+  const long long total = static_cast<long long>(M) * (F / 8);
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const int row = static_cast<int>(i / (F / 8));
+    const int c = static_cast<int>(i % (F / 8)) * 8;
+    const uint4 gv = *reinterpret_cast<const uint4*>(gu + static_cast<long long>(row) * 2 * F + c);
+    const uint4 uv = *reinterpret_cast<const uint4*>(gu + static_cast<long long>(row) * 2 * F + F + c);
+    const uint32_t gw[4] = {gv.x, gv.y, gv.z, gv.w}, uw[4] = {uv.x, uv.y, uv.z, uv.w};
+    uint32_t ow[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const float2 g = unpack_bf16(gw[j]), u = unpack_bf16(uw[j]);
+      const float a0 = g.x / (1.f + __expf(-g.x)) * u.x;
+      const float a1 = g.y / (1.f + __expf(-g.y)) * u.y;
+      ow[j] = pack_bf16(a0, a1);
+    }
+    *reinterpret_cast<uint4*>(act + static_cast<long long>(row) * F + c) = make_uint4(ow[0], ow[1], ow[2], ow[3]);
+  }
+}
+
+// dgu[:, :F] = dact * up * silu'(gate);  dgu[:, F:] = dact * silu(gate)
+__global__ void swiglu_bwd_kernel(const __nv_bfloat16* __restrict__ dact, const __nv_bfloat16* __restrict__ gu,
+                                  __nv_bfloat16* __restrict__ dgu, int M, int F) {
+  const long long total = static_cast<long long>(M) * (F / 8);
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const int row = static_cast<int>(i / (F / 8));
+    const int c = static_cast<int>(i % (F / 8)) * 8;
+    const long long go = static_cast<long long>(row) * 2 * F + c;
+    const uint4 gv = *reinterpret_cast<const uint4*>(gu + go);
+    const uint4 uv = *reinterpret_cast<const uint4*>(gu + go + F);
+    const uint4 dv = *reinterpret_cast<const uint4*>(dact + static_cast<long long>(row) * F + c);
+    const uint32_t gw[4] = {gv.x, gv.y, gv.z, gv.w}, uw[4] = {uv.x, uv.y, uv.z, uv.w},
+                   dw[4] = {dv.x, dv.y, dv.z, dv.w};
+    uint32_t og[4], ou[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const float2 g = unpack_bf16(gw[j]), u = unpack_bf16(uw[j]), d = unpack_bf16(dw[j]);
+      const float s0 = 1.f / (1.f + __expf(-g.x)), s1 = 1.f / (1.f + __expf(-g.y));
+      const float dg0 = d.x * u.x * s0 * (1.f + g.x * (1.f - s0));
+      const float dg1 = d.y * u.y * s1 * (1.f + g.y * (1.f - s1));
+      og[j] = pack_bf16(dg0, dg1);
+      ou[j] = pack_bf16(d.x * g.x * s0, d.y * g.y * s1);
+    }
+    *reinterpret_cast<uint4*>(dgu + go) = make_uint4(og[0], og[1], og[2], og[3]);
+    *reinterpret_cast<uint4*>(dgu + go + F) = make_uint4(ou[0], ou[1], ou[2], ou[3]);
+  }
+}
+
+// tanh-approximation GELU (GPT-2 flavour), elementwise bf16.  Provided because the north-star names GELU; the
+// reference model itself only uses SiLU gating.
+__device__ __forceinline__ float gelu_f(float x) {
+  const float k = 0.7978845608028654f, a = 0.044715f;
+  return 0.5f * x * (1.f + tanhf(k * (x + a * x * x * x)));
+}
+__device__ __forceinline__ float gelu_grad_f(float x) {
+  const float k = 0.7978845608028654f, a = 0.044715f;
+  const float t = tanhf(k * (x + a * x * x * x));
+  return 0.5f * (1.f + t) + 0.5f * x * (1.f - t * t) * k * (1.f + 3.f * a * x * x);
+}
+__global__ void gelu_fwd_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ y, long long n8) {
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < n8;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const uint4 xv = *reinterpret_cast<const uint4*>(x + i * 8);
+    const uint32_t xw[4] = {xv.x, xv.y, xv.z, xv.w};
+    uint32_t ow[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const float2 a = unpack_bf16(xw[j]);
+      ow[j] = pack_bf16(gelu_f(a.x), gelu_f(a.y));
+    }
+    *reinterpret_cast<uint4*>(y + i * 8) = make_uint4(ow[0], ow[1], ow[2], ow[3]);
+  }
+}
+__global__ void gelu_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ x,
+                                __nv_bfloat16* __restrict__ dx, long long n8) {
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < n8;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const uint4 xv = *reinterpret_cast<const uint4*>(x + i * 8);
+    const uint4 dv = *reinterpret_cast<const uint4*>(dy + i * 8);
+    const uint32_t xw[4] = {xv.x, xv.y, xv.z, xv.w}, dw[4] = {dv.x, dv.y, dv.z, dv.w};
+    uint32_t ow[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const float2 a = unpack_bf16(xw[j]), d = unpack_bf16(dw[j]);
+      ow[j] = pack_bf16(d.x * gelu_grad_f(a.x), d.y * gelu_grad_f(a.y));
+    }
+    *reinterpret_cast<uint4*>(dx + i * 8) = make_uint4(ow[0], ow[1], ow[2], ow[3]);
+  }
+}
+
+// --------------------------------------------------------------------------------------------- RoPE
+// In-place rotary embedding ("rotate_half" convention, reference models/model.py:17-31) on the q and k segments of
+// a packed [M][ld] bf16 buffer.  Segment s (0..nseg-1) starts at column s*seg_stride and holds H heads of hd.
+// cos/sin tables: fp32 [maxlen][hd/2], indexed by pos[m].  sign = +1 forward, -1 backward (inverse rotation).
+__global__ void rope_kernel(__nv_bfloat16* __restrict__ buf, long long ld, const long long* __restrict__ pos,
+                            const float* __restrict__ cos_t, const float* __restrict__ sin_t, int M, int nseg,
+                            int seg_stride, int H, int hd, float sign) {
+  const int half = hd / 2;
+  const int vec_per_head = half / 8;
+  const long long per_row = static_cast<long long>(nseg) * H * vec_per_head;
+  const long long total = static_cast<long long>(M) * per_row;
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const int row = static_cast<int>(i / per_row);
+    int r = static_cast<int>(i % per_row);
+    const int seg = r / (H * vec_per_head);
+    r -= seg * H * vec_per_head;
+    const int h = r / vec_per_head;
+    const int j0 = (r % vec_per_head) * 8;
+    const long long p = pos[row];
+    __nv_bfloat16* base = buf + static_cast<long long>(row) * ld + seg * seg_stride + h * hd + j0;
+    const uint4 a = *reinterpret_cast<const uint4*>(base);
+    const uint4 b = *reinterpret_cast<const uint4*>(base + half);
+    const float4 c0 = *reinterpret_cast<const float4*>(cos_t + p * half + j0);
+    const float4 c1 = *reinterpret_cast<const float4*>(cos_t + p * half + j0 + 4);
+    const float4 s0 = *reinterpret_cast<const float4*>(sin_t + p * half + j0);
+    const float4 s1 = *reinterpret_cast<const float4*>(sin_t + p * half + j0 + 4);
+    const float cs[8] = {c0.x, c0.y, c0.z, c0.w, c1.x, c1.y, c1.z, c1.w};
+    const float sn[8] = {s0.x, s0.y, s0.z, s0.w, s1.x, s1.y, s1.z, s1.w};
+    const uint32_t aw[4] = {a.x, a.y, a.z, a.w}, bw[4] = {b.x, b.y, b.z, b.w};
+    uint32_t oa[4], ob[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const float2 x1 = unpack_bf16(aw[j]), x2 = unpack_bf16(bw[j]);
+      const float sA = sign * sn[2 * j], sB = sign * sn[2 * j + 1];
+      oa[j] = pack_bf16(x1.x * cs[2 * j] - x2.x * sA, x1.y * cs[2 * j + 1] - x2.y * sB);
+      ob[j] = pack_bf16(x2.x * cs[2 * j] + x1.x * sA, x2.y * cs[2 * j + 1] + x1.y * sB);
+    }
+    *reinterpret_cast<uint4*>(base) = make_uint4(oa[0], oa[1], oa[2], oa[3]);
+    *reinterpret_cast<uint4*>(base + half) = make_uint4(ob[0], ob[1], ob[2], ob[3]);
+  }
+}
+
+// --------------------------------------------------------------------------------------------- column sum
+// out[c] = sum_r x[r][c] for bf16 x [M][ld] (bias gradients).  Stage 1 writes per-block partials to scratch
+// [nblocks][N]; stage 2 (reduce_partials_kernel) sums them in a fixed order.
+constexpr int kColsumRowsPerBlock = 64;
+__global__ void colsum_partial_kernel(const __nv_bfloat16* __restrict__ x, long long ld, float* __restrict__ scratch,
+                                      int M, int N) {
+  // block = (N/8 column groups covered by threadIdx.x .. ) x row strip blockIdx.y
+  const int cg = blockIdx.x * blockDim.x + threadIdx.x;  // group of 8 columns
+  if (cg * 8 >= N) return;
+  const int r0 = blockIdx.y * kColsumRowsPerBlock;
+  const int r1 = min(M, r0 + kColsumRowsPerBlock);
+  float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+  for (int r = r0; r < r1; ++r) {
+    const uint4 v = *reinterpret_cast<const uint4*>(x + static_cast<long long>(r) * ld + cg * 8);
+    const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const float2 f = unpack_bf16(w[j]);
+      acc[2 * j] += f.x;
+      acc[2 * j + 1] += f.y;
+    }
+  }
+  float* o = scratch + static_cast<long long>(blockIdx.y) * N + cg * 8;
+  *reinterpret_cast<float4*>(o) = make_float4(acc[0], acc[1], acc[2], acc[3]);
+  *reinterpret_cast<float4*>(o + 4) = make_float4(acc[4], acc[5], acc[6], acc[7]);
+}
+
+// --------------------------------------------------------------------------------------------- casts
+__global__ void cast_f32_to_bf16_kernel(const float* __restrict__ x, __nv_bfloat16* __restrict__ y, long long n4) {
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < n4;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const float4 v = *reinterpret_cast<const float4*>(x + i * 4);
+    uint2 o;
+    o.x = pack_bf16(v.x, v.y);
+    o.y = pack_bf16(v.z, v.w);
+    *reinterpret_cast<uint2*>(y + i * 4) = o;
+  }
+}
+
+int num_sms();
+
+static inline int ew_grid(long long work_items, int threads) {
+  long long b = (work_items + threads - 1) / threads;
+  const long long cap = static_cast<long long>(num_sms()) * 16;
+  if (b > cap) b = cap;
+  if (b < 1) b = 1;
+  return static_cast<int>(b);
+}
+
+static inline int norm_grid(int M) {
+  int b = (M + 7) / 8;
+  const int cap = num_sms() * 4;
+  return b < cap ? (b < 1 ? 1 : b) : cap;
+}
+
+}  // namespace dpfs
+
+using namespace dpfs;
+
+#define DISPATCH_NV(D, ...)                   \
+  do {                                        \
+    const int nv_ = ((D) + 127) / 128;        \
+    if (nv_ <= 1) {                           \
+      constexpr int NV = 1;                   \
+      __VA_ARGS__;                            \
+    } else if (nv_ <= 2) {                    \
+      constexpr int NV = 2;                   \
+      __VA_ARGS__;                            \
+    } else if (nv_ <= 4) {                    \
+      constexpr int NV = 4;                   \
+      __VA_ARGS__;                            \
+    } else if (nv_ <= 8) {                    \
+      constexpr int NV = 8;                   \
+      __VA_ARGS__;                            \
+    } else {                                  \
+      constexpr int NV = 16;                  \
+      __VA_ARGS__;                            \
+    }                                         \
+  } while (0)
+
+extern "C" int dpfs_norm_bwd_blocks(int M) { return norm_grid(M); }
+
+extern "C" int dpfs_rmsnorm_fwd(const void* x, int x_bf16, const float* scale, void* y, int y_bf16, float* rstd,
+                                int M, int D, float eps, cudaStream_t stream) {
+  if (D % 4 != 0 || D > 128 * kMaxNV) return -20;
+  if (M <= 0) return 0;
+  const int grid = norm_grid(M);
+  DISPATCH_NV(D, {
+    if (x_bf16 && y_bf16)
+      rmsnorm_fwd_kernel<__nv_bfloat16, __nv_bfloat16, NV><<<grid, kNormThreads, 0, stream>>>(
+          (const __nv_bfloat16*)x, scale, (__nv_bfloat16*)y, rstd, M, D, eps);
+    else if (x_bf16 && !y_bf16)
+      rmsnorm_fwd_kernel<__nv_bfloat16, float, NV><<<grid, kNormThreads, 0, stream>>>(
+          (const __nv_bfloat16*)x, scale, (float*)y, rstd, M, D, eps);
+    else if (!x_bf16 && y_bf16)
+      rmsnorm_fwd_kernel<float, __nv_bfloat16, NV><<<grid, kNormThreads, 0, stream>>>(
+          (const float*)x, scale, (__nv_bfloat16*)y, rstd, M, D, eps);
+    else
+      rmsnorm_fwd_kernel<float, float, NV><<<grid, kNormThreads, 0, stream>>>((const float*)x, scale, (float*)y,
+                                                                              rstd, M, D, eps);
+  });
+  return static_cast<int>(cudaGetLastError());
+}
+
+extern "C" int dpfs_rmsnorm_bwd(const void* dy, int dy_bf16, const void* x, int x_bf16, const float* rstd,
+                                const float* scale, const float* dres, float* dx, void* dx_bf16, float* dscale,
+                                int dscale_accumulate, float* scratch, int M, int D, cudaStream_t stream) {
+  if (D % 4 != 0 || D > 128 * kMaxNV) return -20;
+  if (M <= 0) return 0;
+  const int grid = norm_grid(M);
+  DISPATCH_NV(D, {
+    if (dy_bf16 && !x_bf16)
+      rmsnorm_bwd_kernel<float, __nv_bfloat16, NV><<<grid, kNormThreads, 0, stream>>>(
+          (const __nv_bfloat16*)dy, (const float*)x, rstd, scale, dres, dx, (__nv_bfloat16*)dx_bf16, scratch, M, D);
+    else if (dy_bf16 && x_bf16)
+      rmsnorm_bwd_kernel<__nv_bfloat16, __nv_bfloat16, NV><<<grid, kNormThreads, 0, stream>>>(
+          (const __nv_bfloat16*)dy, (const __nv_bfloat16*)x, rstd, scale, dres, dx, (__nv_bfloat16*)dx_bf16, scratch,
+          M, D);
+    else if (!dy_bf16 && !x_bf16)
+      rmsnorm_bwd_kernel<float, float, NV><<<grid, kNormThreads, 0, stream>>>(
+          (const float*)dy, (const float*)x, rstd, scale, dres, dx, (__nv_bfloat16*)dx_bf16, scratch, M, D);
+    else
+      rmsnorm_bwd_kernel<__nv_bfloat16, float, NV><<<grid, kNormThreads, 0, stream>>>(
+          (const float*)dy, (const __nv_bfloat16*)x, rstd, scale, dres, dx, (__nv_bfloat16*)dx_bf16, scratch, M, D);
+  });
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return static_cast<int>(e);
+  reduce_partials_kernel<<<(D + 255) / 256, 256, 0, stream>>>(scratch, dscale, grid, D, dscale_accumulate);
+  return static_cast<int>(cudaGetLastError());
+}
+
+extern "C" int dpfs_layernorm_fwd(const void* x, int x_bf16, const float* gamma, const float* beta, void* y,
+                                  int y_bf16, float* mean, float* rstd, int M, int D, float eps,
+                                  cudaStream_t stream) {
+  if (D % 4 != 0 || D > 128 * kMaxNV) return -20;
+  if (M <= 0) return 0;
+  const int grid = norm_grid(M);
+  DISPATCH_NV(D, {
+    if (x_bf16 && y_bf16)
+      layernorm_fwd_kernel<__nv_bfloat16, __nv_bfloat16, NV><<<grid, kNormThreads, 0, stream>>>(
+          (const __nv_bfloat16*)x, gamma, beta, (__nv_bfloat16*)y, mean, rstd, M, D, eps);
+    else if (!x_bf16 && y_bf16)
+      layernorm_fwd_kernel<float, __nv_bfloat16, NV><<<grid, kNormThreads, 0, stream>>>(
+          (const float*)x, gamma, beta, (__nv_bfloat16*)y, mean, rstd, M, D, eps);
+    else if (!x_bf16 && !y_bf16)
+      layernorm_fwd_kernel<float, float, NV><<<grid, kNormThreads, 0, stream>>>((const float*)x, gamma, beta,
+                                                                                (float*)y, mean, rstd, M, D, eps);
+    else
+      layernorm_fwd_kernel<__nv_bfloat16, float, NV><<<grid, kNormThreads, 0, stream>>>(
+          (const __nv_bfloat16*)x, gamma, beta, (float*)y, mean, rstd, M, D, eps);
+  });
+  return static_cast<int>(cudaGetLastError());
+}
+
+extern "C" int dpfs_layernorm_bwd(const void* dy, int dy_bf16, const void* x, int x_bf16, const float* mean,
+                                  const float* rstd, const float* gamma, float* dx, float* dgamma, float* dbeta,
+                                  float* scratch, int M, int D, cudaStream_t stream) {
+  if (D % 4 != 0 || D > 128 * kMaxNV) return -20;
+  if (M <= 0) return 0;
+  const int grid = norm_grid(M);
+  DISPATCH_NV(D, {
+    if (dy_bf16 && x_bf16)
+      layernorm_bwd_kernel<__nv_bfloat16, __nv_bfloat16, NV><<<grid, kNormThreads, 0, stream>>>(
+          (const __nv_bfloat16*)dy, (const __nv_bfloat16*)x, mean, rstd, gamma, dx, scratch, M, D);
+    else if (dy_bf16 && !x_bf16)
+      layernorm_bwd_kernel<float, __nv_bfloat16, NV><<<grid, kNormThreads, 0, stream>>>(
+          (const __nv_bfloat16*)dy, (const float*)x, mean, rstd, gamma, dx, scratch, M, D);
+    else if (!dy_bf16 && !x_bf16)
+      layernorm_bwd_kernel<float, float, NV><<<grid, kNormThreads, 0, stream>>>((const float*)dy, (const float*)x,
+                                                                                mean, rstd, gamma, dx, scratch, M, D);
+    else
+      layernorm_bwd_kernel<__nv_bfloat16, float, NV><<<grid, kNormThreads, 0, stream>>>(
+          (const float*)dy, (const __nv_bfloat16*)x, mean, rstd, gamma, dx, scratch, M, D);
+  });
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return static_cast<int>(e);
+  // partial rows are [dgamma(D) | dbeta(D)]: reduce as one 2D-wide vector into a strided pair of outputs
+  reduce_partials_kernel<<<(2 * D + 255) / 256, 256, 0, stream>>>(scratch, scratch + (long long)grid * 2 * D, grid,
+                                                                  2 * D, 0);
+  e = cudaGetLastError();
+  if (e != cudaSuccess) return static_cast<int>(e);
+  cudaMemcpyAsync(dgamma, scratch + (long long)grid * 2 * D, D * sizeof(float), cudaMemcpyDeviceToDevice, stream);
+  if (dbeta)
+    cudaMemcpyAsync(dbeta, scratch + (long long)grid * 2 * D + D, D * sizeof(float), cudaMemcpyDeviceToDevice,
+                    stream);
+  return static_cast<int>(cudaGetLastError());
+}
+
+extern "C" int dpfs_swiglu_fwd(const void* gu, void* act, int M, int F, cudaStream_t stream) {
+  if (F % 8 != 0) return -21;
+  if (M <= 0) return 0;
+  const long long total = static_cast<long long>(M) * (F / 8);
+  swiglu_fwd_kernel<<<ew_grid(total, 256), 256, 0, stream>>>((const __nv_bfloat16*)gu, (__nv_bfloat16*)act, M, F);
+  return static_cast<int>(cudaGetLastError());
+}
+
+extern "C" int dpfs_swiglu_bwd(const void* dact, const void* gu, void* dgu, int M, int F, cudaStream_t stream) {
+  if (F % 8 != 0) return -21;
+  if (M <= 0) return 0;
+  const long long total = static_cast<long long>(M) * (F / 8);
+  swiglu_bwd_kernel<<<ew_grid(total, 256), 256, 0, stream>>>((const __nv_bfloat16*)dact, (const __nv_bfloat16*)gu,
+                                                             (__nv_bfloat16*)dgu, M, F);
+  return static_cast<int>(cudaGetLastError());
+}
+
+extern "C" int dpfs_gelu_fwd(const void* x, void* y, long long n, cudaStream_t stream) {
+  if (n % 8 != 0) return -21;
+  if (n <= 0) return 0;
+  gelu_fwd_kernel<<<ew_grid(n / 8, 256), 256, 0, stream>>>((const __nv_bfloat16*)x, (__nv_bfloat16*)y, n / 8);
+  return static_cast<int>(cudaGetLastError());
+}
+
+extern "C" int dpfs_gelu_bwd(const void* dy, const void* x, void* dx, long long n, cudaStream_t stream) {
+  if (n % 8 != 0) return -21;
+  if (n <= 0) return 0;
+  gelu_bwd_kernel<<<ew_grid(n / 8, 256), 256, 0, stream>>>((const __nv_bfloat16*)dy, (const __nv_bfloat16*)x,
+                                                           (__nv_bfloat16*)dx, n / 8);
+  return static_cast<int>(cudaGetLastError());
+}
+
+extern "C" int dpfs_rope_inplace(void* buf, long long ld, const long long* pos, const float* cos_t,
+                                 const float* sin_t, int M, int nseg, int seg_stride, int H, int hd, int inverse,
+                                 cudaStream_t stream) {
+  if (hd % 16 != 0 || ld % 8 != 0 || seg_stride % 8 != 0) return -22;
+  if (M <= 0) return 0;
+  const long long total = static_cast<long long>(M) * nseg * H * (hd / 16);
+  rope_kernel<<<ew_grid(total, 256), 256, 0, stream>>>((__nv_bfloat16*)buf, ld, pos, cos_t, sin_t, M, nseg,
+                                                       seg_stride, H, hd, inverse ? -1.f : 1.f);
+  return static_cast<int>(cudaGetLastError());
+}
+
+extern "C" int dpfs_colsum_scratch_floats(int M, int N) {
+  return ((M + kColsumRowsPerBlock - 1) / kColsumRowsPerBlock) * N;
+}
+
+extern "C" int dpfs_colsum_bf16(const void* x, long long ld, float* out, int accumulate, float* scratch, int M, int N,
+                                cudaStream_t stream) {
+  if (N % 8 != 0 || ld % 8 != 0) return -23;
+  if (M <= 0) return 0;
+  const int strips = (M + kColsumRowsPerBlock - 1) / kColsumRowsPerBlock;
+  dim3 grid((N / 8 + 127) / 128, strips);
+  colsum_partial_kernel<<<grid, 128, 0, stream>>>((const __nv_bfloat16*)x, ld, scratch, M, N);
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return static_cast<int>(e);
+  reduce_partials_kernel<<<(N + 255) / 256, 256, 0, stream>>>(scratch, out, strips, N, accumulate);
+  return static_cast<int>(cudaGetLastError());
+}
+
+extern "C" int dpfs_cast_f32_to_bf16(const float* x, void* y, long long n, cudaStream_t stream) {
+  if (n % 4 != 0) return -24;
+  if (n <= 0) return 0;
+  cast_f32_to_bf16_kernel<<<ew_grid(n / 4, 256), 256, 0, stream>>>(x, (__nv_bfloat16*)y, n / 4);
+  return static_cast<int>(cudaGetLastError());
+}

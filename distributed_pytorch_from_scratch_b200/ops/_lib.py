@@ -21,31 +21,39 @@ c_ll = ctypes.c_longlong
 c_f = ctypes.c_float
 c_p = ctypes.c_void_p
 
+# name -> argtypes (all entry points return int: 0 ok, >0 cudaError_t, <0 argument error)
+SIGS = {
+    "dpfs_gemm_bf16": (c_p, c_ll, c_int, c_p, c_ll, c_int, c_p, c_ll, c_int, c_p, c_p, c_ll, c_int, c_int, c_int,
+                       c_int, c_p, c_int, c_p),
+    "dpfs_norm_bwd_blocks": (c_int,),
+    "dpfs_rmsnorm_fwd": (c_p, c_int, c_p, c_p, c_int, c_p, c_int, c_int, c_f, c_p),
+    "dpfs_rmsnorm_bwd": (c_p, c_int, c_p, c_int, c_p, c_p, c_p, c_p, c_p, c_p, c_int, c_p, c_int, c_int, c_p),
+    "dpfs_layernorm_fwd": (c_p, c_int, c_p, c_p, c_p, c_int, c_p, c_p, c_int, c_int, c_f, c_p),
+    "dpfs_layernorm_bwd": (c_p, c_int, c_p, c_int, c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_int, c_int, c_p),
+    "dpfs_swiglu_fwd": (c_p, c_p, c_int, c_int, c_p),
+    "dpfs_swiglu_bwd": (c_p, c_p, c_p, c_int, c_int, c_p),
+    "dpfs_gelu_fwd": (c_p, c_p, c_ll, c_p),
+    "dpfs_gelu_bwd": (c_p, c_p, c_p, c_ll, c_p),
+    "dpfs_rope_inplace": (c_p, c_ll, c_p, c_p, c_p, c_int, c_int, c_int, c_int, c_int, c_int, c_p),
+    "dpfs_colsum_scratch_floats": (c_int, c_int),
+    "dpfs_colsum_bf16": (c_p, c_ll, c_p, c_int, c_p, c_int, c_int, c_p),
+    "dpfs_cast_f32_to_bf16": (c_p, c_p, c_ll, c_p),
+    "dpfs_embedding_fwd": (c_p, c_p, c_p, c_int, c_int, c_int, c_ll, c_ll, c_p),
+    "dpfs_embedding_bwd": (c_p, c_p, c_p, c_int, c_ll, c_int, c_int, c_ll, c_ll, c_p),
+    "dpfs_ce_stats": (c_p, c_int, c_ll, c_p, c_p, c_p, c_int, c_int, c_ll, c_ll, c_p),
+    "dpfs_ce_finish": (c_p, c_int, c_ll, c_p, c_p, c_int, c_p, c_ll, c_p, c_p, c_int, c_int, c_ll, c_ll, c_f, c_p),
+    "dpfs_adam_step": (c_p, c_p, c_p, c_p, c_p, c_ll, c_p, c_p),
+    "dpfs_attn_fwd": (c_p, c_p, c_p, c_int, c_int, c_int, c_int, c_f, c_p),
+    "dpfs_attn_bwd": (c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_int, c_int, c_int, c_int, c_f, c_p),
+}
 
-def _declare(lib):
-    def sig(name, *argtypes):
-        fn = getattr(lib, name)
-        fn.argtypes = list(argtypes)
-        fn.restype = c_int
-        return fn
 
-    sig("dpfs_gemm_bf16", c_p, c_ll, c_int, c_p, c_ll, c_int, c_p, c_ll, c_int, c_p, c_p, c_ll, c_int, c_int,
-        c_int, c_int, c_p, c_int, c_p)
-    for name, argtypes in _EXTRA_SIGS.items():
-        if hasattr(lib, name):
-            sig(name, *argtypes)
-
-
-# name -> argtypes; filled by the op modules at import time (before first load) or declared lazily.
-_EXTRA_SIGS = {}
-
-
-def register(name, *argtypes):
-    _EXTRA_SIGS[name] = argtypes
-    if _LIB is not None and hasattr(_LIB, name):
-        fn = getattr(_LIB, name)
-        fn.argtypes = list(argtypes)
-        fn.restype = c_int
+def _declare(handle):
+    for name, argtypes in SIGS.items():
+        if hasattr(handle, name):
+            fn = getattr(handle, name)
+            fn.argtypes = list(argtypes)
+            fn.restype = c_int
 
 
 def available() -> bool:
@@ -79,5 +87,5 @@ class KernelError(RuntimeError):
 
 def check(rc: int, what: str):
     if rc != 0:
-        raise KernelError(f"{what} failed with code {rc}"
-                          + (" (negative = library argument error, positive = cudaError_t)" if rc else ""))
+        raise KernelError(f"{what} failed with code {rc} (negative = library argument error, "
+                          f"positive = cudaError_t)")

@@ -1,0 +1,243 @@
+"""Thin Python wrappers over the memory-bound sm_100a kernels (csrc/elementwise.cu, csrc/train_ops.cu).
+
+Every function launches on the current CUDA stream and returns torch tensors; none of them synchronises.
+Scratch buffers are cached per device (they are tiny) so steady-state steps do not allocate.
+"""
+from __future__ import annotations
+
+from typing import Optional, Tuple
+
+import torch
+
+from . import _lib
+
+_SCRATCH = {}
+BF16 = torch.bfloat16
+F32 = torch.float32
+
+
+def _scratch(device, key: str, nfloats: int) -> torch.Tensor:
+    k = (device, key)
+    buf = _SCRATCH.get(k)
+    if buf is None or buf.numel() < nfloats:
+        buf = torch.empty(max(nfloats, 1024), dtype=F32, device=device)
+        _SCRATCH[k] = buf
+    return buf
+
+
+def _is_bf16(t: torch.Tensor) -> int:
+    if t.dtype == BF16:
+        return 1
+    assert t.dtype == F32, f"expected fp32 or bf16, got {t.dtype}"
+    return 0
+
+
+# ------------------------------------------------------------------------------------------------ RMSNorm
+def rmsnorm_fwd(x: torch.Tensor, scale: torch.Tensor, eps: float, out_dtype=BF16, want_rstd: bool = True):
+    """x: [..., D] fp32 or bf16 (contiguous); scale fp32 [D]. Returns (y[out_dtype], rstd fp32 [rows] | None)."""
+    D = x.shape[-1]
+    x2 = x.reshape(-1, D)
+    assert x2.is_contiguous() and scale.dtype == F32
+    M = x2.shape[0]
+    y = torch.empty(x2.shape, dtype=out_dtype, device=x.device)
+    rstd = torch.empty(M, dtype=F32, device=x.device) if want_rstd else None
+    rc = _lib.lib().dpfs_rmsnorm_fwd(x2.data_ptr(), _is_bf16(x2), scale.data_ptr(), y.data_ptr(), _is_bf16(y),
+                                     _lib.ptr(rstd), M, D, eps, _lib.stream())
+    _lib.check(rc, "dpfs_rmsnorm_fwd")
+    return y.view(x.shape), rstd
+
+
+def rmsnorm_bwd(dy: torch.Tensor, x: torch.Tensor, rstd: torch.Tensor, scale: torch.Tensor,
+                dres: Optional[torch.Tensor] = None, want_fp32: bool = True, want_bf16: bool = False,
+                dscale_out: Optional[torch.Tensor] = None, accumulate: bool = False):
+    """Returns (dx fp32 | None, dx bf16 | None, dscale fp32 [D]).  dx = dres + rmsnorm'(dy)."""
+    D = x.shape[-1]
+    x2, dy2 = x.reshape(-1, D), dy.reshape(-1, D)
+    assert x2.is_contiguous() and dy2.is_contiguous()
+    M = x2.shape[0]
+    dx = torch.empty((M, D), dtype=F32, device=x.device) if want_fp32 else None
+    dxb = torch.empty((M, D), dtype=BF16, device=x.device) if want_bf16 else None
+    dscale = dscale_out if dscale_out is not None else torch.empty(D, dtype=F32, device=x.device)
+    lib = _lib.lib()
+    scratch = _scratch(x.device, "norm", lib.dpfs_norm_bwd_blocks(M) * D)
+    if dres is not None:
+        dres = dres.reshape(-1, D)
+        assert dres.dtype == F32 and dres.is_contiguous()
+    rc = lib.dpfs_rmsnorm_bwd(dy2.data_ptr(), _is_bf16(dy2), x2.data_ptr(), _is_bf16(x2), rstd.data_ptr(),
+                              scale.data_ptr(), _lib.ptr(dres), _lib.ptr(dx), _lib.ptr(dxb), dscale.data_ptr(),
+                              int(accumulate), scratch.data_ptr(), M, D, _lib.stream())
+    _lib.check(rc, "dpfs_rmsnorm_bwd")
+    return dx, dxb, dscale
+
+
+# ------------------------------------------------------------------------------------------------ LayerNorm
+def layernorm_fwd(x, gamma, beta, eps: float, out_dtype=BF16):
+    D = x.shape[-1]
+    x2 = x.reshape(-1, D)
+    M = x2.shape[0]
+    y = torch.empty(x2.shape, dtype=out_dtype, device=x.device)
+    mean = torch.empty(M, dtype=F32, device=x.device)
+    rstd = torch.empty(M, dtype=F32, device=x.device)
+    rc = _lib.lib().dpfs_layernorm_fwd(x2.data_ptr(), _is_bf16(x2), gamma.data_ptr(), _lib.ptr(beta), y.data_ptr(),
+                                       _is_bf16(y), mean.data_ptr(), rstd.data_ptr(), M, D, eps, _lib.stream())
+    _lib.check(rc, "dpfs_layernorm_fwd")
+    return y.view(x.shape), mean, rstd
+
+
+def layernorm_bwd(dy, x, mean, rstd, gamma, want_dbeta: bool = True):
+    D = x.shape[-1]
+    x2, dy2 = x.reshape(-1, D), dy.reshape(-1, D).contiguous()
+    M = x2.shape[0]
+    dx = torch.empty((M, D), dtype=F32, device=x.device)
+    dgamma = torch.empty(D, dtype=F32, device=x.device)
+    dbeta = torch.empty(D, dtype=F32, device=x.device) if want_dbeta else None
+    lib = _lib.lib()
+    scratch = _scratch(x.device, "lnorm", (lib.dpfs_norm_bwd_blocks(M) + 1) * 2 * D)
+    rc = lib.dpfs_layernorm_bwd(dy2.data_ptr(), _is_bf16(dy2), x2.data_ptr(), _is_bf16(x2), mean.data_ptr(),
+                                rstd.data_ptr(), gamma.data_ptr(), dx.data_ptr(), dgamma.data_ptr(),
+                                _lib.ptr(dbeta), scratch.data_ptr(), M, D, _lib.stream())
+    _lib.check(rc, "dpfs_layernorm_bwd")
+    return dx.view(x.shape), dgamma, dbeta
+
+
+# ------------------------------------------------------------------------------------------------ activations
+def swiglu_fwd(gu: torch.Tensor) -> torch.Tensor:
+    """gu: bf16 [M, 2F] (gate | up) -> silu(gate) * up, bf16 [M, F]."""
+    M, F2 = gu.shape
+    assert gu.dtype == BF16 and gu.is_contiguous()
+    act = torch.empty((M, F2 // 2), dtype=BF16, device=gu.device)
+    rc = _lib.lib().dpfs_swiglu_fwd(gu.data_ptr(), act.data_ptr(), M, F2 // 2, _lib.stream())
+    _lib.check(rc, "dpfs_swiglu_fwd")
+    return act
+
+
+def swiglu_bwd(dact: torch.Tensor, gu: torch.Tensor) -> torch.Tensor:
+    M, F2 = gu.shape
+    assert dact.dtype == BF16 and dact.is_contiguous() and dact.shape == (M, F2 // 2)
+    dgu = torch.empty_like(gu)
+    rc = _lib.lib().dpfs_swiglu_bwd(dact.data_ptr(), gu.data_ptr(), dgu.data_ptr(), M, F2 // 2, _lib.stream())
+    _lib.check(rc, "dpfs_swiglu_bwd")
+    return dgu
+
+
+def gelu_fwd(x: torch.Tensor) -> torch.Tensor:
+    assert x.dtype == BF16 and x.is_contiguous()
+    y = torch.empty_like(x)
+    _lib.check(_lib.lib().dpfs_gelu_fwd(x.data_ptr(), y.data_ptr(), x.numel(), _lib.stream()), "dpfs_gelu_fwd")
+    return y
+
+
+def gelu_bwd(dy: torch.Tensor, x: torch.Tensor) -> torch.Tensor:
+    assert dy.dtype == BF16 and dy.is_contiguous() and x.is_contiguous()
+    dx = torch.empty_like(x)
+    _lib.check(_lib.lib().dpfs_gelu_bwd(dy.data_ptr(), x.data_ptr(), dx.data_ptr(), x.numel(), _lib.stream()),
+               "dpfs_gelu_bwd")
+    return dx
+
+
+# ------------------------------------------------------------------------------------------------ RoPE
+def rope_inplace(buf: torch.Tensor, pos: torch.Tensor, cos: torch.Tensor, sin: torch.Tensor, nseg: int,
+                 seg_stride: int, H: int, hd: int, inverse: bool = False):
+    """Rotate the first ``nseg`` segments (q, k) of a packed bf16 [M, ld] buffer in place.
+
+    pos: int64 [M]; cos/sin: fp32 [maxlen, hd/2] tables."""
+    assert buf.dtype == BF16 and buf.stride(1) == 1 and pos.dtype == torch.int64 and pos.is_contiguous()
+    assert cos.dtype == F32 and cos.shape[-1] == hd // 2 and cos.is_contiguous() and sin.is_contiguous()
+    rc = _lib.lib().dpfs_rope_inplace(buf.data_ptr(), buf.stride(0), pos.data_ptr(), cos.data_ptr(), sin.data_ptr(),
+                                      buf.shape[0], nseg, seg_stride, H, hd, int(inverse), _lib.stream())
+    _lib.check(rc, "dpfs_rope_inplace")
+    return buf
+
+
+# ------------------------------------------------------------------------------------------------ reductions
+def colsum(x: torch.Tensor, out: Optional[torch.Tensor] = None, accumulate: bool = False) -> torch.Tensor:
+    """Column sums of a bf16 [M, N] matrix in fp32 (bias gradients), deterministic two-stage reduction."""
+    assert x.dtype == BF16 and x.dim() == 2 and x.stride(1) == 1
+    M, N = x.shape
+    if out is None:
+        out = torch.empty(N, dtype=F32, device=x.device)
+    lib = _lib.lib()
+    scratch = _scratch(x.device, "colsum", lib.dpfs_colsum_scratch_floats(M, N))
+    rc = lib.dpfs_colsum_bf16(x.data_ptr(), x.stride(0), out.data_ptr(), int(accumulate), scratch.data_ptr(), M, N,
+                              _lib.stream())
+    _lib.check(rc, "dpfs_colsum_bf16")
+    return out
+
+
+def cast_to_bf16(x: torch.Tensor, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    assert x.dtype == F32 and x.is_contiguous()
+    if out is None:
+        out = torch.empty(x.shape, dtype=BF16, device=x.device)
+    if x.numel() % 4 != 0:
+        out.copy_(x)
+        return out
+    _lib.check(_lib.lib().dpfs_cast_f32_to_bf16(x.data_ptr(), out.data_ptr(), x.numel(), _lib.stream()),
+               "dpfs_cast_f32_to_bf16")
+    return out
+
+
+# ------------------------------------------------------------------------------------------------ embedding
+def embedding_fwd(ids: torch.Tensor, weight: torch.Tensor, vocab_start: int, vocab_end: int, out_dtype=F32):
+    assert ids.dtype == torch.int64 and weight.dtype == F32 and weight.is_contiguous()
+    ids_flat = ids.reshape(-1).contiguous()
+    M, D = ids_flat.numel(), weight.shape[1]
+    out = torch.empty((M, D), dtype=out_dtype, device=weight.device)
+    rc = _lib.lib().dpfs_embedding_fwd(ids_flat.data_ptr(), weight.data_ptr(), out.data_ptr(), _is_bf16(out), M, D,
+                                       vocab_start, vocab_end, _lib.stream())
+    _lib.check(rc, "dpfs_embedding_fwd")
+    return out
+
+
+def embedding_bwd(ids: torch.Tensor, dout: torch.Tensor, local_vocab: int, vocab_start: int, vocab_end: int,
+                  dweight: Optional[torch.Tensor] = None, zero_first: bool = True):
+    ids_flat = ids.reshape(-1).contiguous()
+    D = dout.shape[-1]
+    dout2 = dout.reshape(-1, D)
+    assert dout2.dtype == F32 and dout2.is_contiguous()
+    if dweight is None:
+        dweight = torch.empty((local_vocab, D), dtype=F32, device=dout.device)
+    rc = _lib.lib().dpfs_embedding_bwd(ids_flat.data_ptr(), dout2.data_ptr(), dweight.data_ptr(), int(zero_first),
+                                       local_vocab, ids_flat.numel(), D, vocab_start, vocab_end, _lib.stream())
+    _lib.check(rc, "dpfs_embedding_bwd")
+    return dweight
+
+
+# ------------------------------------------------------------------------------------------------ cross-entropy
+def ce_stats(logits: torch.Tensor, targets: torch.Tensor, vocab_start: int, ignore_index: int):
+    """Phase 1: per-row (max, sum-exp, target-logit) over the local vocab shard; also counts valid targets."""
+    M, Vl = logits.shape
+    assert logits.stride(1) == 1 and targets.dtype == torch.int64 and targets.is_contiguous()
+    stats = torch.empty((M, 3), dtype=F32, device=logits.device)
+    loss_acc = torch.empty(2, dtype=F32, device=logits.device)  # {sum of row losses, number of valid rows}
+    rc = _lib.lib().dpfs_ce_stats(logits.data_ptr(), _is_bf16(logits), logits.stride(0), targets.data_ptr(),
+                                  stats.data_ptr(), loss_acc.data_ptr(), M, Vl, vocab_start, ignore_index,
+                                  _lib.stream())
+    _lib.check(rc, "dpfs_ce_stats")
+    return stats, loss_acc
+
+
+def ce_finish(logits: torch.Tensor, targets: torch.Tensor, all_stats: torch.Tensor, nranks: int,
+              loss_acc: torch.Tensor, vocab_start: int, ignore_index: int, want_grad: bool = True,
+              grad_scale: float = 1.0, want_row_loss: bool = False):
+    """Phase 2: combine the per-rank stats -> mean loss (loss_acc[0]/loss_acc[1]) and bf16 dlogits."""
+    M, Vl = logits.shape
+    dlogits = torch.empty((M, Vl), dtype=BF16, device=logits.device) if want_grad else None
+    row_loss = torch.empty(M, dtype=F32, device=logits.device) if want_row_loss else None
+    rc = _lib.lib().dpfs_ce_finish(logits.data_ptr(), _is_bf16(logits), logits.stride(0), targets.data_ptr(),
+                                   all_stats.data_ptr(), nranks, _lib.ptr(dlogits), Vl, loss_acc.data_ptr(),
+                                   _lib.ptr(row_loss), M, Vl, vocab_start, ignore_index, grad_scale, _lib.stream())
+    _lib.check(rc, "dpfs_ce_finish")
+    return dlogits, row_loss
+
+
+# ------------------------------------------------------------------------------------------------ optimizer
+def adam_step(p: torch.Tensor, g: torch.Tensor, m: torch.Tensor, v: torch.Tensor, shadow: Optional[torch.Tensor],
+              hyper: torch.Tensor):
+    """One fused Adam/AdamW step over flat fp32 arenas; ``hyper`` is a device tensor
+    [lr, beta1, beta2, eps, bias_correction1, bias_correction2, weight_decay]."""
+    n = p.numel()
+    assert p.dtype == F32 and g.dtype == F32 and m.dtype == F32 and v.dtype == F32 and hyper.dtype == F32
+    assert g.numel() == n and m.numel() == n and v.numel() == n and n % 4 == 0
+    rc = _lib.lib().dpfs_adam_step(p.data_ptr(), g.data_ptr(), m.data_ptr(), v.data_ptr(), _lib.ptr(shadow), n,
+                                   hyper.data_ptr(), _lib.stream())
+    _lib.check(rc, "dpfs_adam_step")

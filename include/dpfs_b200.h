@@ -31,6 +31,88 @@ int dpfs_gemm_bf16(const void* A, long long lda, int a_mn_major, const void* B, 
                    long long ldr, int M, int N, int K, int splits, float* workspace, int bn,
                    cudaStream_t stream);
 
+/* ---- Fused causal flash attention (tcgen05 / TMEM / TMA) ---------------------------------------------------
+ * qkv: bf16 [B*T][3*H*HD] packed q|k|v (RoPE already applied); out: bf16 [B*T][H*HD]; lse: fp32 [B][H][T].
+ * HD must be 64 or 128.  ref: Attention.forward, models/model.py:68-78 (matmul + triu mask + softmax + matmul). */
+int dpfs_attn_fwd(const void* qkv, void* out, float* lse, int B, int T, int H, int HD, float scale,
+                  cudaStream_t stream);
+/* Backward: writes dqkv bf16 [B*T][3*H*HD].  Scratch supplied by the caller: delta fp32 [B][H][T] and
+ * dq_acc fp32 [B*T][H*HD] (zeroed here, accumulated with red.global.add.v4.f32 across kv tiles). */
+int dpfs_attn_bwd(const void* qkv, const void* out, const void* d_out, const float* lse, float* delta,
+                  float* dq_acc, void* dqkv, int B, int T, int H, int HD, float scale, cudaStream_t stream);
+
+/* ---- Normalisation ------------------------------------------------------------------------------------------
+ * One warp per row, fp32 statistics, D % 4 == 0 and D <= 2048.  *_bf16 flags select the element type (0 = fp32).
+ * ref: RMSNorm, models/layers.py:145-155.  (LayerNorm has no counterpart in the reference model; it is provided
+ * because the project brief names it.) */
+int dpfs_norm_bwd_blocks(int M); /* number of CTAs the backward kernels launch == rows of scratch they need */
+int dpfs_rmsnorm_fwd(const void* x, int x_bf16, const float* scale, void* y, int y_bf16, float* rstd /*nullable*/,
+                     int M, int D, float eps, cudaStream_t stream);
+/* dx = dres + d(rmsnorm)(dy); writes dx (fp32, nullable) and/or dx_bf16 (nullable); dscale[D] (+= if accumulate).
+ * scratch: dpfs_norm_bwd_blocks(M) * D floats. */
+int dpfs_rmsnorm_bwd(const void* dy, int dy_bf16, const void* x, int x_bf16, const float* rstd, const float* scale,
+                     const float* dres /*nullable*/, float* dx, void* dx_bf16, float* dscale, int dscale_accumulate,
+                     float* scratch, int M, int D, cudaStream_t stream);
+int dpfs_layernorm_fwd(const void* x, int x_bf16, const float* gamma, const float* beta /*nullable*/, void* y,
+                       int y_bf16, float* mean, float* rstd, int M, int D, float eps, cudaStream_t stream);
+/* scratch: (dpfs_norm_bwd_blocks(M) + 1) * 2 * D floats. */
+int dpfs_layernorm_bwd(const void* dy, int dy_bf16, const void* x, int x_bf16, const float* mean, const float* rstd,
+                       const float* gamma, float* dx, float* dgamma, float* dbeta /*nullable*/, float* scratch,
+                       int M, int D, cudaStream_t stream);
+
+/* ---- Activations ----------------------------------------------------------------------------------------------
+ * gu: bf16 [M][2F] = gate | up;  act = silu(gate) * up.  ref: FFN.forward, models/model.py:95. */
+int dpfs_swiglu_fwd(const void* gu, void* act, int M, int F, cudaStream_t stream);
+int dpfs_swiglu_bwd(const void* dact, const void* gu, void* dgu, int M, int F, cudaStream_t stream);
+/* tanh-GELU on bf16, n % 8 == 0 (no counterpart in the reference model; named by the project brief). */
+int dpfs_gelu_fwd(const void* x, void* y, long long n, cudaStream_t stream);
+int dpfs_gelu_bwd(const void* dy, const void* x, void* dx, long long n, cudaStream_t stream);
+
+/* ---- RoPE -----------------------------------------------------------------------------------------------------
+ * In-place rotate_half RoPE on the first `nseg` segments of a packed bf16 [M][ld] buffer; each segment has H heads
+ * of hd; cos/sin: fp32 [maxlen][hd/2]; pos: int64 [M]; inverse != 0 applies the transpose rotation (backward).
+ * ref: rotate_half / apply_rotary_pos_emb / get_cos_sin, models/model.py:17-46. */
+int dpfs_rope_inplace(void* buf, long long ld, const long long* pos, const float* cos_t, const float* sin_t, int M,
+                      int nseg, int seg_stride, int H, int hd, int inverse, cudaStream_t stream);
+
+/* ---- Column sum (bias gradients) ------------------------------------------------------------------------------
+ * out[N] (+)= sum over rows of bf16 x[M][ld].  Two stages through `scratch` (dpfs_colsum_scratch_floats(M, N)
+ * floats), summed in a fixed order.  ref: the bias-grad reductions autograd runs for models/layers.py:54,96. */
+int dpfs_colsum_scratch_floats(int M, int N);
+int dpfs_colsum_bf16(const void* x, long long ld, float* out, int accumulate, float* scratch, int M, int N,
+                     cudaStream_t stream);
+int dpfs_cast_f32_to_bf16(const float* x, void* y, long long n, cudaStream_t stream);
+
+/* ---- Vocab-parallel embedding -----------------------------------------------------------------------------------
+ * out[m] = weight[ids[m] - vocab_start] for owned ids, 0 otherwise (ids are never modified).
+ * ref: ParallelVocabularyEmbedding.forward, models/layers.py:134-141. */
+int dpfs_embedding_fwd(const long long* ids, const float* weight, void* out, int out_bf16, int M, int D,
+                       long long vocab_start, long long vocab_end, cudaStream_t stream);
+int dpfs_embedding_bwd(const long long* ids, const float* dout, float* dweight, int zero_first,
+                       long long local_vocab, int M, int D, long long vocab_start, long long vocab_end,
+                       cudaStream_t stream);
+
+/* ---- Vocab-parallel softmax cross-entropy ------------------------------------------------------------------------
+ * Phase 1: stats[m] = {max, sum exp(x - max), target logit if owned} over the local shard [M][Vl]; loss_acc[2] is
+ * reset and loss_acc[1] receives the number of non-ignored targets.  Phase 2 (after the ranks exchanged their
+ * stats into all_stats [nranks][M][3]): loss_acc[0] += sum of row losses; dlogits (bf16 [M][ldd], nullable) =
+ * (softmax - onehot) * grad_scale / n_valid; row_loss (nullable) per-row loss.
+ * ref: F.cross_entropy on gathered logits, train.py:101-104 + Gather in models/layers.py:99. */
+int dpfs_ce_stats(const void* logits, int logits_bf16, long long ld, const long long* targets, float* stats,
+                  float* loss_acc, int M, int Vl, long long vocab_start, long long ignore_index,
+                  cudaStream_t stream);
+int dpfs_ce_finish(const void* logits, int logits_bf16, long long ld, const long long* targets,
+                   const float* all_stats, int nranks, void* dlogits, long long ldd, float* loss_acc,
+                   float* row_loss, int M, int Vl, long long vocab_start, long long ignore_index, float grad_scale,
+                   cudaStream_t stream);
+
+/* ---- Fused Adam / AdamW over a flat arena ------------------------------------------------------------------------
+ * hyper (device): {lr, beta1, beta2, eps, bias_correction1, bias_correction2, decoupled weight decay}.
+ * Also refreshes the bf16 shadow of the parameters (nullable).  n % 4 == 0.
+ * ref: optim.Adam + OneCycleLR (which cycles lr and beta1 every step), train.py:83-84,106-109. */
+int dpfs_adam_step(float* p, const float* g, float* m, float* v, void* shadow_bf16, long long n, const float* hyper,
+                   cudaStream_t stream);
+
 #ifdef __cplusplus
 }
 #endif
