@@ -122,22 +122,15 @@ __global__ void ce_count_kernel(const long long* __restrict__ targets, int M, lo
   }
 }
 
-template <typename LT>
-__global__ void __launch_bounds__(kCeThreads) ce_finish_kernel(const LT* __restrict__ logits, long long ld,
-                                                               const long long* __restrict__ targets,
-                                                               const float* __restrict__ all_stats, int nranks,
-                                                               __nv_bfloat16* __restrict__ dlogits, long long ldd,
-                                                               float* __restrict__ loss_acc,
-                                                               float* __restrict__ row_loss, int M, int Vl,
-                                                               long long vocab_start, long long ignore_index,
-                                                               float grad_scale) {
-  __shared__ float sh[2];
-  const float n_valid = loss_acc[1];
-  const float inv_n = n_valid > 0.f ? 1.f / n_valid : 0.f;
-  float block_loss = 0.f;
-  for (int row = blockIdx.x; row < M; row += gridDim.x) {
-    const long long t = targets[row];
-    if (threadIdx.x == 0) {
+// combine the per-rank stats of every row: loss_acc[0] += sum of row losses (valid rows); optional per-row loss
+__global__ void ce_loss_kernel(const long long* __restrict__ targets, const float* __restrict__ all_stats, int nranks,
+                               float* __restrict__ loss_acc, float* __restrict__ row_loss, int M,
+                               long long ignore_index) {
+  __shared__ float sred[8];
+  float acc = 0.f;
+  for (int row = blockIdx.x * blockDim.x + threadIdx.x; row < M; row += gridDim.x * blockDim.x) {
+    float l = 0.f;
+    if (targets[row] != ignore_index) {
       float gmax = -INFINITY;
       for (int r = 0; r < nranks; ++r) gmax = fmaxf(gmax, all_stats[(static_cast<long long>(r) * M + row) * 3]);
       float gsum = 0.f, gt = 0.f;
@@ -146,34 +139,61 @@ __global__ void __launch_bounds__(kCeThreads) ce_finish_kernel(const LT* __restr
         gsum += st[1] * __expf(st[0] - gmax);
         gt += st[2];
       }
+      l = logf(gsum) + gmax - gt;
+    }
+    if (row_loss) row_loss[row] = l;
+    acc += l;
+  }
+  acc = warp_sum(acc);
+  if ((threadIdx.x & 31) == 0) sred[threadIdx.x >> 5] = acc;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    float t = 0.f;
+    for (int w = 0; w < blockDim.x / 32; ++w) t += sred[w];
+    if (t != 0.f) atomicAdd(loss_acc, t);
+  }
+}
+
+// dlogits[m][j] = (softmax_j - [j == target]) * upstream / n_valid  (bf16), zero rows for ignored targets
+template <typename LT>
+__global__ void __launch_bounds__(kCeThreads) ce_grad_kernel(const LT* __restrict__ logits, long long ld,
+                                                             const long long* __restrict__ targets,
+                                                             const float* __restrict__ all_stats, int nranks,
+                                                             __nv_bfloat16* __restrict__ dlogits, long long ldd,
+                                                             const float* __restrict__ loss_acc,
+                                                             const float* __restrict__ upstream, int M, int Vl,
+                                                             long long vocab_start, long long ignore_index) {
+  __shared__ float sh[2];
+  const float n_valid = loss_acc[1];
+  const float g = (n_valid > 0.f ? 1.f / n_valid : 0.f) * (upstream ? upstream[0] : 1.f);
+  for (int row = blockIdx.x; row < M; row += gridDim.x) {
+    const long long t = targets[row];
+    if (threadIdx.x == 0) {
+      float gmax = -INFINITY;
+      for (int r = 0; r < nranks; ++r) gmax = fmaxf(gmax, all_stats[(static_cast<long long>(r) * M + row) * 3]);
+      float gsum = 0.f;
+      for (int r = 0; r < nranks; ++r) {
+        const float* st = all_stats + (static_cast<long long>(r) * M + row) * 3;
+        gsum += st[1] * __expf(st[0] - gmax);
+      }
       sh[0] = gmax;
       sh[1] = gsum;
-      if (t != ignore_index) {
-        const float l = logf(gsum) + gmax - gt;
-        block_loss += l;
-        if (row_loss) row_loss[row] = l;
-      } else if (row_loss) {
-        row_loss[row] = 0.f;
-      }
     }
     __syncthreads();
-    if (dlogits) {
-      const float gmax = sh[0];
-      const float inv_sum = 1.f / sh[1];
-      const LT* x = logits + static_cast<long long>(row) * ld;
-      __nv_bfloat16* d = dlogits + static_cast<long long>(row) * ldd;
-      const bool valid = t != ignore_index;
-      const long long tl = t - vocab_start;
-      const float sc = valid ? inv_n * grad_scale : 0.f;
-      for (int j = threadIdx.x; j < Vl; j += kCeThreads) {
-        float p = __expf(static_cast<float>(x[j]) - gmax) * inv_sum;
-        if (j == tl) p -= 1.f;
-        d[j] = __float2bfloat16(p * sc);
-      }
+    const float gmax = sh[0];
+    const float inv_sum = 1.f / sh[1];
+    const LT* x = logits + static_cast<long long>(row) * ld;
+    __nv_bfloat16* d = dlogits + static_cast<long long>(row) * ldd;
+    const bool valid = t != ignore_index;
+    const long long tl = t - vocab_start;
+    const float sc = valid ? g : 0.f;
+    for (int j = threadIdx.x; j < Vl; j += kCeThreads) {
+      float p = __expf(static_cast<float>(x[j]) - gmax) * inv_sum;
+      if (j == tl) p -= 1.f;
+      d[j] = __float2bfloat16(p * sc);
     }
     __syncthreads();
   }
-  if (threadIdx.x == 0 && block_loss != 0.f) atomicAdd(loss_acc, block_loss);
 }
 
 // --------------------------------------------------------------------------------------------- Adam / AdamW
@@ -272,20 +292,29 @@ extern "C" int dpfs_ce_stats(const void* logits, int logits_bf16, long long ld, 
   return static_cast<int>(cudaGetLastError());
 }
 
-extern "C" int dpfs_ce_finish(const void* logits, int logits_bf16, long long ld, const long long* targets,
-                              const float* all_stats, int nranks, void* dlogits, long long ldd, float* loss_acc,
-                              float* row_loss, int M, int Vl, long long vocab_start, long long ignore_index,
-                              float grad_scale, cudaStream_t stream) {
+extern "C" int dpfs_ce_loss(const long long* targets, const float* all_stats, int nranks, float* loss_acc,
+                            float* row_loss, int M, long long ignore_index, cudaStream_t stream) {
+  if (M <= 0) return 0;
+  int grid = (M + 255) / 256;
+  if (grid > num_sms() * 4) grid = num_sms() * 4;
+  ce_loss_kernel<<<grid, 256, 0, stream>>>(targets, all_stats, nranks, loss_acc, row_loss, M, ignore_index);
+  return static_cast<int>(cudaGetLastError());
+}
+
+extern "C" int dpfs_ce_grad(const void* logits, int logits_bf16, long long ld, const long long* targets,
+                            const float* all_stats, int nranks, void* dlogits, long long ldd, const float* loss_acc,
+                            const float* upstream, int M, int Vl, long long vocab_start, long long ignore_index,
+                            cudaStream_t stream) {
   if (M <= 0) return 0;
   const int grid = M < num_sms() * 8 ? M : num_sms() * 8;
   if (logits_bf16)
-    ce_finish_kernel<__nv_bfloat16><<<grid, kCeThreads, 0, stream>>>(
+    ce_grad_kernel<__nv_bfloat16><<<grid, kCeThreads, 0, stream>>>(
         (const __nv_bfloat16*)logits, ld, targets, all_stats, nranks, (__nv_bfloat16*)dlogits, ldd, loss_acc,
-        row_loss, M, Vl, vocab_start, ignore_index, grad_scale);
+        upstream, M, Vl, vocab_start, ignore_index);
   else
-    ce_finish_kernel<float><<<grid, kCeThreads, 0, stream>>>((const float*)logits, ld, targets, all_stats, nranks,
-                                                             (__nv_bfloat16*)dlogits, ldd, loss_acc, row_loss, M, Vl,
-                                                             vocab_start, ignore_index, grad_scale);
+    ce_grad_kernel<float><<<grid, kCeThreads, 0, stream>>>((const float*)logits, ld, targets, all_stats, nranks,
+                                                           (__nv_bfloat16*)dlogits, ldd, loss_acc, upstream, M, Vl,
+                                                           vocab_start, ignore_index);
   return static_cast<int>(cudaGetLastError());
 }
 

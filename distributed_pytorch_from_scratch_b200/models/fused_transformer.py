@@ -1,0 +1,355 @@
+"""Hand-scheduled forward / backward of the tensor-parallel Transformer on the sm_100a kernel library.
+
+Memory layout (per rank): all parameters live in ONE flat fp32 arena, their gradients in a second arena with the
+same offsets, and a bf16 "shadow" arena (what the tcgen05 GEMMs read) in a third.  The arena order places
+``wq|wk|wv`` and ``gate|up`` of a layer back to back, so a layer's QKV projection and its gate/up projection are
+each ONE GEMM over a contiguous ``[3*Dl, d]`` / ``[2*Fl, d]`` weight — while ``state_dict()`` still exposes the
+separate reference keys (the nn.Parameters are views into the arena; checkpoint format unchanged).
+The fused Adam kernel updates the fp32 arena and rewrites the bf16 shadow in the same pass.
+
+One decoder layer forward (M = b*t rows, per rank; ref models/model.py:116-121 and SURVEY §3.2):
+    h1   = rmsnorm(x)                               fused norm kernel, bf16 out, saves rstd
+    qkv  = h1 @ [Wq;Wk;Wv]^T + b                    tcgen05 GEMM, bias in the epilogue
+    qkv  = rope(qkv)                                in place on the q,k segments
+    a    = flash_attn(qkv)                          tcgen05 flash attention, heads split by TMA maps
+    x2   = x + allreduce(a @ Wo^T) + bo             GEMM (+ residual/bias epilogue at TP=1) / fused GEMM+AR
+    h2   = rmsnorm(x2)
+    gu   = h2 @ [Wg;Wu]^T + b ; act = silu(g) * u
+    x3   = x2 + allreduce(act @ Wd^T) + bd
+Backward mirrors it with dgrad (MN-major weight operand, no transposes), wgrad (split-K over tokens, fp32 straight
+into the grad arena), ONE all-reduce per column-parallel group (q/k/v share one, gate/up share one: the reference
+does five per layer, defect D7).
+"""
+from __future__ import annotations
+
+import math
+from typing import List, Optional
+
+import torch
+
+from ..ops import fused
+from ..ops.attention import attn_bwd, attn_fwd
+from ..ops.gemm import gemm_nt
+from ..parallel import comm_ops
+from ..parallel import process_manager as pm
+
+BF16, F32 = torch.bfloat16, torch.float32
+_ALIGN = 64  # elements; keeps every group 256 B (fp32) / 128 B (bf16) aligned for TMA and vector access
+
+
+def fused_supported(model) -> bool:
+    n = pm.pgm.tp_size
+    hd = model.head_dim
+    d, f, V = model.attn_dim, model.ffn_dim, model.vocab_size
+    if hd not in (64, 128):
+        return False
+    if d % 8 or d > 2048 and d % 4:
+        return False
+    if d > 2048:   # fused norm kernels keep a row in registers (D <= 2048)
+        return False
+    if (d // n) % 8 or (f // n) % 8 or V % n or (V // n) % 8:
+        return False
+    return True
+
+
+# ================================================================================================ parameter arena
+class ParamArena:
+    """Re-homes every parameter of a Transformer into flat fp32 / grad / bf16-shadow arenas (views keep the API)."""
+
+    def __init__(self, model):
+        groups = []
+        for layer in model.layers:
+            a, f = layer.attn, layer.ffn
+            groups += [[a.wq.weight, a.wk.weight, a.wv.weight], [a.wq.bias, a.wk.bias, a.wv.bias],
+                       [a.wo.weight], [a.wo.bias], [f.gate_proj.weight, f.up_proj.weight],
+                       [f.gate_proj.bias, f.up_proj.bias], [f.down_proj.weight], [f.down_proj.bias],
+                       [layer.norm1.scale], [layer.norm2.scale]]
+        groups += [[model.embedding.weight], [model.norm.scale], [model.lm_head.weight], [model.lm_head.bias]]
+        seen = set()
+        for g in groups:
+            for p in g:
+                assert p is not None and p.dtype == F32, "the fused path keeps fp32 master parameters"
+                seen.add(id(p))
+        assert len(seen) == sum(1 for _ in model.parameters()), "unexpected parameter set for the fused path"
+        self.device = groups[0][0].device
+        offs, total = [], 0
+        for g in groups:
+            total = (total + _ALIGN - 1) // _ALIGN * _ALIGN
+            for p in g:
+                offs.append(total)
+                total += p.numel()
+        total = (total + _ALIGN - 1) // _ALIGN * _ALIGN
+        self.numel = total
+        self.params = torch.zeros(total, dtype=F32, device=self.device)
+        self.grads = torch.zeros(total, dtype=F32, device=self.device)
+        self.shadow = torch.zeros(total, dtype=BF16, device=self.device)
+        self.entries = []  # (param, offset)
+        flat = [p for g in groups for p in g]
+        with torch.no_grad():
+            for p, off in zip(flat, offs):
+                n = p.numel()
+                view = self.params[off:off + n].view(p.shape)
+                view.copy_(p.data)
+                p.data = view
+                p.grad = self.grads[off:off + n].view(p.shape)
+                p._dpfs_shadow_view = self.shadow[off:off + n].view(p.shape)
+                p._dpfs_arena_off = off
+                self.entries.append((p, off))
+        self._sig = None
+        self.sync_shadow(force=True)
+
+    def view(self, which: torch.Tensor, first, *shape):
+        off = first._dpfs_arena_off
+        n = 1
+        for s in shape:
+            n *= s
+        return which[off:off + n].view(*shape)
+
+    def valid(self) -> bool:
+        base = self.params.data_ptr()
+        for p, off in (self.entries[0], self.entries[-1]):
+            if p.data_ptr() != base + off * 4 or p.dtype != F32:
+                return False
+        return True
+
+    def _signature(self):
+        return sum(p._version for p, _ in self.entries)
+
+    def sync_shadow(self, force: bool = False):
+        """Re-cast fp32 -> bf16 if anything other than the fused optimizer touched the parameters."""
+        sig = self._signature()
+        if force or sig != self._sig:
+            fused.cast_to_bf16(self.params, out=self.shadow)
+            self._sig = sig
+
+    def reattach_grads(self):
+        for p, off in self.entries:
+            if p.grad is None or p.grad.data_ptr() != self.grads.data_ptr() + off * 4:
+                p.grad = self.grads[off:off + p.numel()].view(p.shape)
+
+
+class LayerPack:
+    """Fused views of one decoder layer's parameters / grads (no copies)."""
+
+    def __init__(self, arena: ParamArena, layer, d: int, Dl: int, Fl: int):
+        a, f = layer.attn, layer.ffn
+        P, G, S = arena.params, arena.grads, arena.shadow
+        v = arena.view
+        self.wqkv, self.g_wqkv = v(S, a.wq.weight, 3 * Dl, d), v(G, a.wq.weight, 3 * Dl, d)
+        self.bqkv, self.g_bqkv = v(P, a.wq.bias, 3 * Dl), v(G, a.wq.bias, 3 * Dl)
+        self.wo, self.g_wo = v(S, a.wo.weight, d, Dl), v(G, a.wo.weight, d, Dl)
+        self.bo, self.g_bo = v(P, a.wo.bias, d), v(G, a.wo.bias, d)
+        self.wgu, self.g_wgu = v(S, f.gate_proj.weight, 2 * Fl, d), v(G, f.gate_proj.weight, 2 * Fl, d)
+        self.bgu, self.g_bgu = v(P, f.gate_proj.bias, 2 * Fl), v(G, f.gate_proj.bias, 2 * Fl)
+        self.wd, self.g_wd = v(S, f.down_proj.weight, d, Fl), v(G, f.down_proj.weight, d, Fl)
+        self.bd, self.g_bd = v(P, f.down_proj.bias, d), v(G, f.down_proj.bias, d)
+        self.s1, self.g_s1 = v(P, layer.norm1.scale, d), v(G, layer.norm1.scale, d)
+        self.s2, self.g_s2 = v(P, layer.norm2.scale, d), v(G, layer.norm2.scale, d)
+        self.params = [a.wq.weight, a.wk.weight, a.wv.weight, a.wq.bias, a.wk.bias, a.wv.bias, a.wo.weight,
+                       a.wo.bias, f.gate_proj.weight, f.up_proj.weight, f.gate_proj.bias, f.up_proj.bias,
+                       f.down_proj.weight, f.down_proj.bias, layer.norm1.scale, layer.norm2.scale]
+
+
+class Meta:
+    """Static shape info of one forward call."""
+
+    def __init__(self, B, T, d, Hl, hd, Fl, n):
+        self.B, self.T, self.M = B, T, B * T
+        self.d, self.Hl, self.hd, self.Dl, self.Fl, self.n = d, Hl, hd, Hl * hd, Fl, n
+        self.scale = 1.0 / math.sqrt(hd)
+
+
+# ================================================================================================ building blocks
+def _rowpar_residual(a_bf16, w_bf16, bias, residual):
+    """x_out = residual + all_reduce(a @ W^T) + bias  (row-parallel linear folded into the residual stream)."""
+    n = pm.pgm.tp_size
+    if n == 1:
+        return gemm_nt(a_bf16, w_bf16, bias=bias, residual=residual, out_dtype=F32)
+    symm = pm.pgm.symm
+    if symm is not None and symm.can_fuse_gemm_ar(a_bf16, w_bf16):
+        return symm.gemm_allreduce_residual(a_bf16, w_bf16, bias, residual)
+    part = gemm_nt(a_bf16, w_bf16, out_dtype=BF16)
+    comm_ops.all_reduce_sum_(part)
+    return fused_residual_bias(part, bias, residual)
+
+
+def fused_residual_bias(part_bf16, bias, residual):
+    # TODO(perf): single kernel; torch ops are only used on the NCCL fallback path
+    return residual + part_bf16.float() + bias
+
+
+def _colpar_dgrad(dy_bf16, w_bf16):
+    """dx = all_reduce(dy @ W)  (column-parallel backward, one collective for the whole fused group)."""
+    n = pm.pgm.tp_size
+    if n == 1:
+        return gemm_nt(dy_bf16, w_bf16, b_mn_major=True, out_dtype=BF16)
+    symm = pm.pgm.symm
+    if symm is not None and symm.can_fuse_gemm_ar(dy_bf16, w_bf16, b_mn_major=True):
+        return symm.gemm_allreduce(dy_bf16, w_bf16, b_mn_major=True)
+    dx = gemm_nt(dy_bf16, w_bf16, b_mn_major=True, out_dtype=BF16)
+    comm_ops.all_reduce_sum_(dx)
+    return dx
+
+
+def _wgrad(dy_bf16, x_bf16, out):
+    gemm_nt(dy_bf16, x_bf16, a_mn_major=True, b_mn_major=True, out=out)
+
+
+class FusedLayerFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, pos, rt, pack: LayerPack, meta: Meta, *params):
+        m = meta
+        h1, rstd1 = fused.rmsnorm_fwd(x, pack.s1, rt.eps)
+        qkv = gemm_nt(h1, pack.wqkv, bias=pack.bqkv, out_dtype=BF16)
+        fused.rope_inplace(qkv, pos, rt.cos_half, rt.sin_half, 2, m.Dl, m.Hl, m.hd, inverse=False)
+        attn, lse = attn_fwd(qkv, m.B, m.T, m.Hl, m.hd, m.scale)
+        x2 = _rowpar_residual(attn, pack.wo, pack.bo, x)
+        h2, rstd2 = fused.rmsnorm_fwd(x2, pack.s2, rt.eps)
+        gu = gemm_nt(h2, pack.wgu, bias=pack.bgu, out_dtype=BF16)
+        act = fused.swiglu_fwd(gu)
+        x3 = _rowpar_residual(act, pack.wd, pack.bd, x2)
+        ctx.save_for_backward(x, pos, h1, rstd1, qkv, attn, lse, x2, h2, rstd2, gu, act)
+        ctx.pack, ctx.meta, ctx.rt = pack, meta, rt
+        return x3
+
+    @staticmethod
+    def backward(ctx, dx3):
+        x, pos, h1, rstd1, qkv, attn, lse, x2, h2, rstd2, gu, act = ctx.saved_tensors
+        pack, m, rt = ctx.pack, ctx.meta, ctx.rt
+        dx3 = dx3.contiguous()
+        dx3_b = fused.cast_to_bf16(dx3)
+        # ---- FFN
+        dact = gemm_nt(dx3_b, pack.wd, b_mn_major=True, out_dtype=BF16)            # [M, Fl]
+        _wgrad(dx3_b, act, pack.g_wd)
+        fused.colsum(dx3_b, out=pack.g_bd)
+        dgu = fused.swiglu_bwd(dact, gu)
+        del dact
+        dh2 = _colpar_dgrad(dgu, pack.wgu)                                            # [M, d]
+        _wgrad(dgu, h2, pack.g_wgu)
+        fused.colsum(dgu, out=pack.g_bgu)
+        del dgu
+        dx2, dx2_b, _ = fused.rmsnorm_bwd(dh2, x2, rstd2, pack.s2, dres=dx3, want_fp32=True, want_bf16=True,
+                                          dscale_out=pack.g_s2)
+        # ---- attention
+        dattn = gemm_nt(dx2_b, pack.wo, b_mn_major=True, out_dtype=BF16)              # [M, Dl]
+        _wgrad(dx2_b, attn, pack.g_wo)
+        fused.colsum(dx2_b, out=pack.g_bo)
+        dqkv = attn_bwd(qkv, attn, dattn, lse, m.B, m.T, m.Hl, m.hd, m.scale)
+        fused.rope_inplace(dqkv, pos, rt.cos_half, rt.sin_half, 2, m.Dl, m.Hl, m.hd, inverse=True)
+        dh1 = _colpar_dgrad(dqkv, pack.wqkv)
+        _wgrad(dqkv, h1, pack.g_wqkv)
+        fused.colsum(dqkv, out=pack.g_bqkv)
+        dx, _, _ = fused.rmsnorm_bwd(dh1, x, rstd1, pack.s1, dres=dx2, want_fp32=True, want_bf16=False,
+                                     dscale_out=pack.g_s1)
+        return (dx, None, None, None, None) + (None,) * len(pack.params)
+
+
+class FusedEmbedFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, ids_flat, rt, weight):
+        emb = rt.model.embedding
+        out = fused.embedding_fwd(ids_flat, weight.detach(), emb.vocab_st_idx, emb.vocab_ed_idx, out_dtype=F32)
+        comm_ops.all_reduce_sum_(out)
+        ctx.save_for_backward(ids_flat)
+        ctx.rt = rt
+        return out
+
+    @staticmethod
+    def backward(ctx, dx):
+        (ids_flat,) = ctx.saved_tensors
+        rt = ctx.rt
+        emb = rt.model.embedding
+        fused.embedding_bwd(ids_flat, dx.contiguous(), emb.weight.shape[0], emb.vocab_st_idx, emb.vocab_ed_idx,
+                            dweight=rt.g_emb, zero_first=True)
+        return None, None, None
+
+
+class FusedHeadLossFn(torch.autograd.Function):
+    """final RMSNorm -> vocab-parallel lm_head GEMM -> vocab-parallel softmax cross-entropy (mean over valid)."""
+
+    @staticmethod
+    def forward(ctx, x, targets_flat, rt, ignore_index, *params):
+        n = pm.pgm.tp_size
+        head = rt.model.lm_head
+        Vl = head.odim_partition
+        vocab_start = pm.pgm.tp_rank * Vl
+        h, rstd = fused.rmsnorm_fwd(x, rt.sN, rt.eps)
+        logits = gemm_nt(h, rt.wlm, bias=rt.blm, out_dtype=F32)
+        stats, loss_acc = fused.ce_stats(logits, targets_flat, vocab_start, ignore_index)
+        all_stats = comm_ops.all_gather_rows(stats) if n > 1 else stats
+        fused.ce_loss(targets_flat, all_stats, n, loss_acc, ignore_index)
+        loss = loss_acc[0] / loss_acc[1]
+        ctx.save_for_backward(x, targets_flat, h, rstd, logits, all_stats, loss_acc)
+        ctx.rt, ctx.ignore_index, ctx.vocab_start = rt, ignore_index, vocab_start
+        return loss
+
+    @staticmethod
+    def backward(ctx, gout):
+        x, targets_flat, h, rstd, logits, all_stats, loss_acc = ctx.saved_tensors
+        rt = ctx.rt
+        n = pm.pgm.tp_size
+        up = gout.detach().reshape(1).float().contiguous()
+        dlogits = fused.ce_grad(logits, targets_flat, all_stats, n, loss_acc, ctx.vocab_start, ctx.ignore_index,
+                                upstream=up)
+        dh = _colpar_dgrad(dlogits, rt.wlm)
+        _wgrad(dlogits, h, rt.g_wlm)
+        fused.colsum(dlogits, out=rt.g_blm)
+        dx, _, _ = fused.rmsnorm_bwd(dh, x, rstd, rt.sN, dres=None, want_fp32=True, dscale_out=rt.g_sN)
+        return (dx, None, None, None) + (None,) * 3
+
+
+# ================================================================================================ runtime
+class FusedRuntime:
+    def __init__(self, model):
+        self.model = model
+        n = pm.pgm.tp_size
+        self.n = n
+        self.eps = model.norm.eps
+        d, hd = model.attn_dim, model.head_dim
+        self.d, self.hd = d, hd
+        self.Hl = model.num_heads // n
+        self.Dl = self.Hl * hd
+        self.Fl = model.ffn_dim // n
+        self.arena = ParamArena(model)
+        A = self.arena
+        self.packs: List[LayerPack] = [LayerPack(A, layer, d, self.Dl, self.Fl) for layer in model.layers]
+        head, emb = model.lm_head, model.embedding
+        Vl = head.odim_partition
+        self.wlm, self.g_wlm = A.view(A.shadow, head.weight, Vl, d), A.view(A.grads, head.weight, Vl, d)
+        self.blm, self.g_blm = A.view(A.params, head.bias, Vl), A.view(A.grads, head.bias, Vl)
+        self.sN, self.g_sN = A.view(A.params, model.norm.scale, d), A.view(A.grads, model.norm.scale, d)
+        self.g_emb = A.view(A.grads, emb.weight, emb.weight.shape[0], d)
+        self.head_params = [model.norm.scale, head.weight, head.bias]
+        half = hd // 2
+        self.cos_half = model.rope_cos_f32[:, :half].contiguous().to(A.device)
+        self.sin_half = model.rope_sin_f32[:, :half].contiguous().to(A.device)
+
+    def valid(self) -> bool:
+        return self.arena.valid() and self.n == pm.pgm.tp_size
+
+    # ---------------------------------------------------------------------------------------------- forward
+    def forward_hidden(self, input_ids: torch.Tensor, position_ids: torch.Tensor) -> torch.Tensor:
+        assert input_ids.dim() == 2
+        B, T = input_ids.shape
+        self.arena.sync_shadow()
+        if torch.is_grad_enabled():
+            self.arena.reattach_grads()
+        meta = Meta(B, T, self.d, self.Hl, self.hd, self.Fl, self.n)
+        ids = input_ids.reshape(-1).contiguous()
+        pos = position_ids.reshape(-1).contiguous()
+        x = FusedEmbedFn.apply(ids, self, self.model.embedding.weight)
+        for pack in self.packs:
+            x = FusedLayerFn.apply(x, pos, self, pack, meta, *pack.params)
+        return x  # fp32 [M, d]
+
+    def forward_loss(self, input_ids, position_ids, target_ids, ignore_index: int = -1) -> torch.Tensor:
+        x = self.forward_hidden(input_ids, position_ids)
+        tg = target_ids.reshape(-1).contiguous()
+        return FusedHeadLossFn.apply(x, tg, self, ignore_index, *self.head_params)
+
+    def forward_logits(self, input_ids, position_ids) -> torch.Tensor:
+        B, T = input_ids.shape
+        x = self.forward_hidden(input_ids, position_ids).view(B, T, self.d)
+        with torch.autocast("cuda", dtype=BF16):
+            logits = self.model.lm_head(self.model.norm(x))
+        return logits

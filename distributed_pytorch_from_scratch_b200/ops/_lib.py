@@ -41,7 +41,8 @@ SIGS = {
     "dpfs_embedding_fwd": (c_p, c_p, c_p, c_int, c_int, c_int, c_ll, c_ll, c_p),
     "dpfs_embedding_bwd": (c_p, c_p, c_p, c_int, c_ll, c_int, c_int, c_ll, c_ll, c_p),
     "dpfs_ce_stats": (c_p, c_int, c_ll, c_p, c_p, c_p, c_int, c_int, c_ll, c_ll, c_p),
-    "dpfs_ce_finish": (c_p, c_int, c_ll, c_p, c_p, c_int, c_p, c_ll, c_p, c_p, c_int, c_int, c_ll, c_ll, c_f, c_p),
+    "dpfs_ce_loss": (c_p, c_p, c_int, c_p, c_p, c_int, c_ll, c_p),
+    "dpfs_ce_grad": (c_p, c_int, c_ll, c_p, c_p, c_int, c_p, c_ll, c_p, c_p, c_int, c_int, c_ll, c_ll, c_p),
     "dpfs_adam_step": (c_p, c_p, c_p, c_p, c_p, c_ll, c_p, c_p),
     "dpfs_attn_fwd": (c_p, c_p, c_p, c_int, c_int, c_int, c_int, c_f, c_p),
     "dpfs_attn_bwd": (c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_int, c_int, c_int, c_int, c_f, c_p),

@@ -216,18 +216,30 @@ def ce_stats(logits: torch.Tensor, targets: torch.Tensor, vocab_start: int, igno
     return stats, loss_acc
 
 
-def ce_finish(logits: torch.Tensor, targets: torch.Tensor, all_stats: torch.Tensor, nranks: int,
-              loss_acc: torch.Tensor, vocab_start: int, ignore_index: int, want_grad: bool = True,
-              grad_scale: float = 1.0, want_row_loss: bool = False):
-    """Phase 2: combine the per-rank stats -> mean loss (loss_acc[0]/loss_acc[1]) and bf16 dlogits."""
+def ce_loss(targets: torch.Tensor, all_stats: torch.Tensor, nranks: int, loss_acc: torch.Tensor,
+            ignore_index: int = -1, want_row_loss: bool = False):
+    """Phase 2a: combine the per-rank stats; loss_acc[0] += sum of row losses (mean = loss_acc[0] / loss_acc[1])."""
+    M = targets.numel()
+    row_loss = torch.empty(M, dtype=F32, device=targets.device) if want_row_loss else None
+    rc = _lib.lib().dpfs_ce_loss(targets.data_ptr(), all_stats.data_ptr(), nranks, loss_acc.data_ptr(),
+                                 _lib.ptr(row_loss), M, ignore_index, _lib.stream())
+    _lib.check(rc, "dpfs_ce_loss")
+    return row_loss
+
+
+
+def ce_grad(logits: torch.Tensor, targets: torch.Tensor, all_stats: torch.Tensor, nranks: int,
+            loss_acc: torch.Tensor, vocab_start: int, ignore_index: int, upstream: Optional[torch.Tensor] = None):
+    """Phase 2b: dlogits = (softmax - onehot) * upstream / n_valid as bf16 [M, Vl]."""
     M, Vl = logits.shape
-    dlogits = torch.empty((M, Vl), dtype=BF16, device=logits.device) if want_grad else None
-    row_loss = torch.empty(M, dtype=F32, device=logits.device) if want_row_loss else None
-    rc = _lib.lib().dpfs_ce_finish(logits.data_ptr(), _is_bf16(logits), logits.stride(0), targets.data_ptr(),
-                                   all_stats.data_ptr(), nranks, _lib.ptr(dlogits), Vl, loss_acc.data_ptr(),
-                                   _lib.ptr(row_loss), M, Vl, vocab_start, ignore_index, grad_scale, _lib.stream())
-    _lib.check(rc, "dpfs_ce_finish")
-    return dlogits, row_loss
+    dlogits = torch.empty((M, Vl), dtype=BF16, device=logits.device)
+    if upstream is not None:
+        assert upstream.dtype == F32 and upstream.numel() == 1
+    rc = _lib.lib().dpfs_ce_grad(logits.data_ptr(), _is_bf16(logits), logits.stride(0), targets.data_ptr(),
+                                 all_stats.data_ptr(), nranks, dlogits.data_ptr(), Vl, loss_acc.data_ptr(),
+                                 _lib.ptr(upstream), M, Vl, vocab_start, ignore_index, _lib.stream())
+    _lib.check(rc, "dpfs_ce_grad")
+    return dlogits
 
 
 # ------------------------------------------------------------------------------------------------ optimizer

@@ -1,0 +1,116 @@
+"""Fused Adam / AdamW (csrc/train_ops.cu:adam_kernel) behind the torch.optim.Optimizer interface.
+
+The reference trains with ``optim.Adam(lr)`` driven by ``OneCycleLR`` (train.py:83-84), which rewrites ``lr`` AND
+``betas[0]`` every step.  ``FusedAdam`` keeps ``param_groups`` so the stock scheduler works unchanged, but the update
+itself is ONE kernel launch over the model's flat parameter arena; ``lr``/``beta1``/bias corrections are read from a
+small device buffer (refreshed by an async H2D copy), which makes the launch CUDA-graph capturable.  The same launch
+rewrites the bf16 shadow weights the tcgen05 GEMMs consume.
+
+Off the fused path (CPU / parameters not in an arena) it runs the identical math with torch ops, so CPU tests can
+compare it against ``torch.optim.Adam`` directly.
+"""
+from __future__ import annotations
+
+import math
+from typing import Optional
+
+import torch
+
+from . import fused
+
+
+class FusedAdam(torch.optim.Optimizer):
+    def __init__(self, params, lr=1e-3, betas=(0.9, 0.999), eps=1e-8, weight_decay=0.0, arena=None):
+        """``arena``: a models.fused_transformer.ParamArena (or None for the generic per-tensor torch fallback).
+        ``weight_decay`` is decoupled (AdamW); with the reference's wd = 0 Adam == AdamW exactly."""
+        defaults = dict(lr=lr, betas=betas, eps=eps, weight_decay=weight_decay)
+        super().__init__(params, defaults)
+        self.arena = arena
+        self.step_count = 0
+        self._hyper_host: Optional[torch.Tensor] = None
+        self._hyper_dev: Optional[torch.Tensor] = None
+        self._m = self._v = None
+        if arena is not None:
+            self._m = torch.zeros_like(arena.params)
+            self._v = torch.zeros_like(arena.params)
+            self._hyper_host = torch.zeros(8, dtype=torch.float32)
+            if arena.params.is_cuda:
+                self._hyper_host = self._hyper_host.pin_memory()
+            self._hyper_dev = torch.zeros(8, dtype=torch.float32, device=arena.params.device)
+
+    @classmethod
+    def for_model(cls, model, lr=1e-3, betas=(0.9, 0.999), eps=1e-8, weight_decay=0.0):
+        """Fused optimizer over the model's arena when the fused path is active, else the generic fallback."""
+        arena = None
+        p0 = next(model.parameters())
+        if p0.is_cuda and hasattr(model, "fused_runtime"):
+            from ..models.fused_transformer import fused_supported
+            from .dispatch import native_available
+            if native_available() and fused_supported(model):
+                arena = model.fused_runtime().arena
+        return cls(model.parameters(), lr=lr, betas=betas, eps=eps, weight_decay=weight_decay, arena=arena)
+
+    def zero_grad(self, set_to_none: bool = False):
+        if self.arena is not None:
+            return  # every gradient slot is overwritten by the wgrad kernels each step
+        super().zero_grad(set_to_none=set_to_none)
+
+    # -- split in two so a CUDA graph can capture only the launch
+    def update_hyper(self):
+        """Advance the step counter and upload {lr, beta1, beta2, eps, bc1, bc2, wd} (async, pinned)."""
+        self.step_count += 1
+        g = self.param_groups[0]
+        b1, b2 = g["betas"]
+        t = self.step_count
+        vals = [g["lr"], b1, b2, g["eps"], 1.0 - b1 ** t, 1.0 - b2 ** t, g["weight_decay"], 0.0]
+        if self._hyper_host is not None:
+            self._hyper_host.copy_(torch.tensor(vals, dtype=torch.float32))
+            self._hyper_dev.copy_(self._hyper_host, non_blocking=True)
+        return vals
+
+    def launch(self):
+        a = self.arena
+        fused.adam_step(a.params, a.grads, self._m, self._v, a.shadow, self._hyper_dev)
+
+    @torch.no_grad()
+    def step(self, closure=None):
+        loss = closure() if closure is not None else None
+        if self.arena is not None:
+            self.update_hyper()
+            self.launch()
+            return loss
+        self.step_count += 1
+        t = self.step_count
+        for g in self.param_groups:
+            b1, b2 = g["betas"]
+            lr, eps, wd = g["lr"], g["eps"], g["weight_decay"]
+            bc1, bc2 = 1.0 - b1 ** t, 1.0 - b2 ** t
+            for p in g["params"]:
+                if p.grad is None:
+                    continue
+                st = self.state[p]
+                if not st:
+                    st["exp_avg"] = torch.zeros_like(p)
+                    st["exp_avg_sq"] = torch.zeros_like(p)
+                m, v = st["exp_avg"], st["exp_avg_sq"]
+                if wd != 0.0:
+                    p.mul_(1.0 - lr * wd)
+                m.mul_(b1).add_(p.grad, alpha=1.0 - b1)
+                v.mul_(b2).addcmul_(p.grad, p.grad, value=1.0 - b2)
+                denom = (v.sqrt() / math.sqrt(bc2)).add_(eps)
+                p.addcdiv_(m, denom, value=-lr / bc1)
+        return loss
+
+    # -- resume support (extra files next to the reference-format checkpoints)
+    def fused_state(self):
+        if self.arena is None:
+            return {"step": self.step_count, "state": self.state_dict()}
+        return {"step": self.step_count, "m": self._m.clone(), "v": self._v.clone()}
+
+    def load_fused_state(self, st):
+        self.step_count = st["step"]
+        if self.arena is None:
+            self.load_state_dict(st["state"])
+        else:
+            self._m.copy_(st["m"])
+            self._v.copy_(st["v"])

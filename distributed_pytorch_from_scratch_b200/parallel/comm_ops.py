@@ -104,3 +104,26 @@ class Gather(torch.autograd.Function):
     @staticmethod
     def backward(ctx, grad_output: torch.Tensor) -> torch.Tensor:
         return local_chunk_last_dim(grad_output)
+
+
+def all_reduce_sum_(t: torch.Tensor) -> torch.Tensor:
+    """In-place SUM all-reduce of a tensor we own (never an autograd input); returns ``t``."""
+    n, _, group = _tp()
+    if n == 1:
+        return t
+    symm = pm.pgm.symm
+    if symm is not None and t.is_cuda and symm.supports(t):
+        return symm.all_reduce(t, out=t)
+    dist.all_reduce(t, op=dist.ReduceOp.SUM, group=group)
+    return t
+
+
+def all_gather_rows(t: torch.Tensor) -> torch.Tensor:
+    """Gather a tensor from every TP rank along a new leading dim: (...) -> (n, ...)."""
+    n, _, group = _tp()
+    if n == 1:
+        return t.unsqueeze(0)
+    t = t.contiguous()
+    out = torch.empty((n,) + tuple(t.shape), dtype=t.dtype, device=t.device)
+    dist.all_gather_into_tensor(out, t, group=group)
+    return out

@@ -93,18 +93,21 @@ int dpfs_embedding_bwd(const long long* ids, const float* dout, float* dweight, 
                        cudaStream_t stream);
 
 /* ---- Vocab-parallel softmax cross-entropy ------------------------------------------------------------------------
- * Phase 1: stats[m] = {max, sum exp(x - max), target logit if owned} over the local shard [M][Vl]; loss_acc[2] is
- * reset and loss_acc[1] receives the number of non-ignored targets.  Phase 2 (after the ranks exchanged their
- * stats into all_stats [nranks][M][3]): loss_acc[0] += sum of row losses; dlogits (bf16 [M][ldd], nullable) =
- * (softmax - onehot) * grad_scale / n_valid; row_loss (nullable) per-row loss.
+ * Phase 1 (dpfs_ce_stats): stats[m] = {max, sum exp(x - max), target logit if owned} over the local shard
+ * [M][Vl]; loss_acc[2] is reset and loss_acc[1] receives the number of non-ignored targets.  The ranks then
+ * exchange their stats into all_stats [nranks][M][3] (tiny all-gather).  dpfs_ce_loss: loss_acc[0] += sum of row
+ * losses (mean loss = loss_acc[0] / loss_acc[1]); row_loss nullable.  dpfs_ce_grad: dlogits (bf16 [M][ldd]) =
+ * (softmax - onehot) * upstream[0] / n_valid, where `upstream` is a device scalar (nullable = 1).
  * ref: F.cross_entropy on gathered logits, train.py:101-104 + Gather in models/layers.py:99. */
 int dpfs_ce_stats(const void* logits, int logits_bf16, long long ld, const long long* targets, float* stats,
                   float* loss_acc, int M, int Vl, long long vocab_start, long long ignore_index,
                   cudaStream_t stream);
-int dpfs_ce_finish(const void* logits, int logits_bf16, long long ld, const long long* targets,
-                   const float* all_stats, int nranks, void* dlogits, long long ldd, float* loss_acc,
-                   float* row_loss, int M, int Vl, long long vocab_start, long long ignore_index, float grad_scale,
-                   cudaStream_t stream);
+int dpfs_ce_loss(const long long* targets, const float* all_stats, int nranks, float* loss_acc, float* row_loss,
+                 int M, long long ignore_index, cudaStream_t stream);
+int dpfs_ce_grad(const void* logits, int logits_bf16, long long ld, const long long* targets,
+                 const float* all_stats, int nranks, void* dlogits, long long ldd, const float* loss_acc,
+                 const float* upstream, int M, int Vl, long long vocab_start, long long ignore_index,
+                 cudaStream_t stream);
 
 /* ---- Fused Adam / AdamW over a flat arena ------------------------------------------------------------------------
  * hyper (device): {lr, beta1, beta2, eps, bias_correction1, bias_correction2, decoupled weight decay}.
