@@ -586,7 +586,7 @@ static int launch_fwd(const CUtensorMap& tm, void* out, float* lse, int B, int T
     configured = true;
   }
   dim3 grid((T + kTile - 1) / kTile, H, B);
-  kfn<<<grid, kAttnThreads, C::kSmem, stream>>>(tm, reinterpret_cast<__nv_bfloat16*>(out), lse, T, H, H * HD,
+  kfn<<<(DPFS_COUNT(), grid), kAttnThreads, C::kSmem, stream>>>(tm, reinterpret_cast<__nv_bfloat16*>(out), lse, T, H, H * HD,
                                                scale * kLog2e);
   return static_cast<int>(cudaGetLastError());
 }
@@ -603,7 +603,7 @@ static int launch_bwd(const CUtensorMap& tm_qkv, const CUtensorMap& tm_do, const
     configured = true;
   }
   dim3 grid((T + kTile - 1) / kTile, H, B);
-  kfn<<<grid, kAttnThreads, C::kSmem, stream>>>(tm_qkv, tm_do, lse, delta, dq_acc,
+  kfn<<<(DPFS_COUNT(), grid), kAttnThreads, C::kSmem, stream>>>(tm_qkv, tm_do, lse, delta, dq_acc,
                                                reinterpret_cast<__nv_bfloat16*>(dqkv), T, H, H * HD, scale,
                                                scale * kLog2e);
   return static_cast<int>(cudaGetLastError());
@@ -642,7 +642,7 @@ extern "C" int dpfs_attn_bwd(const void* qkv, const void* out, const void* d_out
     const long long warps = M * H;
     long long blocks = (warps + 7) / 8;
     if (blocks > num_sms() * 16LL) blocks = num_sms() * 16LL;
-    attn_delta_kernel<<<static_cast<int>(blocks), 256, 0, stream>>>(
+    attn_delta_kernel<<<(DPFS_COUNT(), static_cast<int>(blocks)), 256, 0, stream>>>(
         reinterpret_cast<const __nv_bfloat16*>(out), reinterpret_cast<const __nv_bfloat16*>(d_out), delta, B, T, H,
         HD);
   }
@@ -653,7 +653,7 @@ extern "C" int dpfs_attn_bwd(const void* qkv, const void* out, const void* d_out
     const long long total = M * (Dl / 4);
     long long blocks = (total + 255) / 256;
     if (blocks > num_sms() * 16LL) blocks = num_sms() * 16LL;
-    attn_dq_convert_kernel<<<static_cast<int>(blocks), 256, 0, stream>>>(
+    attn_dq_convert_kernel<<<(DPFS_COUNT(), static_cast<int>(blocks)), 256, 0, stream>>>(
         dq_acc, reinterpret_cast<__nv_bfloat16*>(dqkv), M, Dl);
   }
   return static_cast<int>(cudaGetLastError());

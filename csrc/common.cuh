@@ -12,6 +12,10 @@
 
 namespace dpfs {
 
+// number of kernels this library has launched (bench.py reports it as gpu_launches)
+extern unsigned long long g_launches;
+#define DPFS_COUNT() (++::dpfs::g_launches)
+
 // ---------------------------------------------------------------------------------------------
 // misc
 // ---------------------------------------------------------------------------------------------

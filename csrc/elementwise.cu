@@ -541,16 +541,16 @@ extern "C" int dpfs_rmsnorm_fwd(const void* x, int x_bf16, const float* scale, v
   const int grid = norm_grid(M);
   DISPATCH_NV(D, {
     if (x_bf16 && y_bf16)
-      rmsnorm_fwd_kernel<__nv_bfloat16, __nv_bfloat16, NV><<<grid, kNormThreads, 0, stream>>>(
+      rmsnorm_fwd_kernel<__nv_bfloat16, __nv_bfloat16, NV><<<(DPFS_COUNT(), grid), kNormThreads, 0, stream>>>(
           (const __nv_bfloat16*)x, scale, (__nv_bfloat16*)y, rstd, M, D, eps);
     else if (x_bf16 && !y_bf16)
-      rmsnorm_fwd_kernel<__nv_bfloat16, float, NV><<<grid, kNormThreads, 0, stream>>>(
+      rmsnorm_fwd_kernel<__nv_bfloat16, float, NV><<<(DPFS_COUNT(), grid), kNormThreads, 0, stream>>>(
           (const __nv_bfloat16*)x, scale, (float*)y, rstd, M, D, eps);
     else if (!x_bf16 && y_bf16)
-      rmsnorm_fwd_kernel<float, __nv_bfloat16, NV><<<grid, kNormThreads, 0, stream>>>(
+      rmsnorm_fwd_kernel<float, __nv_bfloat16, NV><<<(DPFS_COUNT(), grid), kNormThreads, 0, stream>>>(
           (const float*)x, scale, (__nv_bfloat16*)y, rstd, M, D, eps);
     else
-      rmsnorm_fwd_kernel<float, float, NV><<<grid, kNormThreads, 0, stream>>>((const float*)x, scale, (float*)y,
+      rmsnorm_fwd_kernel<float, float, NV><<<(DPFS_COUNT(), grid), kNormThreads, 0, stream>>>((const float*)x, scale, (float*)y,
                                                                               rstd, M, D, eps);
   });
   return static_cast<int>(cudaGetLastError());
@@ -564,22 +564,22 @@ extern "C" int dpfs_rmsnorm_bwd(const void* dy, int dy_bf16, const void* x, int 
   const int grid = norm_grid(M);
   DISPATCH_NV(D, {
     if (dy_bf16 && !x_bf16)
-      rmsnorm_bwd_kernel<float, __nv_bfloat16, NV><<<grid, kNormThreads, 0, stream>>>(
+      rmsnorm_bwd_kernel<float, __nv_bfloat16, NV><<<(DPFS_COUNT(), grid), kNormThreads, 0, stream>>>(
           (const __nv_bfloat16*)dy, (const float*)x, rstd, scale, dres, dx, (__nv_bfloat16*)dx_bf16, scratch, M, D);
     else if (dy_bf16 && x_bf16)
-      rmsnorm_bwd_kernel<__nv_bfloat16, __nv_bfloat16, NV><<<grid, kNormThreads, 0, stream>>>(
+      rmsnorm_bwd_kernel<__nv_bfloat16, __nv_bfloat16, NV><<<(DPFS_COUNT(), grid), kNormThreads, 0, stream>>>(
           (const __nv_bfloat16*)dy, (const __nv_bfloat16*)x, rstd, scale, dres, dx, (__nv_bfloat16*)dx_bf16, scratch,
           M, D);
     else if (!dy_bf16 && !x_bf16)
-      rmsnorm_bwd_kernel<float, float, NV><<<grid, kNormThreads, 0, stream>>>(
+      rmsnorm_bwd_kernel<float, float, NV><<<(DPFS_COUNT(), grid), kNormThreads, 0, stream>>>(
           (const float*)dy, (const float*)x, rstd, scale, dres, dx, (__nv_bfloat16*)dx_bf16, scratch, M, D);
     else
-      rmsnorm_bwd_kernel<__nv_bfloat16, float, NV><<<grid, kNormThreads, 0, stream>>>(
+      rmsnorm_bwd_kernel<__nv_bfloat16, float, NV><<<(DPFS_COUNT(), grid), kNormThreads, 0, stream>>>(
           (const float*)dy, (const __nv_bfloat16*)x, rstd, scale, dres, dx, (__nv_bfloat16*)dx_bf16, scratch, M, D);
   });
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) return static_cast<int>(e);
-  reduce_partials_kernel<<<(D + 255) / 256, 256, 0, stream>>>(scratch, dscale, grid, D, dscale_accumulate);
+  reduce_partials_kernel<<<(DPFS_COUNT(), (D + 255) / 256), 256, 0, stream>>>(scratch, dscale, grid, D, dscale_accumulate);
   return static_cast<int>(cudaGetLastError());
 }
 
@@ -591,16 +591,16 @@ extern "C" int dpfs_layernorm_fwd(const void* x, int x_bf16, const float* gamma,
   const int grid = norm_grid(M);
   DISPATCH_NV(D, {
     if (x_bf16 && y_bf16)
-      layernorm_fwd_kernel<__nv_bfloat16, __nv_bfloat16, NV><<<grid, kNormThreads, 0, stream>>>(
+      layernorm_fwd_kernel<__nv_bfloat16, __nv_bfloat16, NV><<<(DPFS_COUNT(), grid), kNormThreads, 0, stream>>>(
           (const __nv_bfloat16*)x, gamma, beta, (__nv_bfloat16*)y, mean, rstd, M, D, eps);
     else if (!x_bf16 && y_bf16)
-      layernorm_fwd_kernel<float, __nv_bfloat16, NV><<<grid, kNormThreads, 0, stream>>>(
+      layernorm_fwd_kernel<float, __nv_bfloat16, NV><<<(DPFS_COUNT(), grid), kNormThreads, 0, stream>>>(
           (const float*)x, gamma, beta, (__nv_bfloat16*)y, mean, rstd, M, D, eps);
     else if (!x_bf16 && !y_bf16)
-      layernorm_fwd_kernel<float, float, NV><<<grid, kNormThreads, 0, stream>>>((const float*)x, gamma, beta,
+      layernorm_fwd_kernel<float, float, NV><<<(DPFS_COUNT(), grid), kNormThreads, 0, stream>>>((const float*)x, gamma, beta,
                                                                                 (float*)y, mean, rstd, M, D, eps);
     else
-      layernorm_fwd_kernel<__nv_bfloat16, float, NV><<<grid, kNormThreads, 0, stream>>>(
+      layernorm_fwd_kernel<__nv_bfloat16, float, NV><<<(DPFS_COUNT(), grid), kNormThreads, 0, stream>>>(
           (const __nv_bfloat16*)x, gamma, beta, (float*)y, mean, rstd, M, D, eps);
   });
   return static_cast<int>(cudaGetLastError());
@@ -614,22 +614,22 @@ extern "C" int dpfs_layernorm_bwd(const void* dy, int dy_bf16, const void* x, in
   const int grid = norm_grid(M);
   DISPATCH_NV(D, {
     if (dy_bf16 && x_bf16)
-      layernorm_bwd_kernel<__nv_bfloat16, __nv_bfloat16, NV><<<grid, kNormThreads, 0, stream>>>(
+      layernorm_bwd_kernel<__nv_bfloat16, __nv_bfloat16, NV><<<(DPFS_COUNT(), grid), kNormThreads, 0, stream>>>(
           (const __nv_bfloat16*)dy, (const __nv_bfloat16*)x, mean, rstd, gamma, dx, scratch, M, D);
     else if (dy_bf16 && !x_bf16)
-      layernorm_bwd_kernel<float, __nv_bfloat16, NV><<<grid, kNormThreads, 0, stream>>>(
+      layernorm_bwd_kernel<float, __nv_bfloat16, NV><<<(DPFS_COUNT(), grid), kNormThreads, 0, stream>>>(
           (const __nv_bfloat16*)dy, (const float*)x, mean, rstd, gamma, dx, scratch, M, D);
     else if (!dy_bf16 && !x_bf16)
-      layernorm_bwd_kernel<float, float, NV><<<grid, kNormThreads, 0, stream>>>((const float*)dy, (const float*)x,
+      layernorm_bwd_kernel<float, float, NV><<<(DPFS_COUNT(), grid), kNormThreads, 0, stream>>>((const float*)dy, (const float*)x,
                                                                                 mean, rstd, gamma, dx, scratch, M, D);
     else
-      layernorm_bwd_kernel<__nv_bfloat16, float, NV><<<grid, kNormThreads, 0, stream>>>(
+      layernorm_bwd_kernel<__nv_bfloat16, float, NV><<<(DPFS_COUNT(), grid), kNormThreads, 0, stream>>>(
           (const float*)dy, (const __nv_bfloat16*)x, mean, rstd, gamma, dx, scratch, M, D);
   });
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) return static_cast<int>(e);
   // partial rows are [dgamma(D) | dbeta(D)]: reduce as one 2D-wide vector into a strided pair of outputs
-  reduce_partials_kernel<<<(2 * D + 255) / 256, 256, 0, stream>>>(scratch, scratch + (long long)grid * 2 * D, grid,
+  reduce_partials_kernel<<<(DPFS_COUNT(), (2 * D + 255) / 256), 256, 0, stream>>>(scratch, scratch + (long long)grid * 2 * D, grid,
                                                                   2 * D, 0);
   e = cudaGetLastError();
   if (e != cudaSuccess) return static_cast<int>(e);
@@ -644,7 +644,7 @@ extern "C" int dpfs_swiglu_fwd(const void* gu, void* act, int M, int F, cudaStre
   if (F % 8 != 0) return -21;
   if (M <= 0) return 0;
   const long long total = static_cast<long long>(M) * (F / 8);
-  swiglu_fwd_kernel<<<ew_grid(total, 256), 256, 0, stream>>>((const __nv_bfloat16*)gu, (__nv_bfloat16*)act, M, F);
+  swiglu_fwd_kernel<<<(DPFS_COUNT(), ew_grid(total, 256)), 256, 0, stream>>>((const __nv_bfloat16*)gu, (__nv_bfloat16*)act, M, F);
   return static_cast<int>(cudaGetLastError());
 }
 
@@ -652,7 +652,7 @@ extern "C" int dpfs_swiglu_bwd(const void* dact, const void* gu, void* dgu, int 
   if (F % 8 != 0) return -21;
   if (M <= 0) return 0;
   const long long total = static_cast<long long>(M) * (F / 8);
-  swiglu_bwd_kernel<<<ew_grid(total, 256), 256, 0, stream>>>((const __nv_bfloat16*)dact, (const __nv_bfloat16*)gu,
+  swiglu_bwd_kernel<<<(DPFS_COUNT(), ew_grid(total, 256)), 256, 0, stream>>>((const __nv_bfloat16*)dact, (const __nv_bfloat16*)gu,
                                                              (__nv_bfloat16*)dgu, M, F);
   return static_cast<int>(cudaGetLastError());
 }
@@ -660,14 +660,14 @@ extern "C" int dpfs_swiglu_bwd(const void* dact, const void* gu, void* dgu, int 
 extern "C" int dpfs_gelu_fwd(const void* x, void* y, long long n, cudaStream_t stream) {
   if (n % 8 != 0) return -21;
   if (n <= 0) return 0;
-  gelu_fwd_kernel<<<ew_grid(n / 8, 256), 256, 0, stream>>>((const __nv_bfloat16*)x, (__nv_bfloat16*)y, n / 8);
+  gelu_fwd_kernel<<<(DPFS_COUNT(), ew_grid(n / 8, 256)), 256, 0, stream>>>((const __nv_bfloat16*)x, (__nv_bfloat16*)y, n / 8);
   return static_cast<int>(cudaGetLastError());
 }
 
 extern "C" int dpfs_gelu_bwd(const void* dy, const void* x, void* dx, long long n, cudaStream_t stream) {
   if (n % 8 != 0) return -21;
   if (n <= 0) return 0;
-  gelu_bwd_kernel<<<ew_grid(n / 8, 256), 256, 0, stream>>>((const __nv_bfloat16*)dy, (const __nv_bfloat16*)x,
+  gelu_bwd_kernel<<<(DPFS_COUNT(), ew_grid(n / 8, 256)), 256, 0, stream>>>((const __nv_bfloat16*)dy, (const __nv_bfloat16*)x,
                                                            (__nv_bfloat16*)dx, n / 8);
   return static_cast<int>(cudaGetLastError());
 }
@@ -678,7 +678,7 @@ extern "C" int dpfs_rope_inplace(void* buf, long long ld, const long long* pos, 
   if (hd % 16 != 0 || ld % 8 != 0 || seg_stride % 8 != 0) return -22;
   if (M <= 0) return 0;
   const long long total = static_cast<long long>(M) * nseg * H * (hd / 16);
-  rope_kernel<<<ew_grid(total, 256), 256, 0, stream>>>((__nv_bfloat16*)buf, ld, pos, cos_t, sin_t, M, nseg,
+  rope_kernel<<<(DPFS_COUNT(), ew_grid(total, 256)), 256, 0, stream>>>((__nv_bfloat16*)buf, ld, pos, cos_t, sin_t, M, nseg,
                                                        seg_stride, H, hd, inverse ? -1.f : 1.f);
   return static_cast<int>(cudaGetLastError());
 }
@@ -693,16 +693,16 @@ extern "C" int dpfs_colsum_bf16(const void* x, long long ld, float* out, int acc
   if (M <= 0) return 0;
   const int strips = (M + kColsumRowsPerBlock - 1) / kColsumRowsPerBlock;
   dim3 grid((N / 8 + 127) / 128, strips);
-  colsum_partial_kernel<<<grid, 128, 0, stream>>>((const __nv_bfloat16*)x, ld, scratch, M, N);
+  colsum_partial_kernel<<<(DPFS_COUNT(), grid), 128, 0, stream>>>((const __nv_bfloat16*)x, ld, scratch, M, N);
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) return static_cast<int>(e);
-  reduce_partials_kernel<<<(N + 255) / 256, 256, 0, stream>>>(scratch, out, strips, N, accumulate);
+  reduce_partials_kernel<<<(DPFS_COUNT(), (N + 255) / 256), 256, 0, stream>>>(scratch, out, strips, N, accumulate);
   return static_cast<int>(cudaGetLastError());
 }
 
 extern "C" int dpfs_cast_f32_to_bf16(const float* x, void* y, long long n, cudaStream_t stream) {
   if (n % 4 != 0) return -24;
   if (n <= 0) return 0;
-  cast_f32_to_bf16_kernel<<<ew_grid(n / 4, 256), 256, 0, stream>>>(x, (__nv_bfloat16*)y, n / 4);
+  cast_f32_to_bf16_kernel<<<(DPFS_COUNT(), ew_grid(n / 4, 256)), 256, 0, stream>>>(x, (__nv_bfloat16*)y, n / 4);
   return static_cast<int>(cudaGetLastError());
 }

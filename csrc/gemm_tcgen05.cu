@@ -18,6 +18,8 @@
 
 namespace dpfs {
 
+unsigned long long g_launches = 0;
+
 constexpr int BM = 128;
 constexpr int BK = 64;
 constexpr int kGemmThreads = 192;  // warp 0: TMA producer, warp 1: MMA issuer + TMEM owner, warps 2-5: epilogue
@@ -357,7 +359,7 @@ static int launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const Gem
   }
   const int tiles = ((args.M + BM - 1) / BM) * ((args.N + BN - 1) / BN) * args.splits;
   const int grid = tiles < num_sms() ? tiles : num_sms();
-  kfn<<<grid, kGemmThreads, S::kTotal, stream>>>(tmA, tmB, args);
+  kfn<<<(DPFS_COUNT(), grid), kGemmThreads, S::kTotal, stream>>>(tmA, tmB, args);
   return static_cast<int>(cudaGetLastError());
 }
 
@@ -437,12 +439,14 @@ extern "C" int dpfs_gemm_bf16(const void* A, long long lda, int a_mn_major, cons
     int blocks = static_cast<int>((total4 + 255) / 256);
     if (blocks > num_sms() * 8) blocks = num_sms() * 8;
     if (out_fp32)
-      splitk_reduce_kernel<float><<<blocks, 256, 0, stream>>>(workspace, reinterpret_cast<float*>(out), ldo, bias,
+      splitk_reduce_kernel<float><<<(DPFS_COUNT(), blocks), 256, 0, stream>>>(workspace, reinterpret_cast<float*>(out), ldo, bias,
                                                              M, N, splits);
     else
-      splitk_reduce_kernel<__nv_bfloat16><<<blocks, 256, 0, stream>>>(
+      splitk_reduce_kernel<__nv_bfloat16><<<(DPFS_COUNT(), blocks), 256, 0, stream>>>(
           workspace, reinterpret_cast<__nv_bfloat16*>(out), ldo, bias, M, N, splits);
     rc = static_cast<int>(cudaGetLastError());
   }
   return rc;
 }
+
+extern "C" unsigned long long dpfs_launch_count(void) { return dpfs::g_launches; }

@@ -256,10 +256,10 @@ extern "C" int dpfs_embedding_fwd(const long long* ids, const float* weight, voi
   if (M <= 0) return 0;
   const long long total = static_cast<long long>(M) * (D / 4);
   if (out_bf16)
-    embedding_fwd_kernel<__nv_bfloat16><<<ew_grid2(total, 256), 256, 0, stream>>>(ids, weight, (__nv_bfloat16*)out, M,
+    embedding_fwd_kernel<__nv_bfloat16><<<(DPFS_COUNT(), ew_grid2(total, 256)), 256, 0, stream>>>(ids, weight, (__nv_bfloat16*)out, M,
                                                                                  D, vocab_start, vocab_end);
   else
-    embedding_fwd_kernel<float><<<ew_grid2(total, 256), 256, 0, stream>>>(ids, weight, (float*)out, M, D, vocab_start,
+    embedding_fwd_kernel<float><<<(DPFS_COUNT(), ew_grid2(total, 256)), 256, 0, stream>>>(ids, weight, (float*)out, M, D, vocab_start,
                                                                          vocab_end);
   return static_cast<int>(cudaGetLastError());
 }
@@ -271,7 +271,7 @@ extern "C" int dpfs_embedding_bwd(const long long* ids, const float* dout, float
   if (zero_first) cudaMemsetAsync(dweight, 0, sizeof(float) * local_vocab * D, stream);
   if (M <= 0) return 0;
   const long long total = static_cast<long long>(M) * (D / 4);
-  embedding_bwd_kernel<<<ew_grid2(total, 256), 256, 0, stream>>>(ids, dout, dweight, M, D, vocab_start, vocab_end);
+  embedding_bwd_kernel<<<(DPFS_COUNT(), ew_grid2(total, 256)), 256, 0, stream>>>(ids, dout, dweight, M, D, vocab_start, vocab_end);
   return static_cast<int>(cudaGetLastError());
 }
 
@@ -280,14 +280,14 @@ extern "C" int dpfs_ce_stats(const void* logits, int logits_bf16, long long ld, 
                              long long ignore_index, cudaStream_t stream) {
   if (M <= 0) return 0;
   cudaMemsetAsync(loss_acc, 0, 2 * sizeof(float), stream);
-  ce_count_kernel<<<(M + 255) / 256 > 64 ? 64 : (M + 255) / 256, 256, 0, stream>>>(targets, M, ignore_index,
+  ce_count_kernel<<<(DPFS_COUNT(), (M + 255) / 256 > 64 ? 64 : (M + 255) / 256), 256, 0, stream>>>(targets, M, ignore_index,
                                                                                   loss_acc);
   const int grid = M < num_sms() * 8 ? M : num_sms() * 8;
   if (logits_bf16)
-    ce_stats_kernel<__nv_bfloat16><<<grid, kCeThreads, 0, stream>>>((const __nv_bfloat16*)logits, ld, targets, stats,
+    ce_stats_kernel<__nv_bfloat16><<<(DPFS_COUNT(), grid), kCeThreads, 0, stream>>>((const __nv_bfloat16*)logits, ld, targets, stats,
                                                                    M, Vl, vocab_start, ignore_index);
   else
-    ce_stats_kernel<float><<<grid, kCeThreads, 0, stream>>>((const float*)logits, ld, targets, stats, M, Vl,
+    ce_stats_kernel<float><<<(DPFS_COUNT(), grid), kCeThreads, 0, stream>>>((const float*)logits, ld, targets, stats, M, Vl,
                                                             vocab_start, ignore_index);
   return static_cast<int>(cudaGetLastError());
 }
@@ -297,7 +297,7 @@ extern "C" int dpfs_ce_loss(const long long* targets, const float* all_stats, in
   if (M <= 0) return 0;
   int grid = (M + 255) / 256;
   if (grid > num_sms() * 4) grid = num_sms() * 4;
-  ce_loss_kernel<<<grid, 256, 0, stream>>>(targets, all_stats, nranks, loss_acc, row_loss, M, ignore_index);
+  ce_loss_kernel<<<(DPFS_COUNT(), grid), 256, 0, stream>>>(targets, all_stats, nranks, loss_acc, row_loss, M, ignore_index);
   return static_cast<int>(cudaGetLastError());
 }
 
@@ -308,11 +308,11 @@ extern "C" int dpfs_ce_grad(const void* logits, int logits_bf16, long long ld, c
   if (M <= 0) return 0;
   const int grid = M < num_sms() * 8 ? M : num_sms() * 8;
   if (logits_bf16)
-    ce_grad_kernel<__nv_bfloat16><<<grid, kCeThreads, 0, stream>>>(
+    ce_grad_kernel<__nv_bfloat16><<<(DPFS_COUNT(), grid), kCeThreads, 0, stream>>>(
         (const __nv_bfloat16*)logits, ld, targets, all_stats, nranks, (__nv_bfloat16*)dlogits, ldd, loss_acc,
         upstream, M, Vl, vocab_start, ignore_index);
   else
-    ce_grad_kernel<float><<<grid, kCeThreads, 0, stream>>>((const float*)logits, ld, targets, all_stats, nranks,
+    ce_grad_kernel<float><<<(DPFS_COUNT(), grid), kCeThreads, 0, stream>>>((const float*)logits, ld, targets, all_stats, nranks,
                                                            (__nv_bfloat16*)dlogits, ldd, loss_acc, upstream, M, Vl,
                                                            vocab_start, ignore_index);
   return static_cast<int>(cudaGetLastError());
@@ -322,6 +322,6 @@ extern "C" int dpfs_adam_step(float* p, const float* g, float* m, float* v, void
                               const float* hyper, cudaStream_t stream) {
   if (n % 4 != 0) return -31;
   if (n <= 0) return 0;
-  adam_kernel<<<ew_grid2(n / 4, 256), 256, 0, stream>>>(p, g, m, v, (__nv_bfloat16*)shadow_bf16, n / 4, hyper);
+  adam_kernel<<<(DPFS_COUNT(), ew_grid2(n / 4, 256)), 256, 0, stream>>>(p, g, m, v, (__nv_bfloat16*)shadow_bf16, n / 4, hyper);
   return static_cast<int>(cudaGetLastError());
 }
