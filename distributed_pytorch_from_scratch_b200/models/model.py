@@ -232,6 +232,8 @@ class Transformer(nn.Module):
     def _fused_ok(self, input_ids: torch.Tensor) -> bool:
         if not input_ids.is_cuda or not dispatch.native_available():
             return False
+        if self.embedding.weight.dtype != torch.float32 or not self.embedding.weight.is_cuda:
+            return False
         bf16 = self._dtype() == torch.bfloat16 or (
             torch.is_autocast_enabled("cuda") and torch.get_autocast_dtype("cuda") == torch.bfloat16)
         if not bf16:

@@ -37,13 +37,20 @@ def all_reduce_sum(t: torch.Tensor) -> torch.Tensor:
     return out
 
 
+def _all_gather_stacked(t: torch.Tensor, n: int, group) -> torch.Tensor:
+    """(...) -> (n, ...) in rank order; one flat buffer, no per-rank list (the reference builds a zeros list + cat)."""
+    t = t.contiguous()
+    flat = t.reshape(-1)
+    out = torch.empty(n * flat.numel(), dtype=t.dtype, device=t.device)
+    dist.all_gather_into_tensor(out, flat, group=group)
+    return out.view((n,) + tuple(t.shape))
+
+
 def all_gather_last_dim(t: torch.Tensor) -> torch.Tensor:
     n, _, group = _tp()
     if n == 1:
         return t
-    t = t.contiguous()
-    gathered = torch.empty((n,) + tuple(t.shape), dtype=t.dtype, device=t.device)
-    dist.all_gather_into_tensor(gathered, t, group=group)
+    gathered = _all_gather_stacked(t, n, group)
     # (n, ..., c) -> (..., n*c)
     return torch.cat(list(gathered.unbind(0)), dim=-1)
 
@@ -123,7 +130,4 @@ def all_gather_rows(t: torch.Tensor) -> torch.Tensor:
     n, _, group = _tp()
     if n == 1:
         return t.unsqueeze(0)
-    t = t.contiguous()
-    out = torch.empty((n,) + tuple(t.shape), dtype=t.dtype, device=t.device)
-    dist.all_gather_into_tensor(out, t, group=group)
-    return out
+    return _all_gather_stacked(t, n, group)

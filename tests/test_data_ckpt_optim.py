@@ -1,0 +1,156 @@
+"""Dataset / collate layout, checkpoint format + rotation + resharding + interchange with the reference loader,
+FusedAdam == torch.optim.Adam under OneCycleLR, C-ABI table consistency."""
+import json
+import os
+import re
+import sys
+
+import pytest
+import torch
+
+REPO = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def test_collate_layout_and_loader(tmp_path):
+    from dataset import ShakespeareDataset, collate_fn, get_dataloader, write_synthetic_corpus
+    b = collate_fn([[5, 6, 7], [8]], bos=0, eos=1, ignore_idx=-1)
+    assert b["input_ids"].tolist() == [[0, 5, 6, 7], [0, 8, 1, 1]]
+    assert b["target_ids"].tolist() == [[5, 6, 7, 1], [8, 1, -1, -1]]
+    assert b["position_ids"].tolist() == [[0, 1, 2, 3], [0, 1, 2, 3]]
+    path = write_synthetic_corpus(str(tmp_path / "tok.json"), vocab_size=64, n_train=10, n_val=3, min_len=4, max_len=40)
+    data = json.load(open(path))
+    assert set(data) == {"train", "validation", "special_ids", "vocab_size"}
+    assert data["special_ids"] == {"<BOS>": 0, "<EOS>": 1, "<UNK>": 2}
+    ds = ShakespeareDataset(path, "train", maxlen=16)
+    assert len(ds) == 10 and ds.vocab_size == 64 and all(len(ds[i]) <= 15 for i in range(10))
+    dl = get_dataloader(path, 4, -1, "validation", maxlen=16, shuffle=False)
+    batch = next(iter(dl))
+    assert set(batch) == {"input_ids", "target_ids", "position_ids"} and batch["input_ids"].shape[0] == 3
+    with pytest.raises(AssertionError):
+        ShakespeareDataset(path, "test", 16)
+
+
+def test_shipped_tokenizer():
+    from tokenizers import Tokenizer
+    tok = Tokenizer.from_file(os.path.join(REPO, "tokenizer", "tokenizer.json"))
+    assert tok.get_vocab_size() == 1024
+    assert [tok.token_to_id(t) for t in ("<BOS>", "<EOS>", "<UNK>")] == [0, 1, 2]
+    assert tok.decode(tok.encode("hello world").ids).strip() == "hello world"
+
+
+def test_checkpoint_format_rotation_reshard(tmp_path):
+    import process_manager as pm
+    from distributed_pytorch_from_scratch_b200.utils import checkpoint as C
+    from models.model import Transformer
+    pm.init_pgm(1)
+    torch.manual_seed(0)
+    cfg = dict(attn_dim=64, ffn_dim=128, num_heads=4, num_layers=2, vocab_size=128, maxlen=32)
+    m = Transformer(**cfg)
+    m.reset_parameters()
+    d = str(tmp_path / "ck")
+    for step in (10, 20, 30):
+        p = C.save_checkpoint(m, d, 0, step, 2.34567, keep_last_n=2, verbose=False)
+    assert os.path.basename(p) == "tprank-0_iter-30_loss-2.3457.pth"
+    assert [os.path.basename(x) for x in C.list_checkpoints(d, 0)] == [
+        "tprank-0_iter-20_loss-2.3457.pth", "tprank-0_iter-30_loss-2.3457.pth"]
+    assert re.findall(r"tprank-\d+_iter-(\d+)_loss-.*?.pth", p) == ["30"]          # reference test.py:95 regex
+    sd = torch.load(p, weights_only=True)
+    assert isinstance(sd, dict) and len(sd) == 36 and all(v.dtype == torch.float32 for v in sd.values())
+    assert sd["layers.0.attn.wq.weight"].shape == (64, 64) and sd["layers.0.norm1.scale"].shape == (64,)
+    m2 = Transformer(**cfg)
+    m2.reset_parameters()
+    C.load_checkpoint(m2, p)
+    for (k, a), (_, b) in zip(m.state_dict().items(), m2.state_dict().items()):
+        assert torch.equal(a, b), k
+    # TP1 -> TP2 -> TP1 resharding is lossless
+    full = {k: v.clone() for k, v in sd.items()}
+    shards = C.split_full(full, 2)
+    assert shards[1]["layers.0.attn.wo.weight"].shape == (64, 32) and shards[0]["lm_head.bias"].shape == (64,)
+    merged = C.merge_shards(shards)
+    assert all(torch.equal(merged[k], full[k]) for k in full)
+    out = C.reshard_checkpoint(d, str(tmp_path / "tp2"), 30, 1, 2)
+    assert len(out) == 2 and os.path.basename(out[1]) == "tprank-1_iter-30_loss-2.3457.pth"
+
+
+def test_checkpoint_interchange_with_reference(tmp_path):
+    """Our .pth loads into the UNMODIFIED reference model and the reference's .pth loads into ours."""
+    ref = os.path.join(REPO, "baseline", "_ref")
+    if not os.path.isdir(os.path.join(ref, "models")):
+        pytest.skip("baseline/_ref not installed")
+    import subprocess
+    script = f"""
+import sys, os, torch
+sys.path = [{ref!r}] + [p for p in sys.path if os.path.abspath(p or '.') != {REPO!r}]
+import torch.distributed as dist
+os.environ['MASTER_ADDR']='127.0.0.1'; os.environ['MASTER_PORT']='{29000 + os.getpid() % 1000}'
+os.environ['DEVICE']='cpu'
+dist.init_process_group('gloo', rank=0, world_size=1)
+import process_manager as pm
+assert pm.__file__.startswith({ref!r})
+pm.init_pgm(1)
+from models.model import Transformer
+m = Transformer(64, 128, 4, 2, 128, 32)
+m.reset_parameters()
+ck = torch.load({str(tmp_path / 'ours.pth')!r}, map_location='cpu')
+m.load_state_dict(ck)            # strict: same keys and shapes
+torch.manual_seed(5); m2 = Transformer(64, 128, 4, 2, 128, 32); m2.reset_parameters()
+torch.save(m2.state_dict(), {str(tmp_path / 'theirs.pth')!r})
+ids = torch.arange(10).view(1, 10); pos = torch.arange(10).view(1, 10)
+torch.save(m2(ids.clone(), pos), {str(tmp_path / 'theirs_logits.pt')!r})
+dist.destroy_process_group()
+print('REF_OK')
+"""
+    import process_manager as pm
+    from distributed_pytorch_from_scratch_b200.utils import checkpoint as C
+    from models.model import Transformer
+    pm.init_pgm(1)
+    torch.manual_seed(1)
+    m = Transformer(64, 128, 4, 2, 128, 32)
+    m.reset_parameters()
+    p = C.save_checkpoint(m, str(tmp_path), 0, 1, 1.0, verbose=False)
+    os.replace(p, str(tmp_path / "ours.pth"))
+    r = subprocess.run([sys.executable, "-c", script], capture_output=True, text=True, cwd=str(tmp_path), timeout=300)
+    assert "REF_OK" in r.stdout, r.stderr[-2000:]
+    C.load_checkpoint(m, str(tmp_path / "theirs.pth"))
+    ids = torch.arange(10).view(1, 10)
+    theirs = torch.load(str(tmp_path / "theirs_logits.pt"))
+    assert torch.allclose(m(ids, ids.clone()), theirs, atol=1e-5)    # same weights -> same logits as the reference
+
+
+def test_fused_adam_matches_torch_adam_with_onecycle():
+    torch.manual_seed(0)
+    from distributed_pytorch_from_scratch_b200.ops.optim import FusedAdam
+    w0 = [torch.randn(7, 5), torch.randn(11)]
+    pa = [torch.nn.Parameter(w.clone()) for w in w0]
+    pb = [torch.nn.Parameter(w.clone()) for w in w0]
+    oa = FusedAdam(pa, lr=3e-4)
+    ob = torch.optim.Adam(pb, lr=3e-4)
+    sa = torch.optim.lr_scheduler.OneCycleLR(oa, 3e-4, 40, pct_start=0.25)
+    sb = torch.optim.lr_scheduler.OneCycleLR(ob, 3e-4, 40, pct_start=0.25)
+    for step in range(30):
+        for p, q in zip(pa, pb):
+            g = torch.randn_like(p)
+            p.grad, q.grad = g.clone(), g.clone()
+        oa.step(); ob.step(); sa.step(); sb.step()
+        assert oa.param_groups[0]["betas"][0] == ob.param_groups[0]["betas"][0]       # OneCycleLR cycles beta1 too
+    for p, q in zip(pa, pb):
+        assert torch.allclose(p, q, atol=1e-6, rtol=1e-5)
+
+
+def test_c_abi_header_matches_ctypes_table():
+    """Every entry point declared in include/dpfs_b200.h is bound with the right arity and exported by the .so."""
+    from distributed_pytorch_from_scratch_b200.ops import _lib
+    hdr = open(os.path.join(REPO, "include", "dpfs_b200.h")).read()
+    hdr = re.sub(r"/\*.*?\*/", "", hdr, flags=re.S)
+    decls = dict()
+    for m in re.finditer(r"\b(?:int|unsigned long long)\s+(dpfs_\w+)\s*\(([^;]*?)\)\s*;", hdr, flags=re.S):
+        args = m.group(2).strip()
+        decls[m.group(1)] = 0 if args in ("", "void") else len(args.split(","))
+    assert len(decls) >= 20
+    handle = _lib.lib()
+    for name, n in decls.items():
+        assert hasattr(handle, name), f"{name} not exported"
+        if name in _lib.SIGS:
+            assert len(_lib.SIGS[name]) == n, f"{name}: header has {n} args, ctypes table {len(_lib.SIGS[name])}"
+    for name in _lib.SIGS:
+        assert name in decls, f"{name} bound in python but not declared in the header"
