@@ -86,8 +86,12 @@ def load_resume_state(save_dir: str, rank: int, optimizer, scheduler):
         optimizer.load_fused_state(o)
     else:
         optimizer.load_state_dict(st["optimizer"])
-    if scheduler is not None and st["scheduler"] is not None:
-        scheduler.load_state_dict(st["scheduler"])
+    if scheduler is not None:
+        # fast-forward instead of load_state_dict: the resumed run may use a different --max_steps, and the saved
+        # state would overwrite the new schedule length
+        optimizer._opt_called = True
+        for _ in range(int(st["step"])):
+            scheduler.step()
     torch.set_rng_state(st["rng_cpu"])
     if st["rng_cuda"] is not None and torch.cuda.is_available():
         torch.cuda.set_rng_state(st["rng_cuda"])
