@@ -4,6 +4,10 @@
 #include "common.cuh"
 #include "dpfs_b200.h"
 
+#include <stdio.h>
+
+#include <mutex>
+
 namespace dpfs {
 
 // --------------------------------------------------------------------------------------------- helpers
@@ -704,5 +708,72 @@ extern "C" int dpfs_cast_f32_to_bf16(const float* x, void* y, long long n, cudaS
   if (n % 4 != 0) return -24;
   if (n <= 0) return 0;
   cast_f32_to_bf16_kernel<<<(DPFS_COUNT(), ew_grid(n / 4, 256)), 256, 0, stream>>>(x, (__nv_bfloat16*)y, n / 4);
+  return static_cast<int>(cudaGetLastError());
+}
+
+// ------------------------------------------------------------------------------------- allocation-free column sum
+// Some hosts of this library cannot give it scratch memory: a serving process whose own allocator already owns the
+// whole GPU (any cudaMalloc may fail, and it synchronises the device), or a plain C / embedded caller that has no
+// device allocator at all and only holds the input and output buffers it was handed.  For them the two-stage column
+// sum is also offered with its partial-sum scratch living in a fixed array inside the library image.
+//
+// The array costs DPFS_COLSUM_STATIC_MAX_FLOATS * 4 bytes (8 MiB) on EVERY GPU that loads libdpfs_b200.so, for the
+// life of the process, whether or not this entry point is ever called.
+static __device__ __align__(256) float g_colsum_static_scratch[DPFS_COLSUM_STATIC_MAX_FLOATS];
+
+namespace {
+constexpr int kMaxDevices = 64;
+float* g_static_scratch_ptr[kMaxDevices] = {nullptr};
+std::mutex g_static_scratch_mutex;
+
+// In host code `g_colsum_static_scratch` is only a stand-in for the symbol, NOT a device address, so it must never be
+// handed to a kernel.  Resolve the real address once per device (with that device current) and cache it.
+int static_scratch_for_current_device(float** out) {
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return static_cast<int>(e);
+  if (dev < 0 || dev >= kMaxDevices) return -26;
+  std::lock_guard<std::mutex> lock(g_static_scratch_mutex);
+  if (g_static_scratch_ptr[dev] == nullptr) {
+    void* p = nullptr;
+    e = cudaGetSymbolAddress(&p, g_colsum_static_scratch);
+    if (e != cudaSuccess) return static_cast<int>(e);
+    if (p == nullptr) return -27;
+    g_static_scratch_ptr[dev] = static_cast<float*>(p);
+  }
+  *out = g_static_scratch_ptr[dev];
+  return 0;
+}
+}  // namespace
+
+// Same result as dpfs_colsum_bf16 (same kernels, same summation order) without any caller-provided scratch and
+// without allocating: no cudaMalloc / cudaFree / allocating library call happens here.
+//   * Size limit: ceil(M / 64) * N <= DPFS_COLSUM_STATIC_MAX_FLOATS, otherwise -25 is returned and nothing runs.
+//   * The first call on each device looks up the scratch address (cudaGetSymbolAddress); make that first call
+//     before starting any stream capture on that device.
+//   * All calls share the one array and it keeps whatever the previous call left in it.  Nothing has to be cleared:
+//     stage 1 overwrites every slot that stage 2 reads.  For the same reason two calls that may run on the GPU at the
+//     same time (different streams, no ordering between them) race on the array — serialise them.
+extern "C" int dpfs_colsum_bf16_static(const void* x, long long ld, float* out, int accumulate, int M, int N,
+                                       cudaStream_t stream) {
+  if (N % 8 != 0 || ld % 8 != 0) return -23;
+  if (M <= 0) return 0;
+  const long long strips = (static_cast<long long>(M) + kColsumRowsPerBlock - 1) / kColsumRowsPerBlock;
+  if (strips * N > static_cast<long long>(DPFS_COLSUM_STATIC_MAX_FLOATS)) {
+    fprintf(stderr,
+            "dpfs_colsum_bf16_static: M=%d N=%d needs %lld scratch floats but the built-in scratch holds %d; "
+            "use dpfs_colsum_bf16 with caller-provided scratch\n",
+            M, N, strips * N, DPFS_COLSUM_STATIC_MAX_FLOATS);
+    return -25;
+  }
+  float* scratch = nullptr;
+  const int rc = static_scratch_for_current_device(&scratch);
+  if (rc != 0) return rc;
+  dim3 grid((N / 8 + 127) / 128, static_cast<unsigned>(strips));
+  colsum_partial_kernel<<<(DPFS_COUNT(), grid), 128, 0, stream>>>((const __nv_bfloat16*)x, ld, scratch, M, N);
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return static_cast<int>(e);
+  reduce_partials_kernel<<<(DPFS_COUNT(), (N + 255) / 256), 256, 0, stream>>>(scratch, out, static_cast<int>(strips),
+                                                                             N, accumulate);
   return static_cast<int>(cudaGetLastError());
 }

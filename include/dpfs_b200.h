@@ -83,6 +83,21 @@ int dpfs_colsum_bf16(const void* x, long long ld, float* out, int accumulate, fl
                      cudaStream_t stream);
 int dpfs_cast_f32_to_bf16(const float* x, void* y, long long n, cudaStream_t stream);
 
+/* Column sum for callers that cannot allocate device memory and have no scratch buffer to lend: a host process whose
+ * own allocator already owns the whole GPU (so a cudaMalloc may fail, and would stall the device), or a plain C /
+ * embedded host with no device allocator at all.  Same result as dpfs_colsum_bf16, but the partial sums go through a
+ * fixed array that is part of the library image, so nothing is allocated (no cudaMalloc / cudaFree / allocating
+ * library call).  This entry point has no counterpart in the reference.
+ *   - Limit: ceil(M / 64) * N <= DPFS_COLSUM_STATIC_MAX_FLOATS; larger problems return -25 and launch nothing.
+ *   - Cost: the array (8 MiB) is resident on every GPU that loads the library until the process exits.
+ *   - The first call on a device resolves the array's device address; make that first call before any stream
+ *     capture on that device.
+ *   - Every call shares the array and it keeps the previous call's contents (nothing needs clearing: each slot is
+ *     written before it is read).  Calls that can overlap on the GPU race on it; keep them ordered. */
+#define DPFS_COLSUM_STATIC_MAX_FLOATS (2 * 1024 * 1024)
+int dpfs_colsum_bf16_static(const void* x, long long ld, float* out, int accumulate, int M, int N,
+                            cudaStream_t stream);
+
 /* ---- Vocab-parallel embedding -----------------------------------------------------------------------------------
  * out[m] = weight[ids[m] - vocab_start] for owned ids, 0 otherwise (ids are never modified).
  * ref: ParallelVocabularyEmbedding.forward, models/layers.py:134-141. */
