@@ -145,6 +145,11 @@ def timed(fn_step, steps: int, warmup: int, world: int, sampler):
     return ms / steps, t0, t1
 
 
+def dbg(msg):
+    if os.environ.get("DPFS_DEBUG"):
+        print(f"[bench rank {os.environ.get('RANK', '0')}] {msg}", file=sys.stderr, flush=True)
+
+
 def emit(rank, payload):
     if rank == 0:
         print(json.dumps(payload), flush=True)
@@ -186,6 +191,7 @@ def run_ours(args):
     opt._opt_called = True
     step = TrainStep(model, opt, sched, ignore_index=IGNORE_INDEX, use_graph=not args.no_graph)
     ids_h, pos_h, tgt_h = make_batch(margs.vocab_size)
+    dbg("model built")
 
     # ---- device-timed steps (inputs already resident in the static buffers)
     shape, bufs = step.load_batch(ids_h, pos_h, tgt_h)
@@ -198,6 +204,7 @@ def run_ours(args):
 
     def dev_step():
         last["loss"] = step.run_loaded(shape, bufs)
+        dbg("step done")
 
     ms_step, t0, t1 = timed(dev_step, args.steps, args.warmup, world, sampler)
     clocks = sampler.stop(t0, t1) if sampler else None

@@ -95,6 +95,66 @@ __global__ void __launch_bounds__(kNormThreads) rmsnorm_fwd_kernel(const XT* __r
   }
 }
 
+
+// --------------------------------------------------------------------------------------------- residual + RMSNorm
+// x_out = x + y + bias (fp32 residual stream), h = rmsnorm(x_out) * scale (bf16).  `y` is the all-reduced bf16 output
+// of a row-parallel GEMM (reference models/layers.py:51-54 followed by models/model.py:119-120): the residual add,
+// the replicated bias and the next layer's norm become one pass.  h / scale may be null (residual add only).
+template <int NV>
+__global__ void __launch_bounds__(kNormThreads) add_rmsnorm_fwd_kernel(
+    const float* __restrict__ x, const __nv_bfloat16* __restrict__ y, const float* __restrict__ bias,
+    const float* __restrict__ scale, float* __restrict__ x_out, __nv_bfloat16* __restrict__ h,
+    float* __restrict__ rstd_out, int M, int D, float eps) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int wpb = kNormThreads / 32;
+  float sc[NV][4], bs[NV][4];
+#pragma unroll
+  for (int i = 0; i < NV; ++i) {
+    const int c = (i * 32 + lane) * 4;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) sc[i][j] = bs[i][j] = 0.f;
+    if (c < D) {
+      if (scale) load4<float>(scale + c, sc[i]);
+      if (bias) load4<float>(bias + c, bs[i]);
+    }
+  }
+  for (int row = blockIdx.x * wpb + warp; row < M; row += gridDim.x * wpb) {
+    const long long off = static_cast<long long>(row) * D;
+    float v[NV][4];
+    float ss = 0.f;
+#pragma unroll
+    for (int i = 0; i < NV; ++i) {
+      const int c = (i * 32 + lane) * 4;
+      if (c < D) {
+        float a[4], b[4];
+        load4<float>(x + off + c, a);
+        load4<__nv_bfloat16>(y + off + c, b);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          v[i][j] = a[j] + b[j] + bs[i][j];
+          ss += v[i][j] * v[i][j];
+        }
+        store4<float>(x_out + off + c, v[i]);
+      }
+    }
+    if (h) {
+      ss = warp_sum(ss);
+      const float rstd = rsqrtf(ss / D + eps);
+      if (lane == 0 && rstd_out) rstd_out[row] = rstd;
+#pragma unroll
+      for (int i = 0; i < NV; ++i) {
+        const int c = (i * 32 + lane) * 4;
+        if (c < D) {
+          float o[4];
+#pragma unroll
+          for (int j = 0; j < 4; ++j) o[j] = v[i][j] * rstd * sc[i][j];
+          store4<__nv_bfloat16>(h + off + c, o);
+        }
+      }
+    }
+  }
+}
+
 // --------------------------------------------------------------------------------------------- RMSNorm bwd
 // dx = dres + rstd * (g - xhat * mean(g * xhat)),  g = dy * scale, xhat = x * rstd;  dscale = sum_rows dy * xhat.
 // Each block writes one row of per-block dscale partials into `scratch` [gridDim.x][D]; a second kernel sums them
@@ -556,6 +616,20 @@ extern "C" int dpfs_rmsnorm_fwd(const void* x, int x_bf16, const float* scale, v
     else
       rmsnorm_fwd_kernel<float, float, NV><<<(DPFS_COUNT(), grid), kNormThreads, 0, stream>>>((const float*)x, scale, (float*)y,
                                                                               rstd, M, D, eps);
+  });
+  return static_cast<int>(cudaGetLastError());
+}
+
+
+extern "C" int dpfs_add_rmsnorm_fwd(const float* x, const void* y_bf16, const float* bias, const float* scale,
+                                    float* x_out, void* h_bf16, float* rstd, int M, int D, float eps,
+                                    cudaStream_t stream) {
+  if (D % 4 != 0 || D > 128 * kMaxNV) return -20;
+  if (M <= 0) return 0;
+  const int grid = norm_grid(M);
+  DISPATCH_NV(D, {
+    add_rmsnorm_fwd_kernel<NV><<<(DPFS_COUNT(), grid), kNormThreads, 0, stream>>>(
+        x, (const __nv_bfloat16*)y_bf16, bias, scale, x_out, (__nv_bfloat16*)h_bf16, rstd, M, D, eps);
   });
   return static_cast<int>(cudaGetLastError());
 }

@@ -10,7 +10,7 @@
 //   wgrad    dW = dy^T x : A = dy (MN-major), B = x  (MN-major), reduction over tokens, split-K over the SMs
 //
 // Replaces the cuBLAS calls behind F.linear in the reference (models/layers.py:49,93 and their autograd).
-#include "common.cuh"
+#include "comm.cuh"
 #include "dpfs_b200.h"
 
 #include <cudaTypedefs.h>
@@ -34,6 +34,9 @@ struct GemmArgs {
   const float* bias;       // [N] or nullptr
   const float* residual;   // fp32 [M][ldr] or nullptr
   long long ldr;
+  // fused all-reduce (FUSE_AR kernels only): `out` is this rank's symmetric buffer, `mc_out` its multicast alias
+  uint8_t* mc_out;
+  CommCtx comm;
 };
 
 template <int BN>
@@ -75,7 +78,12 @@ __device__ __forceinline__ void store_chunk32<__nv_bfloat16>(__nv_bfloat16* dst,
   }
 }
 
-template <int BN, bool A_MN, bool B_MN, typename OutT>
+// FUSE_AR: GEMM -> all-reduce in ONE kernel.  Each CTA writes the bf16 partial tiles it computes into this rank's
+// symmetric buffer and raises a per-tile flag on the tile's owner rank (tile row-block m_blk belongs to rank
+// m_blk % n).  When its GEMM tiles are done, the CTA turns to the tiles its rank owns: as soon as all n partials of a
+// tile are flagged, it pulls their sum through the NVSwitch (multimem.ld_reduce) and broadcasts the result into every
+// rank's buffer (multimem.st).  A closing rank-wide barrier makes the full result visible before the kernel exits.
+template <int BN, bool A_MN, bool B_MN, typename OutT, bool FUSE_AR = false>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                  const GemmArgs args) {
@@ -257,11 +265,44 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         as = 0;
         aphase ^= 1;
       }
+      if constexpr (FUSE_AR) {
+        // all 128 epilogue threads have stored their rows of the partial tile -> tell the owner rank
+        asm volatile("bar.sync 1, 128;" ::: "memory");
+        if (threadIdx.x == 64) {
+          const int m_blk = t / tiles_n;
+          const int owner = m_blk % args.comm.n;
+          __threadfence_system();
+          put_signal(args.comm.flags[owner] + (kMaxBlocks + t) * kMaxRanks + args.comm.rank);
+        }
+      }
+    }
+    if constexpr (FUSE_AR) {
+      // ---------------------------------------------------------------- reduce phase: tiles owned by this rank
+      const int et = threadIdx.x - 64;  // 0..127
+      const int n = args.comm.n, rank = args.comm.rank;
+      int k = 0;
+      for (int m_blk = rank; m_blk < tiles_m; m_blk += n) {
+        for (int n_blk = 0; n_blk < tiles_n; ++n_blk, ++k) {
+          if (k % static_cast<int>(gridDim.x) != static_cast<int>(blockIdx.x)) continue;
+          const int t = m_blk * tiles_n + n_blk;
+          if (et < n) wait_signal(args.comm.flags[rank] + (kMaxBlocks + t) * kMaxRanks + et);
+          asm volatile("bar.sync 1, 128;" ::: "memory");
+          const int m0 = m_blk * BM, n0 = n_blk * BN;
+          const int rows = min(BM, args.M - m0);
+          const int cpr = min(BN, args.N - n0) / 8;  // 16-byte chunks per row
+          for (int idx = et; idx < rows * cpr; idx += 128) {
+            const int r = idx / cpr, cc = idx - r * cpr;
+            uint8_t* p = args.mc_out + (static_cast<long long>(m0 + r) * args.ldo + n0 + cc * 8) * 2;
+            multimem_st_16B(p, multimem_ld_reduce_bf16x8(p));
+          }
+        }
+      }
     }
   }
 
   tc_fence_before();
   __syncthreads();
+  if constexpr (FUSE_AR) sync_ranks(args.comm, blockIdx.x);
   if (warp == 1) {
     tc_fence_after();
     tmem_dealloc(tmem_base, 2 * BN);
@@ -363,6 +404,24 @@ static int launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const Gem
   return static_cast<int>(cudaGetLastError());
 }
 
+template <int BN, bool B_MN>
+static int launch_gemm_ar(const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmArgs& args, cudaStream_t stream) {
+  using S = GemmSmem<BN>;
+  auto kfn = gemm_bf16_kernel<BN, false, B_MN, __nv_bfloat16, true>;
+  static bool configured = false;
+  if (!configured) {
+    cudaError_t e = cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, S::kTotal);
+    if (e != cudaSuccess) return static_cast<int>(e);
+    configured = true;
+  }
+  const int tiles = ((args.M + BM - 1) / BM) * ((args.N + BN - 1) / BN);
+  if (tiles > kMaxTiles) return -52;
+  int grid = tiles < num_sms() ? tiles : num_sms();
+  if (grid > kMaxBlocks) grid = kMaxBlocks;
+  kfn<<<(DPFS_COUNT(), grid), kGemmThreads, S::kTotal, stream>>>(tmA, tmB, args);
+  return static_cast<int>(cudaGetLastError());
+}
+
 template <int BN, typename OutT>
 static int dispatch_major(bool a_mn, bool b_mn, const CUtensorMap& tmA, const CUtensorMap& tmB,
                           const GemmArgs& args, cudaStream_t stream) {
@@ -404,6 +463,10 @@ extern "C" int dpfs_gemm_bf16(const void* A, long long lda, int a_mn_major, cons
   if (rc) return rc;
 
   GemmArgs args;
+  args.mc_out = nullptr;
+  args.comm.rank = 0;
+  args.comm.n = 1;
+  for (int i = 0; i < kMaxRanks; ++i) args.comm.flags[i] = nullptr;
   args.M = M;
   args.N = N;
   args.K = K;
@@ -450,3 +513,44 @@ extern "C" int dpfs_gemm_bf16(const void* A, long long lda, int a_mn_major, cons
 }
 
 extern "C" unsigned long long dpfs_launch_count(void) { return dpfs::g_launches; }
+
+// Fused GEMM -> all-reduce: out (bf16 [M][N], row stride N) must be this rank's symmetric buffer and mc_out the
+// multicast alias of the same offset; on return every rank's `out` holds sum_r A_r B_r^T.
+extern "C" int dpfs_gemm_allreduce_bf16(const void* A, long long lda, const void* B, long long ldb, int b_mn_major,
+                                        void* out, void* mc_out, int M, int N, int K,
+                                        const unsigned long long* flag_ptrs, int rank, int n, int bn,
+                                        cudaStream_t stream) {
+  if (M <= 0 || N <= 0 || K <= 0) return 0;
+  if (n < 2 || n > kMaxRanks) return -50;
+  if ((N % 8) != 0 || (lda % 8) != 0 || (ldb % 8) != 0) return -10;
+  if (bn != 256) bn = 128;
+  CUtensorMap tmA, tmB;
+  int rc = make_tmap_bf16_2d(&tmA, A, K, M, lda, 64, BM);
+  if (rc) return rc;
+  if (!b_mn_major)
+    rc = make_tmap_bf16_2d(&tmB, B, K, N, ldb, 64, bn);
+  else
+    rc = make_tmap_bf16_2d(&tmB, B, N, K, ldb, 64, BK);
+  if (rc) return rc;
+  GemmArgs args;
+  args.M = M;
+  args.N = N;
+  args.K = K;
+  args.splits = 1;
+  args.kb_per_split = (K + BK - 1) / BK;
+  args.out = out;
+  args.ldo = N;
+  args.split_stride = 0;
+  args.bias = nullptr;
+  args.residual = nullptr;
+  args.ldr = 0;
+  args.mc_out = static_cast<uint8_t*>(mc_out);
+  for (int i = 0; i < kMaxRanks; ++i) args.comm.flags[i] = i < n ? reinterpret_cast<uint32_t*>(flag_ptrs[i]) : nullptr;
+  args.comm.rank = rank;
+  args.comm.n = n;
+  if (bn == 256)
+    return b_mn_major ? launch_gemm_ar<256, true>(tmA, tmB, args, stream)
+                      : launch_gemm_ar<256, false>(tmA, tmB, args, stream);
+  return b_mn_major ? launch_gemm_ar<128, true>(tmA, tmB, args, stream)
+                    : launch_gemm_ar<128, false>(tmA, tmB, args, stream);
+}

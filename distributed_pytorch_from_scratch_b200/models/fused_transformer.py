@@ -160,22 +160,26 @@ class Meta:
 
 
 # ================================================================================================ building blocks
-def _rowpar_residual(a_bf16, w_bf16, bias, residual):
-    """x_out = residual + all_reduce(a @ W^T) + bias  (row-parallel linear folded into the residual stream)."""
+def _rowpar_residual(a_bf16, w_bf16, bias, residual, norm_scale=None, eps=1e-5):
+    """x_out = residual + all_reduce(a @ W^T) + bias  (row-parallel linear folded into the residual stream) and,
+    when ``norm_scale`` is given, h = rmsnorm(x_out) for the next sub-block.  Returns (x_out, h | None, rstd | None).
+
+    TP=1: residual + bias ride in the GEMM epilogue.  TP>1: ONE kernel does GEMM + all-reduce over NVLink (tiles are
+    summed through the NVSwitch as they complete), then residual + bias + norm are one fused pass."""
     n = pm.pgm.tp_size
     if n == 1:
-        return gemm_nt(a_bf16, w_bf16, bias=bias, residual=residual, out_dtype=F32)
+        x_out = gemm_nt(a_bf16, w_bf16, bias=bias, residual=residual, out_dtype=F32)
+        if norm_scale is None:
+            return x_out, None, None
+        h, rstd = fused.rmsnorm_fwd(x_out, norm_scale, eps)
+        return x_out, h, rstd
     symm = pm.pgm.symm
     if symm is not None and symm.can_fuse_gemm_ar(a_bf16, w_bf16):
-        return symm.gemm_allreduce_residual(a_bf16, w_bf16, bias, residual)
-    part = gemm_nt(a_bf16, w_bf16, out_dtype=BF16)
-    comm_ops.all_reduce_sum_(part)
-    return fused_residual_bias(part, bias, residual)
-
-
-def fused_residual_bias(part_bf16, bias, residual):
-    # TODO(perf): single kernel; torch ops are only used on the NCCL fallback path
-    return residual + part_bf16.float() + bias
+        y = symm.gemm_allreduce(a_bf16, w_bf16)
+    else:
+        y = gemm_nt(a_bf16, w_bf16, out_dtype=BF16)
+        comm_ops.all_reduce_sum_(y)
+    return fused.add_rmsnorm_fwd(residual, y, bias, norm_scale, eps, want_norm=norm_scale is not None)
 
 
 def _colpar_dgrad(dy_bf16, w_bf16):
@@ -203,11 +207,10 @@ class FusedLayerFn(torch.autograd.Function):
         qkv = gemm_nt(h1, pack.wqkv, bias=pack.bqkv, out_dtype=BF16)
         fused.rope_inplace(qkv, pos, rt.cos_half, rt.sin_half, 2, m.Dl, m.Hl, m.hd, inverse=False)
         attn, lse = attn_fwd(qkv, m.B, m.T, m.Hl, m.hd, m.scale)
-        x2 = _rowpar_residual(attn, pack.wo, pack.bo, x)
-        h2, rstd2 = fused.rmsnorm_fwd(x2, pack.s2, rt.eps)
+        x2, h2, rstd2 = _rowpar_residual(attn, pack.wo, pack.bo, x, pack.s2, rt.eps)
         gu = gemm_nt(h2, pack.wgu, bias=pack.bgu, out_dtype=BF16)
         act = fused.swiglu_fwd(gu)
-        x3 = _rowpar_residual(act, pack.wd, pack.bd, x2)
+        x3, _, _ = _rowpar_residual(act, pack.wd, pack.bd, x2)
         ctx.save_for_backward(x, pos, h1, rstd1, qkv, attn, lse, x2, h2, rstd2, gu, act)
         ctx.pack, ctx.meta, ctx.rt = pack, meta, rt
         return x3
@@ -248,8 +251,21 @@ class FusedEmbedFn(torch.autograd.Function):
     @staticmethod
     def forward(ctx, ids_flat, rt, weight):
         emb = rt.model.embedding
-        out = fused.embedding_fwd(ids_flat, weight.detach(), emb.vocab_st_idx, emb.vocab_ed_idx, out_dtype=F32)
-        comm_ops.all_reduce_sum_(out)
+        if pm.pgm.tp_size == 1:
+            out = fused.embedding_fwd(ids_flat, weight.detach(), emb.vocab_st_idx, emb.vocab_ed_idx, out_dtype=F32)
+        else:
+            # exactly one rank owns each row, so summing bf16 rows is exact; the reference also casts the embedding
+            # output to bf16 before the first layer (models/model.py:153-154)
+            symm = pm.pgm.symm
+            D = weight.shape[1]
+            if symm is not None and ids_flat.numel() * D * 2 <= symm.gather_off:
+                part = symm.buffer((ids_flat.numel(), D), BF16)
+                fused.embedding_fwd(ids_flat, weight.detach(), emb.vocab_st_idx, emb.vocab_ed_idx, out=part)
+                out = symm.all_reduce(part, out=part).float()
+            else:
+                part = fused.embedding_fwd(ids_flat, weight.detach(), emb.vocab_st_idx, emb.vocab_ed_idx,
+                                           out_dtype=BF16)
+                out = comm_ops.all_reduce_sum_(part).float()
         ctx.save_for_backward(ids_flat)
         ctx.rt = rt
         return out
@@ -276,7 +292,11 @@ class FusedHeadLossFn(torch.autograd.Function):
         h, rstd = fused.rmsnorm_fwd(x, rt.sN, rt.eps)
         logits = gemm_nt(h, rt.wlm, bias=rt.blm, out_dtype=F32)
         stats, loss_acc = fused.ce_stats(logits, targets_flat, vocab_start, ignore_index)
-        all_stats = comm_ops.all_gather_rows(stats) if n > 1 else stats
+        if n > 1:
+            symm = pm.pgm.symm
+            all_stats = symm.all_gather_rows(stats) if symm is not None else comm_ops.all_gather_rows(stats)
+        else:
+            all_stats = stats
         fused.ce_loss(targets_flat, all_stats, n, loss_acc, ignore_index)
         loss = loss_acc[0] / loss_acc[1]
         ctx.save_for_backward(x, targets_flat, h, rstd, logits, all_stats, loss_acc)

@@ -25,6 +25,14 @@ c_p = ctypes.c_void_p
 SIGS = {
     "dpfs_gemm_bf16": (c_p, c_ll, c_int, c_p, c_ll, c_int, c_p, c_ll, c_int, c_p, c_p, c_ll, c_int, c_int, c_int,
                        c_int, c_p, c_int, c_p),
+    "dpfs_gemm_allreduce_bf16": (c_p, c_ll, c_p, c_ll, c_int, c_p, c_p, c_int, c_int, c_int, c_p, c_int, c_int,
+                                 c_int, c_p),
+    "dpfs_comm_flag_words": (),
+    "dpfs_allreduce_nvls": (c_p, c_ll, c_int, c_p, c_int, c_int, c_p),
+    "dpfs_allgather_nvls": (c_p, c_p, c_ll, c_p, c_int, c_int, c_p),
+    "dpfs_comm_barrier": (c_p, c_int, c_int, c_p),
+    "dpfs_launch_count": (),
+    "dpfs_add_rmsnorm_fwd": (c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_int, c_int, c_f, c_p),
     "dpfs_norm_bwd_blocks": (c_int,),
     "dpfs_rmsnorm_fwd": (c_p, c_int, c_p, c_p, c_int, c_p, c_int, c_int, c_f, c_p),
     "dpfs_rmsnorm_bwd": (c_p, c_int, c_p, c_int, c_p, c_p, c_p, c_p, c_p, c_p, c_int, c_p, c_int, c_int, c_p),
@@ -55,7 +63,7 @@ def _declare(handle):
         if hasattr(handle, name):
             fn = getattr(handle, name)
             fn.argtypes = list(argtypes)
-            fn.restype = c_int
+            fn.restype = ctypes.c_ulonglong if name == "dpfs_launch_count" else c_int
 
 
 def available() -> bool:

@@ -47,6 +47,22 @@ def rmsnorm_fwd(x: torch.Tensor, scale: torch.Tensor, eps: float, out_dtype=BF16
     return y.view(x.shape), rstd
 
 
+def add_rmsnorm_fwd(x: torch.Tensor, y: torch.Tensor, bias: Optional[torch.Tensor], scale: Optional[torch.Tensor],
+                    eps: float, want_norm: bool = True):
+    """x_out = x + y + bias (fp32); h = rmsnorm(x_out) * scale (bf16).  x fp32 [M, D], y bf16 [M, D] (the all-reduced
+    row-parallel GEMM output).  Returns (x_out, h | None, rstd | None)."""
+    M, D = x.shape
+    assert x.dtype == F32 and y.dtype == BF16 and x.is_contiguous() and y.is_contiguous() and y.shape == x.shape
+    x_out = torch.empty_like(x)
+    h = torch.empty((M, D), dtype=BF16, device=x.device) if want_norm else None
+    rstd = torch.empty(M, dtype=F32, device=x.device) if want_norm else None
+    rc = _lib.lib().dpfs_add_rmsnorm_fwd(x.data_ptr(), y.data_ptr(), _lib.ptr(bias),
+                                         _lib.ptr(scale) if want_norm else 0, x_out.data_ptr(), _lib.ptr(h),
+                                         _lib.ptr(rstd), M, D, eps, _lib.stream())
+    _lib.check(rc, "dpfs_add_rmsnorm_fwd")
+    return x_out, h, rstd
+
+
 def rmsnorm_bwd(dy: torch.Tensor, x: torch.Tensor, rstd: torch.Tensor, scale: torch.Tensor,
                 dres: Optional[torch.Tensor] = None, want_fp32: bool = True, want_bf16: bool = False,
                 dscale_out: Optional[torch.Tensor] = None, accumulate: bool = False):
@@ -177,11 +193,14 @@ def cast_to_bf16(x: torch.Tensor, out: Optional[torch.Tensor] = None) -> torch.T
 
 
 # ------------------------------------------------------------------------------------------------ embedding
-def embedding_fwd(ids: torch.Tensor, weight: torch.Tensor, vocab_start: int, vocab_end: int, out_dtype=F32):
+def embedding_fwd(ids: torch.Tensor, weight: torch.Tensor, vocab_start: int, vocab_end: int, out_dtype=F32,
+                  out: Optional[torch.Tensor] = None):
     assert ids.dtype == torch.int64 and weight.dtype == F32 and weight.is_contiguous()
     ids_flat = ids.reshape(-1).contiguous()
     M, D = ids_flat.numel(), weight.shape[1]
-    out = torch.empty((M, D), dtype=out_dtype, device=weight.device)
+    if out is None:
+        out = torch.empty((M, D), dtype=out_dtype, device=weight.device)
+    assert out.shape == (M, D) and out.is_contiguous()
     rc = _lib.lib().dpfs_embedding_fwd(ids_flat.data_ptr(), weight.data_ptr(), out.data_ptr(), _is_bf16(out), M, D,
                                        vocab_start, vocab_end, _lib.stream())
     _lib.check(rc, "dpfs_embedding_fwd")

@@ -1,0 +1,144 @@
+"""Symmetric-memory communicator: NVLink peer / NVLS multicast buffers + the kernels that use them.
+
+torch.distributed._symmetric_memory is used ONLY to allocate and exchange the buffers (rendezvous over the existing
+process group: peer pointers + one multicast address through the NVSwitch); all data movement is done by our own
+kernels (csrc/comm.cu, the FUSE_AR variant in csrc/gemm_tcgen05.cu):
+
+    all_reduce(t)                      two-shot NVLS all-reduce (multimem.ld_reduce + multimem.st), in place when ``t``
+                                       already lives in the symmetric buffer, staged through it otherwise
+    all_gather_rows(t)                 multimem.st broadcast of each rank's block
+    gemm_allreduce(a, w, b_mn_major)   ONE kernel: tcgen05 GEMM whose tiles are reduced across ranks through the
+                                       switch as they complete (RowParallelLinear fwd, ColumnParallelLinear dgrad)
+
+Synchronisation uses binary semaphores in a peer-mapped flag buffer (no epochs -> safe under CUDA-graph replay).
+All ranks must issue the same sequence of collectives (SPMD), on one stream.
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+from typing import Optional
+
+import torch
+import torch.distributed as dist
+
+from ..ops import _lib
+from . import process_manager as pm
+
+BF16, F32 = torch.bfloat16, torch.float32
+
+
+class SymmComm:
+    def __init__(self, data, data_hdl, flags, flags_hdl, rank, n):
+        self.data, self.hdl = data, data_hdl
+        self.flags, self.flags_hdl = flags, flags_hdl
+        self.rank, self.n = rank, n
+        self.base = data.data_ptr()
+        self.capacity = data.numel()
+        self.mc_base = int(data_hdl.multicast_ptr)
+        self.flag_ptrs = (ctypes.c_ulonglong * 8)(*([int(p) for p in flags_hdl.buffer_ptrs] + [0] * (8 - n)))
+        self.gather_off = self.capacity - self.capacity // 8        # last 1/8th: all-gather landing zone
+        self.closed = False
+
+    # ------------------------------------------------------------------------------------------ construction
+    @classmethod
+    def create(cls, data_bytes: Optional[int] = None) -> "SymmComm":
+        import torch.distributed._symmetric_memory as symm_mem
+        n, rank, group = pm.pgm.tp_size, pm.pgm.tp_rank, pm.pgm.tp_group
+        assert n > 1 and dist.get_backend(group) == "nccl"
+        dev = torch.device("cuda", torch.cuda.current_device())
+        if data_bytes is None:
+            data_bytes = int(os.environ.get("DPFS_SYMM_MB", "512")) << 20
+        name = group.group_name
+        try:
+            symm_mem.enable_symm_mem_for_group(name)
+        except Exception:  # noqa: BLE001  (not needed / deprecated on newer torch)
+            pass
+        data = symm_mem.empty(data_bytes, dtype=torch.uint8, device=dev)
+        hdl = symm_mem.rendezvous(data, name)
+        if not getattr(hdl, "multicast_ptr", 0):
+            raise RuntimeError("NVLS multicast is not available for this process group")
+        words = _lib.lib().dpfs_comm_flag_words()
+        flags = symm_mem.empty(words, dtype=torch.int32, device=dev)
+        flags.zero_()
+        fh = symm_mem.rendezvous(flags, name)
+        torch.cuda.synchronize()
+        dist.barrier(group=group)
+        return cls(data, hdl, flags, fh, rank, n)
+
+    def close(self):
+        self.closed = True
+
+    # ------------------------------------------------------------------------------------------ buffers
+    def buffer(self, shape, dtype, offset_bytes: int = 0) -> torch.Tensor:
+        """A tensor view into this rank's symmetric buffer (producers write collective inputs here directly)."""
+        numel = 1
+        for s in shape:
+            numel *= s
+        nbytes = numel * torch.empty((), dtype=dtype).element_size()
+        assert offset_bytes % 256 == 0 and offset_bytes + nbytes <= self.gather_off, "symmetric buffer too small"
+        return self.data[offset_bytes:offset_bytes + nbytes].view(dtype).view(*shape)
+
+    def _inside(self, t: torch.Tensor) -> bool:
+        p = t.data_ptr()
+        return self.base <= p and p + t.numel() * t.element_size() <= self.base + self.capacity
+
+    def supports(self, t: torch.Tensor) -> bool:
+        nbytes = t.numel() * t.element_size()
+        return (not self.closed and t.is_cuda and t.dtype in (BF16, F32) and nbytes % 16 == 0
+                and nbytes <= self.gather_off and t.is_contiguous())
+
+    # ------------------------------------------------------------------------------------------ collectives
+    def all_reduce(self, t: torch.Tensor, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+        nbytes = t.numel() * t.element_size()
+        if self._inside(t):
+            work = t
+        else:
+            work = self.buffer(t.shape, t.dtype)
+            work.copy_(t)
+        mc = self.mc_base + (work.data_ptr() - self.base)
+        rc = _lib.lib().dpfs_allreduce_nvls(mc, nbytes, int(t.dtype == BF16), self.flag_ptrs, self.rank, self.n,
+                                            _lib.stream())
+        _lib.check(rc, "dpfs_allreduce_nvls")
+        if out is None:
+            return work if work is t else work.clone()
+        if out.data_ptr() != work.data_ptr():
+            out.copy_(work)
+        return out
+
+    def all_gather_rows(self, t: torch.Tensor) -> torch.Tensor:
+        """(...) -> (n, ...), rank order; the result is a private copy."""
+        t = t.contiguous()
+        nbytes = t.numel() * t.element_size()
+        pad = (-nbytes) % 16
+        assert pad == 0 and nbytes * self.n <= self.capacity - self.gather_off
+        mc = self.mc_base + self.gather_off
+        rc = _lib.lib().dpfs_allgather_nvls(t.data_ptr(), mc, nbytes, self.flag_ptrs, self.rank, self.n,
+                                            _lib.stream())
+        _lib.check(rc, "dpfs_allgather_nvls")
+        view = self.data[self.gather_off:self.gather_off + nbytes * self.n].view(t.dtype).view((self.n,) + t.shape)
+        return view.clone()
+
+    def can_fuse_gemm_ar(self, a: torch.Tensor, w: torch.Tensor, b_mn_major: bool = False) -> bool:
+        if self.closed or a.dtype != BF16 or w.dtype != BF16:
+            return False
+        M = a.shape[0]
+        N = w.shape[1] if b_mn_major else w.shape[0]
+        tiles = ((M + 127) // 128) * ((N + 127) // 128)
+        return N % 8 == 0 and M * N * 2 <= self.gather_off and tiles <= 16384
+
+    def gemm_allreduce(self, a: torch.Tensor, w: torch.Tensor, b_mn_major: bool = False, bn: int = 0) -> torch.Tensor:
+        """all_reduce(a @ w^T) (or a @ w when ``b_mn_major``) in ONE kernel; the result is a view of the symmetric
+        buffer, valid until the next collective — consume it right away."""
+        M, K = a.shape
+        N = w.shape[1] if b_mn_major else w.shape[0]
+        out = self.buffer((M, N), BF16)
+        mc = self.mc_base + (out.data_ptr() - self.base)
+        rc = _lib.lib().dpfs_gemm_allreduce_bf16(a.data_ptr(), a.stride(0), w.data_ptr(), w.stride(0), int(b_mn_major),
+                                                 out.data_ptr(), mc, M, N, K, self.flag_ptrs, self.rank, self.n, bn,
+                                                 _lib.stream())
+        _lib.check(rc, "dpfs_gemm_allreduce_bf16")
+        return out
+
+    def barrier(self):
+        _lib.check(_lib.lib().dpfs_comm_barrier(self.flag_ptrs, self.rank, self.n, _lib.stream()), "dpfs_comm_barrier")

@@ -31,6 +31,30 @@ int dpfs_gemm_bf16(const void* A, long long lda, int a_mn_major, const void* B, 
                    long long ldr, int M, int N, int K, int splits, float* workspace, int bn,
                    cudaStream_t stream);
 
+/* Fused GEMM -> all-reduce over NVLink (one kernel): every rank computes its partial out = A_r B_r^T (bf16) into
+ * its symmetric buffer `out` ([M][N], row stride N) and the ranks sum the tiles through the NVSwitch with
+ * multimem.ld_reduce / multimem.st on `mc_out` (the multicast alias of `out`).  flag_ptrs: HOST array of the n ranks'
+ * flag-buffer addresses (dpfs_comm_flag_words() uint32 each, zero-initialised, peer-mapped).  On return of the kernel
+ * every rank's `out` holds the full sum.  ref: RowParallelLinear.forward GEMM + Reduce (models/layers.py:49-51,
+ * models/comm_ops.py:39) and the Copy.backward all-reduce after the dgrad GEMM (models/comm_ops.py:59). */
+int dpfs_gemm_allreduce_bf16(const void* A, long long lda, const void* B, long long ldb, int b_mn_major, void* out,
+                             void* mc_out, int M, int N, int K, const unsigned long long* flag_ptrs, int rank, int n,
+                             int bn, cudaStream_t stream);
+
+/* ---- Stand-alone NVLS collectives over symmetric memory ----------------------------------------------------------
+ * In-place two-shot all-reduce of the `nbytes` at multicast address mc_ptr (every rank passes the same offset),
+ * all-gather of nbytes_per_rank from local `src` into slot `rank` of mc_dst on every rank, and a rank-wide barrier.
+ * ref: dist.all_reduce / dist.all_gather in models/comm_ops.py:26,39,59,74 (NCCL in the reference). */
+int dpfs_comm_flag_words(void);
+int dpfs_allreduce_nvls(void* mc_ptr, long long nbytes, int is_bf16, const unsigned long long* flag_ptrs, int rank,
+                        int n, cudaStream_t stream);
+int dpfs_allgather_nvls(const void* src, void* mc_dst, long long nbytes_per_rank,
+                        const unsigned long long* flag_ptrs, int rank, int n, cudaStream_t stream);
+int dpfs_comm_barrier(const unsigned long long* flag_ptrs, int rank, int n, cudaStream_t stream);
+
+/* number of kernels launched by this library so far (bench.py's gpu_launches) */
+unsigned long long dpfs_launch_count(void);
+
 /* ---- Fused causal flash attention (tcgen05 / TMEM / TMA) ---------------------------------------------------
  * qkv: bf16 [B*T][3*H*HD] packed q|k|v (RoPE already applied); out: bf16 [B*T][H*HD]; lse: fp32 [B][H][T].
  * HD must be 64 or 128.  ref: Attention.forward, models/model.py:68-78 (matmul + triu mask + softmax + matmul). */
@@ -48,6 +72,11 @@ int dpfs_attn_bwd(const void* qkv, const void* out, const void* d_out, const flo
 int dpfs_norm_bwd_blocks(int M); /* number of CTAs the backward kernels launch == rows of scratch they need */
 int dpfs_rmsnorm_fwd(const void* x, int x_bf16, const float* scale, void* y, int y_bf16, float* rstd /*nullable*/,
                      int M, int D, float eps, cudaStream_t stream);
+/* x_out = x + y + bias (fp32); h = rmsnorm(x_out) * scale (bf16, nullable together with scale/rstd).  y is the
+ * all-reduced bf16 output of a row-parallel GEMM.  ref: models/layers.py:51-54 + models/model.py:119-120. */
+int dpfs_add_rmsnorm_fwd(const float* x, const void* y_bf16, const float* bias /*nullable*/,
+                         const float* scale /*nullable*/, float* x_out, void* h_bf16 /*nullable*/,
+                         float* rstd /*nullable*/, int M, int D, float eps, cudaStream_t stream);
 /* dx = dres + d(rmsnorm)(dy); writes dx (fp32, nullable) and/or dx_bf16 (nullable); dscale[D] (+= if accumulate).
  * scratch: dpfs_norm_bwd_blocks(M) * D floats. */
 int dpfs_rmsnorm_bwd(const void* dy, int dy_bf16, const void* x, int x_bf16, const float* rstd, const float* scale,
