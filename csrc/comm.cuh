@@ -93,4 +93,102 @@ __device__ __forceinline__ void multimem_st_16B(void* mc_ptr, uint4 v) {
                : "memory");
 }
 
+// ---------------------------------------------------------------------------------------------------------------
+// P2P data path: plain loads / stores on peer-mapped pointers.  Measured on 2xB200 (profiles/comm_paths_r1.md) this
+// moves ~1.5-2x the bytes per SM-thread of the multimem path, so it is the default for the reduce phase.
+struct PeerPtrs {
+  uint8_t* p[kMaxRanks];
+};
+__device__ __forceinline__ uint4 ld_peer_16B(const void* p) {
+  uint4 v;
+  asm volatile("ld.global.relaxed.sys.v4.u32 {%0,%1,%2,%3}, [%4];"
+               : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w)
+               : "l"(p)
+               : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_peer_16B(void* p, uint4 v) {
+  asm volatile("st.global.relaxed.sys.v4.u32 [%0], {%1,%2,%3,%4};" ::"l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w)
+               : "memory");
+}
+
+// Sum the NR ranks' copies of a [rows][cpr x 16 B] bf16 region (row pitch ld_bytes, starting at byte offset off0) in
+// fp32, in rank order (bitwise identical on every rank and run to run), and write the bf16 result into every rank's
+// copy.  16 / NR independent 16-byte loads per rank are in flight per thread.
+template <int NR, int INFLIGHT = 16>
+__device__ __forceinline__ void reduce_region_p2p(const PeerPtrs& peers, long long off0, long long ld_bytes, int rows,
+                                                  int cpr, int tid, int nthreads) {
+  constexpr int KC = INFLIGHT / NR;
+  const int total = rows * cpr;
+  for (int base = tid; base < total; base += nthreads * KC) {
+    uint4 v[KC][NR];
+    long long off[KC];
+#pragma unroll
+    for (int k = 0; k < KC; ++k) {
+      const int idx = base + k * nthreads;
+      const int r_ = idx / cpr, cc = idx - r_ * cpr;
+      off[k] = off0 + r_ * ld_bytes + cc * 16;
+      if (idx < total) {
+#pragma unroll
+        for (int r = 0; r < NR; ++r) v[k][r] = ld_peer_16B(peers.p[r] + off[k]);
+      }
+    }
+#pragma unroll
+    for (int k = 0; k < KC; ++k) {
+      if (base + k * nthreads < total) {
+        float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+        for (int r = 0; r < NR; ++r) {
+          const uint32_t w[4] = {v[k][r].x, v[k][r].y, v[k][r].z, v[k][r].w};
+#pragma unroll
+          for (int i = 0; i < 4; ++i) {
+            const float2 f = unpack_bf16(w[i]);
+            acc[2 * i] += f.x;
+            acc[2 * i + 1] += f.y;
+          }
+        }
+        const uint4 o = make_uint4(pack_bf16(acc[0], acc[1]), pack_bf16(acc[2], acc[3]), pack_bf16(acc[4], acc[5]),
+                                   pack_bf16(acc[6], acc[7]));
+#pragma unroll
+        for (int r = 0; r < NR; ++r) st_peer_16B(peers.p[r] + off[k], o);
+      }
+    }
+  }
+}
+
+// fp32 variant (4 floats per 16-byte unit)
+template <int NR>
+__device__ __forceinline__ void reduce_region_p2p_f32(const PeerPtrs& peers, long long off0, long long units, int tid,
+                                                      long long nthreads) {
+  constexpr int KC = 16 / NR;
+  for (long long base = tid; base < units; base += nthreads * KC) {
+    uint4 v[KC][NR];
+#pragma unroll
+    for (int k = 0; k < KC; ++k) {
+      const long long u = base + k * nthreads;
+      if (u < units) {
+#pragma unroll
+        for (int r = 0; r < NR; ++r) v[k][r] = ld_peer_16B(peers.p[r] + off0 + u * 16);
+      }
+    }
+#pragma unroll
+    for (int k = 0; k < KC; ++k) {
+      const long long u = base + k * nthreads;
+      if (u < units) {
+        float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
+#pragma unroll
+        for (int r = 0; r < NR; ++r) {
+          a0 += __uint_as_float(v[k][r].x);
+          a1 += __uint_as_float(v[k][r].y);
+          a2 += __uint_as_float(v[k][r].z);
+          a3 += __uint_as_float(v[k][r].w);
+        }
+        const uint4 o = make_uint4(__float_as_uint(a0), __float_as_uint(a1), __float_as_uint(a2), __float_as_uint(a3));
+#pragma unroll
+        for (int r = 0; r < NR; ++r) st_peer_16B(peers.p[r] + off0 + u * 16, o);
+      }
+    }
+  }
+}
+
 }  // namespace dpfs

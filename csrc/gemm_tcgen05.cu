@@ -15,6 +15,7 @@
 
 #include <cudaTypedefs.h>
 #include <stdio.h>
+#include <stdlib.h>
 
 namespace dpfs {
 
@@ -23,6 +24,7 @@ unsigned long long g_launches = 0;
 constexpr int BM = 128;
 constexpr int BK = 64;
 constexpr int kGemmThreads = 192;  // warp 0: TMA producer, warp 1: MMA issuer + TMEM owner, warps 2-5: epilogue
+constexpr int kCommThreads = 256;  // FUSE_AR only: warps 6-13 reduce finished tiles over NVLink while the GEMM runs
 
 struct GemmArgs {
   int M, N, K;
@@ -35,7 +37,9 @@ struct GemmArgs {
   const float* residual;   // fp32 [M][ldr] or nullptr
   long long ldr;
   // fused all-reduce (FUSE_AR kernels only): `out` is this rank's symmetric buffer, `mc_out` its multicast alias
-  uint8_t* mc_out;
+  uint8_t* mc_out;   // multicast alias of out (NVLS reduce path) or nullptr (P2P reduce path)
+  PeerPtrs peers;    // every rank's `out` (P2P reduce path)
+  int debug;         // bring-up only: bit0 skip tile signals, bit1 skip tile waits, bit2 skip the reduce traffic
   CommCtx comm;
 };
 
@@ -84,7 +88,7 @@ __device__ __forceinline__ void store_chunk32<__nv_bfloat16>(__nv_bfloat16* dst,
 // tile are flagged, it pulls their sum through the NVSwitch (multimem.ld_reduce) and broadcasts the result into every
 // rank's buffer (multimem.st).  A closing rank-wide barrier makes the full result visible before the kernel exits.
 template <int BN, bool A_MN, bool B_MN, typename OutT, bool FUSE_AR = false>
-__global__ void __launch_bounds__(kGemmThreads, 1)
+__global__ void __launch_bounds__(FUSE_AR ? kGemmThreads + kCommThreads : kGemmThreads, 1)
 gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                  const GemmArgs args) {
   using S = GemmSmem<BN>;
@@ -211,7 +215,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         }
       }
     }
-  } else {
+  } else if (warp < 6) {
     // ------------------------------------------------------------------ epilogue warps (TMEM -> regs -> global)
     const int q = warp & 3;  // TMEM lane quarter this warp may access
     int as = 0;
@@ -268,7 +272,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       if constexpr (FUSE_AR) {
         // all 128 epilogue threads have stored their rows of the partial tile -> tell the owner rank
         asm volatile("bar.sync 1, 128;" ::: "memory");
-        if (threadIdx.x == 64) {
+        if (threadIdx.x == 64 && !(args.debug & 1)) {
           const int m_blk = t / tiles_n;
           const int owner = m_blk % args.comm.n;
           __threadfence_system();
@@ -276,24 +280,35 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         }
       }
     }
+  } else {
     if constexpr (FUSE_AR) {
-      // ---------------------------------------------------------------- reduce phase: tiles owned by this rank
-      const int et = threadIdx.x - 64;  // 0..127
+      // ---------------------------------------------------------------- comm warps: reduce the tiles this rank owns
+      // Tile row-block m_blk belongs to rank m_blk % n; owned tiles are dealt round-robin to the CTAs.  As soon as the
+      // n partial copies of a tile are flagged, sum them over NVLink (fp32, rank order) and write the bf16 result into
+      // every rank's buffer — while warps 0-5 of this CTA are still computing other tiles.
+      const int ct = threadIdx.x - kGemmThreads;
       const int n = args.comm.n, rank = args.comm.rank;
-      int k = 0;
-      for (int m_blk = rank; m_blk < tiles_m; m_blk += n) {
-        for (int n_blk = 0; n_blk < tiles_n; ++n_blk, ++k) {
-          if (k % static_cast<int>(gridDim.x) != static_cast<int>(blockIdx.x)) continue;
+      const int owned_rows = (tiles_m - rank + n - 1) / n;  // row-blocks m_blk = rank, rank + n, ...
+      const int n_owned = owned_rows * tiles_n;
+      for (int k = blockIdx.x; k < n_owned; k += gridDim.x) {
+        {
+          const int m_blk = rank + n * (k / tiles_n);
+          const int n_blk = k % tiles_n;
           const int t = m_blk * tiles_n + n_blk;
-          if (et < n) wait_signal(args.comm.flags[rank] + (kMaxBlocks + t) * kMaxRanks + et);
-          asm volatile("bar.sync 1, 128;" ::: "memory");
+          if (ct < n && !(args.debug & 2)) wait_signal(args.comm.flags[rank] + (kMaxBlocks + t) * kMaxRanks + ct);
+          asm volatile("bar.sync 2, 256;" ::: "memory");
+          if (args.debug & 4) continue;
           const int m0 = m_blk * BM, n0 = n_blk * BN;
           const int rows = min(BM, args.M - m0);
           const int cpr = min(BN, args.N - n0) / 8;  // 16-byte chunks per row
-          for (int idx = et; idx < rows * cpr; idx += 128) {
-            const int r = idx / cpr, cc = idx - r * cpr;
-            uint8_t* p = args.mc_out + (static_cast<long long>(m0 + r) * args.ldo + n0 + cc * 8) * 2;
-            multimem_st_16B(p, multimem_ld_reduce_bf16x8(p));
+          const long long off0 = (static_cast<long long>(m0) * args.ldo + n0) * 2;
+          const long long ldb = args.ldo * 2;
+          if (n == 2) {
+            reduce_region_p2p<2, 8>(args.peers, off0, ldb, rows, cpr, ct, kCommThreads);
+          } else if (n == 4) {
+            reduce_region_p2p<4, 8>(args.peers, off0, ldb, rows, cpr, ct, kCommThreads);
+          } else {
+            reduce_region_p2p<8, 8>(args.peers, off0, ldb, rows, cpr, ct, kCommThreads);
           }
         }
       }
@@ -302,7 +317,9 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
 
   tc_fence_before();
   __syncthreads();
-  if constexpr (FUSE_AR) sync_ranks(args.comm, blockIdx.x);
+  if constexpr (FUSE_AR) {
+    if (!(args.debug & 8)) sync_ranks(args.comm, blockIdx.x);
+  }
   if (warp == 1) {
     tc_fence_after();
     tmem_dealloc(tmem_base, 2 * BN);
@@ -418,7 +435,7 @@ static int launch_gemm_ar(const CUtensorMap& tmA, const CUtensorMap& tmB, const 
   if (tiles > kMaxTiles) return -52;
   int grid = tiles < num_sms() ? tiles : num_sms();
   if (grid > kMaxBlocks) grid = kMaxBlocks;
-  kfn<<<(DPFS_COUNT(), grid), kGemmThreads, S::kTotal, stream>>>(tmA, tmB, args);
+  kfn<<<(DPFS_COUNT(), grid), kGemmThreads + kCommThreads, S::kTotal, stream>>>(tmA, tmB, args);
   return static_cast<int>(cudaGetLastError());
 }
 
@@ -464,6 +481,8 @@ extern "C" int dpfs_gemm_bf16(const void* A, long long lda, int a_mn_major, cons
 
   GemmArgs args;
   args.mc_out = nullptr;
+  args.debug = 0;
+  for (int i = 0; i < kMaxRanks; ++i) args.peers.p[i] = nullptr;
   args.comm.rank = 0;
   args.comm.n = 1;
   for (int i = 0; i < kMaxRanks; ++i) args.comm.flags[i] = nullptr;
@@ -517,11 +536,13 @@ extern "C" unsigned long long dpfs_launch_count(void) { return dpfs::g_launches;
 // Fused GEMM -> all-reduce: out (bf16 [M][N], row stride N) must be this rank's symmetric buffer and mc_out the
 // multicast alias of the same offset; on return every rank's `out` holds sum_r A_r B_r^T.
 extern "C" int dpfs_gemm_allreduce_bf16(const void* A, long long lda, const void* B, long long ldb, int b_mn_major,
-                                        void* out, void* mc_out, int M, int N, int K,
+                                        void* out, void* mc_out, const unsigned long long* data_ptrs,
+                                        long long out_offset, int M, int N, int K,
                                         const unsigned long long* flag_ptrs, int rank, int n, int bn,
                                         cudaStream_t stream) {
   if (M <= 0 || N <= 0 || K <= 0) return 0;
   if (n < 2 || n > kMaxRanks) return -50;
+  if (n != 2 && n != 4 && n != 8) return -50;  // the in-kernel reduce is templated on the rank count
   if ((N % 8) != 0 || (lda % 8) != 0 || (ldb % 8) != 0) return -10;
   if (bn != 256) bn = 128;
   CUtensorMap tmA, tmB;
@@ -545,6 +566,12 @@ extern "C" int dpfs_gemm_allreduce_bf16(const void* A, long long lda, const void
   args.residual = nullptr;
   args.ldr = 0;
   args.mc_out = static_cast<uint8_t*>(mc_out);
+  {
+    const char* e = getenv("DPFS_FUSE_DEBUG");
+    args.debug = e ? atoi(e) : 0;
+  }
+  for (int i = 0; i < kMaxRanks; ++i)
+    args.peers.p[i] = (i < n && data_ptrs) ? reinterpret_cast<uint8_t*>(data_ptrs[i]) + out_offset : nullptr;
   for (int i = 0; i < kMaxRanks; ++i) args.comm.flags[i] = i < n ? reinterpret_cast<uint32_t*>(flag_ptrs[i]) : nullptr;
   args.comm.rank = rank;
   args.comm.n = n;

@@ -25,12 +25,15 @@ c_p = ctypes.c_void_p
 SIGS = {
     "dpfs_gemm_bf16": (c_p, c_ll, c_int, c_p, c_ll, c_int, c_p, c_ll, c_int, c_p, c_p, c_ll, c_int, c_int, c_int,
                        c_int, c_p, c_int, c_p),
-    "dpfs_gemm_allreduce_bf16": (c_p, c_ll, c_p, c_ll, c_int, c_p, c_p, c_int, c_int, c_int, c_p, c_int, c_int,
-                                 c_int, c_p),
+    "dpfs_gemm_allreduce_bf16": (c_p, c_ll, c_p, c_ll, c_int, c_p, c_p, c_p, c_ll, c_int, c_int, c_int, c_p, c_int,
+                                 c_int, c_int, c_p),
+    "dpfs_allreduce_p2p": (c_p, c_ll, c_ll, c_int, c_p, c_int, c_int, c_p),
     "dpfs_comm_flag_words": (),
     "dpfs_allreduce_nvls": (c_p, c_ll, c_int, c_p, c_int, c_int, c_p),
+    "dpfs_allgather_p2p": (c_p, c_p, c_ll, c_ll, c_p, c_int, c_int, c_p),
     "dpfs_allgather_nvls": (c_p, c_p, c_ll, c_p, c_int, c_int, c_p),
     "dpfs_comm_barrier": (c_p, c_int, c_int, c_p),
+    "dpfs_allreduce_exp": (c_p, c_p, c_ll, c_ll, c_int, c_int, c_p, c_int, c_int, c_p),
     "dpfs_launch_count": (),
     "dpfs_add_rmsnorm_fwd": (c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_int, c_int, c_f, c_p),
     "dpfs_norm_bwd_blocks": (c_int,),

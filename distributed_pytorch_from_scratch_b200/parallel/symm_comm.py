@@ -35,10 +35,17 @@ class SymmComm:
         self.rank, self.n = rank, n
         self.base = data.data_ptr()
         self.capacity = data.numel()
-        self.mc_base = int(data_hdl.multicast_ptr)
+        self.mc_base = int(getattr(data_hdl, "multicast_ptr", 0) or 0)
         self.flag_ptrs = (ctypes.c_ulonglong * 8)(*([int(p) for p in flags_hdl.buffer_ptrs] + [0] * (8 - n)))
+        self.data_ptrs = (ctypes.c_ulonglong * 8)(*([int(p) for p in data_hdl.buffer_ptrs] + [0] * (8 - n)))
         self.gather_off = self.capacity - self.capacity // 8        # last 1/8th: all-gather landing zone
         self.closed = False
+        # data path of the reduce: "p2p" (plain NVLink loads/stores, rank-ordered fp32 sums) or "nvls" (multimem.*)
+        self.mode = os.environ.get("DPFS_AR_MODE", "p2p")
+        if n not in (2, 4, 8):
+            self.mode = "nvls"
+        if self.mode == "nvls" and not self.mc_base:
+            raise RuntimeError("NVLS multicast is not available for this process group")
 
     # ------------------------------------------------------------------------------------------ construction
     @classmethod
@@ -56,8 +63,6 @@ class SymmComm:
             pass
         data = symm_mem.empty(data_bytes, dtype=torch.uint8, device=dev)
         hdl = symm_mem.rendezvous(data, name)
-        if not getattr(hdl, "multicast_ptr", 0):
-            raise RuntimeError("NVLS multicast is not available for this process group")
         words = _lib.lib().dpfs_comm_flag_words()
         flags = symm_mem.empty(words, dtype=torch.int32, device=dev)
         flags.zero_()
@@ -96,10 +101,14 @@ class SymmComm:
         else:
             work = self.buffer(t.shape, t.dtype)
             work.copy_(t)
-        mc = self.mc_base + (work.data_ptr() - self.base)
-        rc = _lib.lib().dpfs_allreduce_nvls(mc, nbytes, int(t.dtype == BF16), self.flag_ptrs, self.rank, self.n,
-                                            _lib.stream())
-        _lib.check(rc, "dpfs_allreduce_nvls")
+        off = work.data_ptr() - self.base
+        if self.mode == "nvls":
+            rc = _lib.lib().dpfs_allreduce_nvls(self.mc_base + off, nbytes, int(t.dtype == BF16), self.flag_ptrs,
+                                                self.rank, self.n, _lib.stream())
+        else:
+            rc = _lib.lib().dpfs_allreduce_p2p(self.data_ptrs, off, nbytes, int(t.dtype == BF16), self.flag_ptrs,
+                                               self.rank, self.n, _lib.stream())
+        _lib.check(rc, "dpfs_allreduce")
         if out is None:
             return work if work is t else work.clone()
         if out.data_ptr() != work.data_ptr():
@@ -112,10 +121,13 @@ class SymmComm:
         nbytes = t.numel() * t.element_size()
         pad = (-nbytes) % 16
         assert pad == 0 and nbytes * self.n <= self.capacity - self.gather_off
-        mc = self.mc_base + self.gather_off
-        rc = _lib.lib().dpfs_allgather_nvls(t.data_ptr(), mc, nbytes, self.flag_ptrs, self.rank, self.n,
-                                            _lib.stream())
-        _lib.check(rc, "dpfs_allgather_nvls")
+        if self.mc_base and self.mode == "nvls":
+            rc = _lib.lib().dpfs_allgather_nvls(t.data_ptr(), self.mc_base + self.gather_off, nbytes, self.flag_ptrs,
+                                                self.rank, self.n, _lib.stream())
+        else:
+            rc = _lib.lib().dpfs_allgather_p2p(t.data_ptr(), self.data_ptrs, self.gather_off, nbytes, self.flag_ptrs,
+                                               self.rank, self.n, _lib.stream())
+        _lib.check(rc, "dpfs_allgather")
         view = self.data[self.gather_off:self.gather_off + nbytes * self.n].view(t.dtype).view((self.n,) + t.shape)
         return view.clone()
 
@@ -133,10 +145,11 @@ class SymmComm:
         M, K = a.shape
         N = w.shape[1] if b_mn_major else w.shape[0]
         out = self.buffer((M, N), BF16)
-        mc = self.mc_base + (out.data_ptr() - self.base)
+        off = out.data_ptr() - self.base
+        mc = self.mc_base + off if self.mode == "nvls" else 0
         rc = _lib.lib().dpfs_gemm_allreduce_bf16(a.data_ptr(), a.stride(0), w.data_ptr(), w.stride(0), int(b_mn_major),
-                                                 out.data_ptr(), mc, M, N, K, self.flag_ptrs, self.rank, self.n, bn,
-                                                 _lib.stream())
+                                                 out.data_ptr(), mc, self.data_ptrs, off, M, N, K, self.flag_ptrs,
+                                                 self.rank, self.n, bn, _lib.stream())
         _lib.check(rc, "dpfs_gemm_allreduce_bf16")
         return out
 

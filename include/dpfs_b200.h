@@ -38,8 +38,11 @@ int dpfs_gemm_bf16(const void* A, long long lda, int a_mn_major, const void* B, 
  * every rank's `out` holds the full sum.  ref: RowParallelLinear.forward GEMM + Reduce (models/layers.py:49-51,
  * models/comm_ops.py:39) and the Copy.backward all-reduce after the dgrad GEMM (models/comm_ops.py:59). */
 int dpfs_gemm_allreduce_bf16(const void* A, long long lda, const void* B, long long ldb, int b_mn_major, void* out,
-                             void* mc_out, int M, int N, int K, const unsigned long long* flag_ptrs, int rank, int n,
-                             int bn, cudaStream_t stream);
+                             void* mc_out /* NVLS reduce path; NULL = P2P reduce path */,
+                             const unsigned long long* data_ptrs /* HOST array: every rank's symmetric base */,
+                             long long out_offset /* byte offset of `out` inside the symmetric buffer */, int M,
+                             int N, int K, const unsigned long long* flag_ptrs, int rank, int n, int bn,
+                             cudaStream_t stream);
 
 /* ---- Stand-alone NVLS collectives over symmetric memory ----------------------------------------------------------
  * In-place two-shot all-reduce of the `nbytes` at multicast address mc_ptr (every rank passes the same offset),
@@ -48,8 +51,18 @@ int dpfs_gemm_allreduce_bf16(const void* A, long long lda, const void* B, long l
 int dpfs_comm_flag_words(void);
 int dpfs_allreduce_nvls(void* mc_ptr, long long nbytes, int is_bf16, const unsigned long long* flag_ptrs, int rank,
                         int n, cudaStream_t stream);
+/* Same all-reduce over plain peer loads / stores (fp32 accumulation in rank order; n in {2,4,8}). */
+int dpfs_allreduce_p2p(const unsigned long long* data_ptrs, long long offset, long long nbytes, int is_bf16,
+                       const unsigned long long* flag_ptrs, int rank, int n, cudaStream_t stream);
+int dpfs_allgather_p2p(const void* src, const unsigned long long* data_ptrs, long long dst_offset,
+                       long long nbytes_per_rank, const unsigned long long* flag_ptrs, int rank, int n,
+                       cudaStream_t stream);
 int dpfs_allgather_nvls(const void* src, void* mc_dst, long long nbytes_per_rank,
                         const unsigned long long* flag_ptrs, int rank, int n, cudaStream_t stream);
+/* experimental data-path variants of the all-reduce (tools/gpu_ar_sweep.py); mode 3/4 are correct all-reduces */
+int dpfs_allreduce_exp(void* mc_base, const unsigned long long* data_ptrs, long long offset, long long nbytes,
+                       int mode, int blocks, const unsigned long long* flag_ptrs, int rank, int n,
+                       cudaStream_t stream);
 int dpfs_comm_barrier(const unsigned long long* flag_ptrs, int rank, int n, cudaStream_t stream);
 
 /* number of kernels launched by this library so far (bench.py's gpu_launches) */

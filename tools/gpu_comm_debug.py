@@ -55,6 +55,15 @@ for dtype, shape in [(torch.bfloat16, (32000, 512)), (torch.float32, (4096, 512)
     torch.cuda.synchronize()
     err = (buf.float() - ref.float()).abs().max().item()
     log(f"[allreduce x50 in place] err {err:.4g} {'OK' if err < 0.1 else 'FAIL'}")
+for shape in [(32000, 512), (32000, 2048)]:
+    buf = symm.buffer(shape, torch.bfloat16)
+    buf.normal_()
+    t_own = timeit(lambda: symm.all_reduce(buf, out=buf))
+    y = torch.randn(shape, device="cuda").to(torch.bfloat16)
+    t_nccl = timeit(lambda: dist.all_reduce(y))
+    S = shape[0] * shape[1] * 2
+    log(f"[allreduce time] {shape} bf16 ({S/1e6:.1f} MB): NVLS kernel {t_own:.1f} us ({S/t_own/1e3:.0f} GB/s algbw), "
+        f"NCCL {t_nccl:.1f} us ({S/t_nccl/1e3:.0f} GB/s)")
 st = torch.randn(32000, 3, device="cuda")
 g = symm.all_gather_rows(st)
 ref = torch.empty(world, 32000, 3, device="cuda")
