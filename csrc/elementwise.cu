@@ -235,14 +235,34 @@ __global__ void __launch_bounds__(kNormThreads) rmsnorm_bwd_kernel(
   }
 }
 
-// out[c] = sum_b partial[b][c]
-__global__ void reduce_partials_kernel(const float* __restrict__ partial, float* __restrict__ out, int nblocks,
-                                       int D, int accumulate) {
-  const int c = blockIdx.x * blockDim.x + threadIdx.x;
-  if (c >= D) return;
+// out[c] = sum_b partial[b][c].  Block = 32 columns x 8 row-groups: each warp sums a strided subset of the rows of
+// its 32 columns (coalesced 128-byte reads), the 8 partial sums meet in shared memory in a fixed order.
+__global__ void __launch_bounds__(256) reduce_partials_kernel(const float* __restrict__ partial,
+                                                              float* __restrict__ out, int nblocks, int D,
+                                                              int accumulate) {
+  __shared__ float sm[8][33];
+  const int lane = threadIdx.x & 31, grp = threadIdx.x >> 5;
+  const int c = blockIdx.x * 32 + lane;
   float s = 0.f;
-  for (int b = 0; b < nblocks; ++b) s += partial[static_cast<long long>(b) * D + c];
-  out[c] = accumulate ? out[c] + s : s;
+  if (c < D) {
+    int b = grp;
+    for (; b + 24 < nblocks; b += 32) {  // 4 independent loads in flight
+      const float a0 = partial[static_cast<long long>(b) * D + c];
+      const float a1 = partial[static_cast<long long>(b + 8) * D + c];
+      const float a2 = partial[static_cast<long long>(b + 16) * D + c];
+      const float a3 = partial[static_cast<long long>(b + 24) * D + c];
+      s += (a0 + a1) + (a2 + a3);
+    }
+    for (; b < nblocks; b += 8) s += partial[static_cast<long long>(b) * D + c];
+  }
+  sm[grp][lane] = s;
+  __syncthreads();
+  if (grp == 0 && c < D) {
+    float t = 0.f;
+#pragma unroll
+    for (int g = 0; g < 8; ++g) t += sm[g][lane];
+    out[c] = accumulate ? out[c] + t : t;
+  }
 }
 
 // --------------------------------------------------------------------------------------------- LayerNorm
@@ -657,7 +677,7 @@ extern "C" int dpfs_rmsnorm_bwd(const void* dy, int dy_bf16, const void* x, int 
   });
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) return static_cast<int>(e);
-  reduce_partials_kernel<<<(DPFS_COUNT(), (D + 255) / 256), 256, 0, stream>>>(scratch, dscale, grid, D, dscale_accumulate);
+  reduce_partials_kernel<<<(DPFS_COUNT(), (D + 31) / 32), 256, 0, stream>>>(scratch, dscale, grid, D, dscale_accumulate);
   return static_cast<int>(cudaGetLastError());
 }
 
@@ -707,7 +727,7 @@ extern "C" int dpfs_layernorm_bwd(const void* dy, int dy_bf16, const void* x, in
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) return static_cast<int>(e);
   // partial rows are [dgamma(D) | dbeta(D)]: reduce as one 2D-wide vector into a strided pair of outputs
-  reduce_partials_kernel<<<(DPFS_COUNT(), (2 * D + 255) / 256), 256, 0, stream>>>(scratch, scratch + (long long)grid * 2 * D, grid,
+  reduce_partials_kernel<<<(DPFS_COUNT(), (2 * D + 31) / 32), 256, 0, stream>>>(scratch, scratch + (long long)grid * 2 * D, grid,
                                                                   2 * D, 0);
   e = cudaGetLastError();
   if (e != cudaSuccess) return static_cast<int>(e);
@@ -774,7 +794,7 @@ extern "C" int dpfs_colsum_bf16(const void* x, long long ld, float* out, int acc
   colsum_partial_kernel<<<(DPFS_COUNT(), grid), 128, 0, stream>>>((const __nv_bfloat16*)x, ld, scratch, M, N);
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) return static_cast<int>(e);
-  reduce_partials_kernel<<<(DPFS_COUNT(), (N + 255) / 256), 256, 0, stream>>>(scratch, out, strips, N, accumulate);
+  reduce_partials_kernel<<<(DPFS_COUNT(), (N + 31) / 32), 256, 0, stream>>>(scratch, out, strips, N, accumulate);
   return static_cast<int>(cudaGetLastError());
 }
 
@@ -847,7 +867,7 @@ extern "C" int dpfs_colsum_bf16_static(const void* x, long long ld, float* out, 
   colsum_partial_kernel<<<(DPFS_COUNT(), grid), 128, 0, stream>>>((const __nv_bfloat16*)x, ld, scratch, M, N);
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) return static_cast<int>(e);
-  reduce_partials_kernel<<<(DPFS_COUNT(), (N + 255) / 256), 256, 0, stream>>>(scratch, out, static_cast<int>(strips),
+  reduce_partials_kernel<<<(DPFS_COUNT(), (N + 31) / 32), 256, 0, stream>>>(scratch, out, static_cast<int>(strips),
                                                                              N, accumulate);
   return static_cast<int>(cudaGetLastError());
 }

@@ -31,6 +31,10 @@ class TrainStep:
         self.autocast_bf16 = autocast_bf16
         fused_opt = isinstance(optimizer, FusedAdam) and optimizer.arena is not None
         self.use_graph = bool(use_graph and self.device.type == "cuda" and fused_opt)
+        from .parallel import process_manager as pm
+        if pm.pgm is not None and pm.pgm.tp_size > 1 and pm.pgm.symm is None:
+            # NCCL collectives inside a captured step hang on this stack; only our own NVLink kernels are captured
+            self.use_graph = False
         self.fused_opt = fused_opt
         self.max_graphs = max_graphs
         self._graphs: Dict[Tuple[int, int], dict] = {}

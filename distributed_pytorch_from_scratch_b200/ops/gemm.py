@@ -13,7 +13,10 @@ import torch
 
 from . import _lib
 
+import os
+
 _WS = {}
+_DEFAULT_BN = int(os.environ.get("DPFS_GEMM_BN", "256"))
 
 
 def _workspace(device, nfloats: int) -> torch.Tensor:
@@ -64,6 +67,9 @@ def gemm_nt(a: torch.Tensor, b: torch.Tensor, *, a_mn_major: bool = False, b_mn_
         assert bias.dtype == torch.float32 and bias.numel() == N and bias.is_contiguous()
     if residual is not None:
         assert residual.dtype == torch.float32 and residual.shape == (M, N) and residual.stride(1) == 1
+    if bn == 0:
+        # 128x256 tiles halve the smem operand traffic per MMA (measured 5-40% faster than 128x128 on B200)
+        bn = _DEFAULT_BN if (_DEFAULT_BN != 256 or N % 256 == 0) else 128
     if splits == 0:
         splits = auto_splits(M, N, K, bn or 128) if residual is None else 1
     ws = _workspace(a.device, splits * M * N) if splits > 1 else None
