@@ -79,7 +79,10 @@ class TrainStep:
         torch.cuda.synchronize()
         g = torch.cuda.CUDAGraph()
         before = _lib.lib().dpfs_launch_count() if _lib.available() else 0
-        kw = {"pool": self._pool} if self._pool is not None else {}
+        # thread_local: NCCL's watchdog thread may poll events while we capture (it never touches our stream)
+        kw = {"capture_error_mode": "thread_local"}
+        if self._pool is not None:
+            kw["pool"] = self._pool
         with torch.cuda.graph(g, **kw):
             loss = self._loss_backward(ids, pos, tgt)
             opt.launch()
