@@ -182,7 +182,8 @@ def run_ours(args):
         from distributed_pytorch_from_scratch_b200.parallel.symm import try_enable_symm
         try_enable_symm(required=(args.comm == "fused"))
     margs = ModelArgumments()
-    model = Transformer(**asdict(margs)).cuda()
+    sp = world > 1 and args.sp == "on"
+    model = Transformer(**asdict(margs), sequence_parallel=sp).cuda()
     model.reset_parameters()
     model.compute_dtype = torch.bfloat16
     model.train()
@@ -224,7 +225,7 @@ def run_ours(args):
         "data": "synthetic tokens (uniform ids, collate_fn layout), random-init weights",
         "impl": "ours",
         "config": {"model": "reference default ModelArgumments (d512 ffn2048 h8 L12 V1024 maxlen1000, 51.5M params)",
-                   "global_batch": BATCH, "seq_len": SEQ, "parallelism": f"tp{world}",
+                   "global_batch": BATCH, "seq_len": SEQ, "parallelism": f"tp{world}" + ("+sp" if sp else ""),
                    "optimizer": "Adam(3e-4) + OneCycleLR (fused, one launch)",
                    "cuda_graph": bool(step.use_graph),
                    "comm": ("fused-symm" if (pm.pgm.symm is not None) else ("nccl" if world > 1 else "none")),
@@ -345,6 +346,8 @@ def main():
     ap.add_argument("--comm", choices=["auto", "fused", "nccl"], default="auto",
                     help="TP collectives: our NVLink kernels over symmetric memory (fused), NCCL, or auto")
     ap.add_argument("--no-graph", action="store_true", help="run eagerly instead of replaying a CUDA graph")
+    ap.add_argument("--sp", choices=["on", "off"], default="off",
+                    help="Megatron sequence parallelism on top of TP (reduce-scatter / all-gather forms)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)
     if args.impl == "reference":

@@ -60,6 +60,52 @@ __global__ void __launch_bounds__(512) allreduce_p2p_kernel(CommCtx c, PeerPtrs 
   sync_ranks(c, blockIdx.x);
 }
 
+
+// P2P reduce-scatter over rows (sequence parallelism): the n ranks hold partial [rows_total][row_units*16 B] bf16
+// matrices at the same symmetric offset; rank r sums ITS block of rows over all ranks (fp32, rank order) and writes the
+// bf16 result to a private local buffer.  This is the first half of the two-shot all-reduce; the all-gather half is
+// allgather_p2p_kernel.  ref: the reference has no reduce-scatter (sequence parallel is an extension).
+template <int NR>
+__global__ void __launch_bounds__(512) reduce_scatter_p2p_kernel(CommCtx c, PeerPtrs peers, uint4* __restrict__ out,
+                                                                 long long units_per_rank) {
+  sync_ranks(c, blockIdx.x);  // every rank's partial matrix is complete
+  constexpr int KC = 16 / NR;
+  const long long src0 = static_cast<long long>(c.rank) * units_per_rank;
+  const long long nthreads = static_cast<long long>(gridDim.x) * blockDim.x;
+  for (long long base = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; base < units_per_rank;
+       base += nthreads * KC) {
+    uint4 v[KC][NR];
+#pragma unroll
+    for (int k = 0; k < KC; ++k) {
+      const long long u = base + k * nthreads;
+      if (u < units_per_rank) {
+#pragma unroll
+        for (int r = 0; r < NR; ++r) v[k][r] = ld_peer_16B(peers.p[r] + (src0 + u) * 16);
+      }
+    }
+#pragma unroll
+    for (int k = 0; k < KC; ++k) {
+      const long long u = base + k * nthreads;
+      if (u < units_per_rank) {
+        float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+        for (int r = 0; r < NR; ++r) {
+          const uint32_t w[4] = {v[k][r].x, v[k][r].y, v[k][r].z, v[k][r].w};
+#pragma unroll
+          for (int i = 0; i < 4; ++i) {
+            const float2 f = unpack_bf16(w[i]);
+            acc[2 * i] += f.x;
+            acc[2 * i + 1] += f.y;
+          }
+        }
+        out[u] = make_uint4(pack_bf16(acc[0], acc[1]), pack_bf16(acc[2], acc[3]), pack_bf16(acc[4], acc[5]),
+                            pack_bf16(acc[6], acc[7]));
+      }
+    }
+  }
+  sync_ranks(c, blockIdx.x);  // nobody overwrites its partial matrix while a peer still reads it
+}
+
 // all-gather: rank r broadcasts its `units` 16-byte units into slot r of every rank's buffer with multimem.st
 __global__ void __launch_bounds__(512) allgather_nvls_kernel(CommCtx c, const uint4* __restrict__ src, uint8_t* mc_base,
                                                              long long units) {
@@ -234,6 +280,33 @@ extern "C" int dpfs_allgather_nvls(const void* src, void* mc_dst, long long nbyt
   return static_cast<int>(cudaGetLastError());
 }
 
+
+template <int NR>
+static int launch_rs_p2p(const CommCtx& c, const PeerPtrs& pp, void* out, long long units, cudaStream_t stream) {
+  long long blocks = (units + 511) / 512;
+  const long long cap = 2ll * num_sms();
+  if (blocks > cap) blocks = cap;
+  if (blocks < 1) blocks = 1;
+  reduce_scatter_p2p_kernel<NR><<<(DPFS_COUNT(), static_cast<int>(blocks)), 512, 0, stream>>>(
+      c, pp, static_cast<uint4*>(out), units);
+  return static_cast<int>(cudaGetLastError());
+}
+
+// out (local, bf16) = sum over ranks of rows [rank*rows/n, (rank+1)*rows/n) of the symmetric partial matrix at `offset`
+extern "C" int dpfs_reduce_scatter_p2p(const unsigned long long* data_ptrs, long long offset, long long nbytes_total,
+                                       void* out, const unsigned long long* flag_ptrs, int rank, int n,
+                                       cudaStream_t stream) {
+  if (n != 2 && n != 4 && n != 8) return -50;
+  if (nbytes_total % (16ll * n) != 0 || offset % 16 != 0 || (reinterpret_cast<uintptr_t>(out) & 15)) return -51;
+  if (nbytes_total == 0) return 0;
+  CommCtx c = make_ctx(flag_ptrs, rank, n);
+  PeerPtrs pp = make_peers(data_ptrs, offset, n);
+  const long long units = nbytes_total / 16 / n;
+  if (n == 2) return launch_rs_p2p<2>(c, pp, out, units, stream);
+  if (n == 4) return launch_rs_p2p<4>(c, pp, out, units, stream);
+  return launch_rs_p2p<8>(c, pp, out, units, stream);
+}
+
 extern "C" int dpfs_allgather_p2p(const void* src, const unsigned long long* data_ptrs, long long dst_offset,
                                   long long nbytes_per_rank, const unsigned long long* flag_ptrs, int rank, int n,
                                   cudaStream_t stream) {
@@ -242,7 +315,7 @@ extern "C" int dpfs_allgather_p2p(const void* src, const unsigned long long* dat
   if (nbytes_per_rank == 0) return 0;
   const long long units = nbytes_per_rank / 16;
   long long blocks = (units + 511) / 512;
-  if (blocks > 32) blocks = 32;
+  if (blocks > 2ll * num_sms()) blocks = 2ll * num_sms();
   CommCtx c = make_ctx(flag_ptrs, rank, n);
   PeerPtrs pp = make_peers(data_ptrs, dst_offset, n);
   allgather_p2p_kernel<<<(DPFS_COUNT(), static_cast<int>(blocks)), 512, 0, stream>>>(

@@ -62,9 +62,13 @@ class ParamArena:
             a, f = layer.attn, layer.ffn
             groups += [[a.wq.weight, a.wk.weight, a.wv.weight], [a.wq.bias, a.wk.bias, a.wv.bias],
                        [a.wo.weight], [a.wo.bias], [f.gate_proj.weight, f.up_proj.weight],
-                       [f.gate_proj.bias, f.up_proj.bias], [f.down_proj.weight], [f.down_proj.bias],
-                       [layer.norm1.scale], [layer.norm2.scale]]
-        groups += [[model.embedding.weight], [model.norm.scale], [model.lm_head.weight], [model.lm_head.bias]]
+                       [f.gate_proj.bias, f.up_proj.bias], [f.down_proj.weight], [f.down_proj.bias]]
+        groups += [[model.embedding.weight], [model.lm_head.weight], [model.lm_head.bias]]
+        # every RMSNorm scale in ONE contiguous block: under sequence parallelism their gradients are partial sums
+        # over the local rows and are all-reduced with a single small collective
+        norm_group = [s_ for layer in model.layers for s_ in (layer.norm1.scale, layer.norm2.scale)]
+        norm_group.append(model.norm.scale)
+        groups.append(norm_group)
         seen = set()
         for g in groups:
             for p in g:
@@ -95,6 +99,8 @@ class ParamArena:
                 p._dpfs_shadow_view = self.shadow[off:off + n].view(p.shape)
                 p._dpfs_arena_off = off
                 self.entries.append((p, off))
+        first, last = norm_group[0], norm_group[-1]
+        self.norm_grads = self.grads[first._dpfs_arena_off:last._dpfs_arena_off + last.numel()]
         self._sig = None
         self.sync_shadow(force=True)
 
@@ -258,7 +264,7 @@ class FusedEmbedFn(torch.autograd.Function):
             # output to bf16 before the first layer (models/model.py:153-154)
             symm = pm.pgm.symm
             D = weight.shape[1]
-            if symm is not None and ids_flat.numel() * D * 2 <= symm.gather_off:
+            if symm is not None and ids_flat.numel() * D * 2 <= symm.ag_off:
                 part = symm.buffer((ids_flat.numel(), D), BF16)
                 fused.embedding_fwd(ids_flat, weight.detach(), emb.vocab_st_idx, emb.vocab_ed_idx, out=part)
                 out = symm.all_reduce(part, out=part).float()
@@ -357,19 +363,194 @@ class FusedRuntime:
         meta = Meta(B, T, self.d, self.Hl, self.hd, self.Fl, self.n)
         ids = input_ids.reshape(-1).contiguous()
         pos = position_ids.reshape(-1).contiguous()
+        if self.sp_active(B * T):
+            x = FusedEmbedSPFn.apply(ids, self, self.model.embedding.weight)
+            for pack in self.packs:
+                x = FusedLayerSPFn.apply(x, pos, self, pack, meta, *pack.params)
+            return x  # fp32 [M / n, d]: this rank's rows
         x = FusedEmbedFn.apply(ids, self, self.model.embedding.weight)
         for pack in self.packs:
             x = FusedLayerFn.apply(x, pos, self, pack, meta, *pack.params)
         return x  # fp32 [M, d]
 
+    def sp_active(self, M: int) -> bool:
+        """Sequence parallelism is on when the model asks for it, TP > 1 and the rows split evenly (16 B units)."""
+        return bool(getattr(self.model, "sequence_parallel", False)) and self.n > 1 and M % self.n == 0 \
+            and ((M // self.n) * self.d * 2) % 16 == 0
+
     def forward_loss(self, input_ids, position_ids, target_ids, ignore_index: int = -1) -> torch.Tensor:
         x = self.forward_hidden(input_ids, position_ids)
         tg = target_ids.reshape(-1).contiguous()
+        if self.sp_active(tg.numel()):
+            return FusedHeadLossSPFn.apply(x, tg, self, ignore_index, *self.head_params)
         return FusedHeadLossFn.apply(x, tg, self, ignore_index, *self.head_params)
 
     def forward_logits(self, input_ids, position_ids) -> torch.Tensor:
         B, T = input_ids.shape
-        x = self.forward_hidden(input_ids, position_ids).view(B, T, self.d)
+        x = self.forward_hidden(input_ids, position_ids)
+        if self.sp_active(B * T):
+            x = _all_gather_rows(x, keep=True)      # gather the rows back for the (replicated) logits path
+        x = x.view(B, T, self.d)
         with torch.autocast("cuda", dtype=BF16):
             logits = self.model.lm_head(self.model.norm(x))
         return logits
+
+
+# ================================================================================================ sequence parallel
+# Megatron-style sequence parallelism on top of TP (north-star config 4; the reference has none, SURVEY §2.3/§5.7):
+# the residual stream, the norms and every elementwise op work on this rank's M/n rows; each all-reduce becomes
+#     row-parallel GEMM  -> reduce-scatter over rows        (forward of wo / down, backward of q|k|v / gate|up / lm_head)
+#     all-gather of rows -> column-parallel GEMM            (forward of q|k|v / gate|up / lm_head, backward of wo / down)
+# Same bytes on the wire, 1/n of the norm / residual work and of the fp32 residual-stream memory.  RMSNorm scale
+# gradients become partial sums over local rows and are all-reduced once per step (ParamArena.norm_grads).
+def _reduce_scatter_rows(part_bf16):
+    """Sum the ranks' partial [M, N] matrices and keep this rank's block of rows -> [M / n, N] bf16."""
+    symm = pm.pgm.symm
+    if symm is not None and symm._inside(part_bf16) and symm.n in (2, 4, 8):
+        return symm.reduce_scatter_rows(part_bf16)
+    import torch.distributed as dist
+    M, N = part_bf16.shape
+    out = torch.empty((M // pm.pgm.tp_size, N), dtype=part_bf16.dtype, device=part_bf16.device)
+    dist.reduce_scatter_tensor(out, part_bf16.contiguous(), group=pm.pgm.tp_group)
+    return out
+
+
+def _all_gather_rows(local, keep: bool = False):
+    """[Ml, ...] -> [n * Ml, ...] in rank order.  ``keep``: return a private copy (saved for backward)."""
+    symm = pm.pgm.symm
+    if symm is not None and local.numel() * local.element_size() * symm.n <= symm.ag_bytes:
+        full = symm.all_gather_into_buffer(local)
+        return full.clone() if keep else full
+    import torch.distributed as dist
+    local = local.contiguous()
+    out = torch.empty((pm.pgm.tp_size * local.shape[0],) + tuple(local.shape[1:]), dtype=local.dtype,
+                      device=local.device)
+    dist.all_gather_into_tensor(out, local, group=pm.pgm.tp_group)
+    return out
+
+
+def _partial_out(M, N):
+    """Where a row-parallel GEMM writes its partial sums: straight into the symmetric buffer when there is one."""
+    symm = pm.pgm.symm
+    if symm is not None and M * N * 2 <= symm.ag_off:
+        return symm.buffer((M, N), BF16)
+    return torch.empty((M, N), dtype=BF16, device=torch.device("cuda", torch.cuda.current_device()))
+
+
+def _rowpar_rs(a_bf16, w_bf16, b_mn_major=False):
+    """reduce_scatter_rows(a @ W^T)  (or a @ W when b_mn_major)."""
+    M = a_bf16.shape[0]
+    N = w_bf16.shape[1] if b_mn_major else w_bf16.shape[0]
+    part = _partial_out(M, N)
+    gemm_nt(a_bf16, w_bf16, b_mn_major=b_mn_major, out=part)
+    return _reduce_scatter_rows(part)
+
+
+class FusedLayerSPFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x_l, pos, rt, pack: LayerPack, meta: Meta, *params):
+        m = meta
+        h1_l, rstd1 = fused.rmsnorm_fwd(x_l, pack.s1, rt.eps)
+        h1 = _all_gather_rows(h1_l, keep=True)
+        qkv = gemm_nt(h1, pack.wqkv, bias=pack.bqkv, out_dtype=BF16)
+        fused.rope_inplace(qkv, pos, rt.cos_half, rt.sin_half, 2, m.Dl, m.Hl, m.hd, inverse=False)
+        attn, lse = attn_fwd(qkv, m.B, m.T, m.Hl, m.hd, m.scale)
+        y_l = _rowpar_rs(attn, pack.wo)
+        x2_l, h2_l, rstd2 = fused.add_rmsnorm_fwd(x_l, y_l, pack.bo, pack.s2, rt.eps)
+        h2 = _all_gather_rows(h2_l, keep=True)
+        gu = gemm_nt(h2, pack.wgu, bias=pack.bgu, out_dtype=BF16)
+        act = fused.swiglu_fwd(gu)
+        y_l = _rowpar_rs(act, pack.wd)
+        x3_l, _, _ = fused.add_rmsnorm_fwd(x2_l, y_l, pack.bd, None, rt.eps, want_norm=False)
+        ctx.save_for_backward(x_l, pos, h1, rstd1, qkv, attn, lse, x2_l, h2, rstd2, gu, act)
+        ctx.pack, ctx.meta, ctx.rt = pack, meta, rt
+        return x3_l
+
+    @staticmethod
+    def backward(ctx, dx3_l):
+        x_l, pos, h1, rstd1, qkv, attn, lse, x2_l, h2, rstd2, gu, act = ctx.saved_tensors
+        pack, m, rt = ctx.pack, ctx.meta, ctx.rt
+        dx3_l = dx3_l.contiguous()
+        dx3 = _all_gather_rows(fused.cast_to_bf16(dx3_l))                              # [M, d] bf16
+        dact = gemm_nt(dx3, pack.wd, b_mn_major=True, out_dtype=BF16)
+        _wgrad(dx3, act, pack.g_wd)
+        fused.colsum(dx3, out=pack.g_bd)
+        dgu = fused.swiglu_bwd(dact, gu)
+        del dact
+        dh2_l = _rowpar_rs(dgu, pack.wgu, b_mn_major=True)                               # [Ml, d]
+        _wgrad(dgu, h2, pack.g_wgu)
+        fused.colsum(dgu, out=pack.g_bgu)
+        del dgu
+        dx2_l, dx2_lb, _ = fused.rmsnorm_bwd(dh2_l, x2_l, rstd2, pack.s2, dres=dx3_l, want_fp32=True, want_bf16=True,
+                                             dscale_out=pack.g_s2)
+        dx2 = _all_gather_rows(dx2_lb)
+        dattn = gemm_nt(dx2, pack.wo, b_mn_major=True, out_dtype=BF16)
+        _wgrad(dx2, attn, pack.g_wo)
+        fused.colsum(dx2, out=pack.g_bo)
+        dqkv = attn_bwd(qkv, attn, dattn, lse, m.B, m.T, m.Hl, m.hd, m.scale)
+        fused.rope_inplace(dqkv, pos, rt.cos_half, rt.sin_half, 2, m.Dl, m.Hl, m.hd, inverse=True)
+        dh1_l = _rowpar_rs(dqkv, pack.wqkv, b_mn_major=True)
+        _wgrad(dqkv, h1, pack.g_wqkv)
+        fused.colsum(dqkv, out=pack.g_bqkv)
+        dx_l, _, _ = fused.rmsnorm_bwd(dh1_l, x_l, rstd1, pack.s1, dres=dx2_l, want_fp32=True, want_bf16=False,
+                                       dscale_out=pack.g_s1)
+        return (dx_l, None, None, None, None) + (None,) * len(pack.params)
+
+
+class FusedEmbedSPFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, ids_flat, rt, weight):
+        emb = rt.model.embedding
+        M, D = ids_flat.numel(), weight.shape[1]
+        part = _partial_out(M, D)
+        fused.embedding_fwd(ids_flat, weight.detach(), emb.vocab_st_idx, emb.vocab_ed_idx, out=part)
+        x_l = _reduce_scatter_rows(part).float()       # exact: one owner per row
+        ctx.save_for_backward(ids_flat)
+        ctx.rt = rt
+        return x_l
+
+    @staticmethod
+    def backward(ctx, dx_l):
+        (ids_flat,) = ctx.saved_tensors
+        rt = ctx.rt
+        emb = rt.model.embedding
+        dx = _all_gather_rows(dx_l.contiguous())       # fp32 [M, d]
+        fused.embedding_bwd(ids_flat, dx, emb.weight.shape[0], emb.vocab_st_idx, emb.vocab_ed_idx, dweight=rt.g_emb,
+                            zero_first=True)
+        # last node of the backward pass: complete the RMSNorm scale gradients (partial sums over local rows)
+        comm_ops.all_reduce_sum_(rt.arena.norm_grads)
+        return None, None, None
+
+
+class FusedHeadLossSPFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x_l, targets_flat, rt, ignore_index, *params):
+        n = pm.pgm.tp_size
+        head = rt.model.lm_head
+        Vl = head.odim_partition
+        vocab_start = pm.pgm.tp_rank * Vl
+        h_l, rstd = fused.rmsnorm_fwd(x_l, rt.sN, rt.eps)
+        h = _all_gather_rows(h_l, keep=True)
+        logits = gemm_nt(h, rt.wlm, bias=rt.blm, out_dtype=F32)
+        stats, loss_acc = fused.ce_stats(logits, targets_flat, vocab_start, ignore_index)
+        symm = pm.pgm.symm
+        all_stats = symm.all_gather_rows(stats) if symm is not None else comm_ops.all_gather_rows(stats)
+        fused.ce_loss(targets_flat, all_stats, n, loss_acc, ignore_index)
+        loss = loss_acc[0] / loss_acc[1]
+        ctx.save_for_backward(x_l, targets_flat, h, rstd, logits, all_stats, loss_acc)
+        ctx.rt, ctx.ignore_index, ctx.vocab_start = rt, ignore_index, vocab_start
+        return loss
+
+    @staticmethod
+    def backward(ctx, gout):
+        x_l, targets_flat, h, rstd, logits, all_stats, loss_acc = ctx.saved_tensors
+        rt = ctx.rt
+        n = pm.pgm.tp_size
+        up = gout.detach().reshape(1).float().contiguous()
+        dlogits = fused.ce_grad(logits, targets_flat, all_stats, n, loss_acc, ctx.vocab_start, ctx.ignore_index,
+                                upstream=up)
+        dh_l = _rowpar_rs(dlogits, rt.wlm, b_mn_major=True)
+        _wgrad(dlogits, h, rt.g_wlm)
+        fused.colsum(dlogits, out=rt.g_blm)
+        dx_l, _, _ = fused.rmsnorm_bwd(dh_l, x_l, rstd, rt.sN, dres=None, want_fp32=True, dscale_out=rt.g_sN)
+        return (dx_l, None, None, None) + (None,) * 3

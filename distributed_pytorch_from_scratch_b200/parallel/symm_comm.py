@@ -38,7 +38,11 @@ class SymmComm:
         self.mc_base = int(getattr(data_hdl, "multicast_ptr", 0) or 0)
         self.flag_ptrs = (ctypes.c_ulonglong * 8)(*([int(p) for p in flags_hdl.buffer_ptrs] + [0] * (8 - n)))
         self.data_ptrs = (ctypes.c_ulonglong * 8)(*([int(p) for p in data_hdl.buffer_ptrs] + [0] * (8 - n)))
-        self.gather_off = self.capacity - self.capacity // 8        # last 1/8th: all-gather landing zone
+        # layout: [0, ag_off) collective inputs / GEMM partials | [ag_off, gather_off) sequence-parallel all-gather
+        # landing zone | [gather_off, capacity) small all-gathers (cross-entropy statistics)
+        self.gather_off = self.capacity - self.capacity // 16
+        self.ag_off = (self.capacity // 2) // 256 * 256
+        self.ag_bytes = self.gather_off - self.ag_off
         self.closed = False
         # data path of the reduce: "p2p" (plain NVLink loads/stores, rank-ordered fp32 sums) or "nvls" (multimem.*)
         self.mode = os.environ.get("DPFS_AR_MODE", "p2p")
@@ -81,7 +85,7 @@ class SymmComm:
         for s in shape:
             numel *= s
         nbytes = numel * torch.empty((), dtype=dtype).element_size()
-        assert offset_bytes % 256 == 0 and offset_bytes + nbytes <= self.gather_off, "symmetric buffer too small"
+        assert offset_bytes % 256 == 0 and offset_bytes + nbytes <= self.ag_off, "symmetric buffer too small"
         return self.data[offset_bytes:offset_bytes + nbytes].view(dtype).view(*shape)
 
     def _inside(self, t: torch.Tensor) -> bool:
@@ -91,7 +95,7 @@ class SymmComm:
     def supports(self, t: torch.Tensor) -> bool:
         nbytes = t.numel() * t.element_size()
         return (not self.closed and t.is_cuda and t.dtype in (BF16, F32) and nbytes % 16 == 0
-                and nbytes <= self.gather_off and t.is_contiguous())
+                and nbytes <= self.ag_off and t.is_contiguous())
 
     # ------------------------------------------------------------------------------------------ collectives
     def all_reduce(self, t: torch.Tensor, out: Optional[torch.Tensor] = None) -> torch.Tensor:
@@ -137,7 +141,7 @@ class SymmComm:
         M = a.shape[0]
         N = w.shape[1] if b_mn_major else w.shape[0]
         tiles = ((M + 127) // 128) * ((N + 127) // 128)
-        return N % 8 == 0 and M * N * 2 <= self.gather_off and tiles <= 16384
+        return N % 8 == 0 and M * N * 2 <= self.ag_off and tiles <= 16384
 
     def gemm_allreduce(self, a: torch.Tensor, w: torch.Tensor, b_mn_major: bool = False, bn: int = 0) -> torch.Tensor:
         """all_reduce(a @ w^T) (or a @ w when ``b_mn_major``) in ONE kernel; the result is a view of the symmetric
@@ -152,6 +156,32 @@ class SymmComm:
                                                  self.rank, self.n, bn, _lib.stream())
         _lib.check(rc, "dpfs_gemm_allreduce_bf16")
         return out
+
+    # ------------------------------------------------------------------------------------------ sequence parallel
+    def reduce_scatter_rows(self, partial: torch.Tensor) -> torch.Tensor:
+        """partial: bf16 [M, N] living in the symmetric buffer (each rank's partial sums) -> this rank's reduced block
+        of rows, bf16 [M / n, N] in private memory."""
+        assert self._inside(partial) and partial.dtype == BF16 and partial.is_contiguous()
+        assert self.n in (2, 4, 8), "the P2P reduce-scatter kernel is instantiated for 2, 4 and 8 ranks"
+        M, N = partial.shape
+        assert M % self.n == 0
+        out = torch.empty((M // self.n, N), dtype=BF16, device=partial.device)
+        rc = _lib.lib().dpfs_reduce_scatter_p2p(self.data_ptrs, partial.data_ptr() - self.base, M * N * 2,
+                                                out.data_ptr(), self.flag_ptrs, self.rank, self.n, _lib.stream())
+        _lib.check(rc, "dpfs_reduce_scatter_p2p")
+        return out
+
+    def all_gather_into_buffer(self, local: torch.Tensor) -> torch.Tensor:
+        """local: [Ml, ...] (any dtype) -> view [n * Ml, ...] of the symmetric landing zone holding every rank's block
+        in rank order.  The view is overwritten by the next all-gather: consume (or clone) it first."""
+        local = local.contiguous()
+        nbytes = local.numel() * local.element_size()
+        assert nbytes % 16 == 0 and nbytes * self.n <= self.ag_bytes, "all-gather landing zone too small"
+        rc = _lib.lib().dpfs_allgather_p2p(local.data_ptr(), self.data_ptrs, self.ag_off, nbytes, self.flag_ptrs,
+                                           self.rank, self.n, _lib.stream())
+        _lib.check(rc, "dpfs_allgather_p2p")
+        shape = (self.n * local.shape[0],) + tuple(local.shape[1:])
+        return self.data[self.ag_off:self.ag_off + nbytes * self.n].view(local.dtype).view(shape)
 
     def barrier(self):
         _lib.check(_lib.lib().dpfs_comm_barrier(self.flag_ptrs, self.rank, self.n, _lib.stream()), "dpfs_comm_barrier")

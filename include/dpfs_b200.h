@@ -54,6 +54,12 @@ int dpfs_allreduce_nvls(void* mc_ptr, long long nbytes, int is_bf16, const unsig
 /* Same all-reduce over plain peer loads / stores (fp32 accumulation in rank order; n in {2,4,8}). */
 int dpfs_allreduce_p2p(const unsigned long long* data_ptrs, long long offset, long long nbytes, int is_bf16,
                        const unsigned long long* flag_ptrs, int rank, int n, cudaStream_t stream);
+/* Sequence-parallel halves of the all-reduce.  reduce-scatter: out (local bf16, nbytes_total / n bytes) = sum over
+ * ranks of this rank's block of rows of the symmetric partial matrix at `offset`.  all-gather: every rank's
+ * nbytes_per_rank block lands in slot `rank` of every rank's symmetric buffer at dst_offset.  No counterpart in the
+ * reference (it has no sequence parallelism; SURVEY §2.3 lists it as a required extension). */
+int dpfs_reduce_scatter_p2p(const unsigned long long* data_ptrs, long long offset, long long nbytes_total, void* out,
+                            const unsigned long long* flag_ptrs, int rank, int n, cudaStream_t stream);
 int dpfs_allgather_p2p(const void* src, const unsigned long long* data_ptrs, long long dst_offset,
                        long long nbytes_per_rank, const unsigned long long* flag_ptrs, int rank, int n,
                        cudaStream_t stream);

@@ -39,7 +39,7 @@ def _comm_worker(rank, world):
         assert (out.float() - ref).abs().max().item() < 0.03 * ref.abs().max().item()
 
 
-def _model_worker(rank, world, comm):
+def _model_worker(rank, world, comm, sp=False):
     import process_manager as pm
     from distributed_pytorch_from_scratch_b200.engine import TrainStep
     from distributed_pytorch_from_scratch_b200.ops.optim import FusedAdam
@@ -51,7 +51,7 @@ def _model_worker(rank, world, comm):
     torch.manual_seed(0)
     torch.cuda.manual_seed(0)
     state, cstate = torch.get_rng_state(), torch.cuda.get_rng_state()
-    model = Transformer(**cfg).cuda()
+    model = Transformer(**cfg, sequence_parallel=sp).cuda()
     torch.set_rng_state(state); torch.cuda.set_rng_state(cstate)
     model.reset_parameters()
     van = VallinaTransformer(**cfg).cuda()
@@ -84,7 +84,7 @@ def _model_worker(rank, world, comm):
     # in train.py: the step is captured before any eager backward has run on the default stream
     del model
     torch.set_rng_state(state); torch.cuda.set_rng_state(cstate)
-    model = Transformer(**cfg).cuda()
+    model = Transformer(**cfg, sequence_parallel=sp).cuda()
     model.reset_parameters()
     model.compute_dtype = torch.bfloat16
     opt = FusedAdam.for_model(model, lr=1e-3)
@@ -103,6 +103,12 @@ def test_symm_collectives_and_fused_gemm_allreduce():
 @pytest.mark.parametrize("comm", ["nccl", "fused"])
 def test_tp2_fused_transformer_matches_oracle(comm):
     run_distributed(_model_worker, 2, free_port(), backend="nccl", args=(comm,))
+
+
+@pytest.mark.skipif(_ngpu() < 2, reason="needs >= 2 GPUs")
+@pytest.mark.parametrize("comm", ["nccl", "fused"])
+def test_tp2_sequence_parallel_matches_oracle(comm):
+    run_distributed(_model_worker, 2, free_port(), backend="nccl", args=(comm, True))
 
 
 @pytest.mark.skipif(_ngpu() < 4, reason="needs >= 4 GPUs")
