@@ -1,0 +1,436 @@
+// 2-SM (cta_group::2) variant of the bf16 GEMM: a thread-block cluster of two CTAs on one TPC computes a 256x256 output
+// tile with ONE stream of tcgen05.mma.cta_group::2 instructions issued by the leader CTA.  Each CTA stages only its own
+// 128 rows of A and HALF of the B tile (128 of the 256 N rows), so the L2->SMEM operand traffic per FLOP is 2/3 of the
+// 1-SM 128x256 kernel — the 1-SM kernel is bound by exactly that traffic on the transformer shapes
+// (profiles/step_breakdown_tp1_r1.md).  Accumulators: 128 lanes x 256 fp32 columns per CTA, double buffered (512 TMEM
+// columns), so the epilogue of tile i still overlaps the main loop of tile i+1.
+//
+// Pipeline (per CTA): warp 0 = TMA producer (both CTAs load; transaction bytes of BOTH land on the leader's full
+// barrier), warp 1 = MMA issuer (leader CTA only) + TMEM owner (both CTAs allocate with cta_group::2), warps 2-5 =
+// epilogue.  tcgen05.commit multicasts "slot free" / "accumulator ready" to the same barrier offsets in both CTAs; the
+// follower's epilogue warps release the accumulator with a remote mbarrier arrive on the leader.
+//
+// Same operand-major options and epilogues as gemm_tcgen05.cu (ref: F.linear in models/layers.py:49,93).
+#include "common.cuh"
+#include "dpfs_b200.h"
+
+#include <cudaTypedefs.h>
+
+namespace dpfs {
+
+int make_tmap_bf16_2d(CUtensorMap* tm, const void* ptr, uint64_t inner, uint64_t outer, uint64_t ld_elems,
+                      uint32_t box_inner, uint32_t box_outer);
+int num_sms();
+
+namespace sm2 {
+
+constexpr int BM = 128;   // rows per CTA (256 per cluster)
+constexpr int BNH = 128;  // B rows staged per CTA (half of the 256-wide tile)
+constexpr int BN = 256;
+constexpr int BK = 64;
+constexpr int kThreads = 192;
+constexpr int kStages = 6;
+constexpr int kABytes = BM * BK * 2;
+constexpr int kBBytes = BNH * BK * 2;
+constexpr int kStageBytes = kABytes + kBBytes;
+constexpr int kSmem = kStages * kStageBytes + 256 + 1024;
+constexpr uint32_t kPeerMask = 0xFEFFFFFFu;  // clears the CTA-rank bit of a shared-window address -> leader CTA's copy
+
+struct Args {
+  int M, N, K;
+  int splits, kb_per_split;
+  void* out;
+  long long ldo, split_stride;
+  const float* bias;
+  const float* residual;
+  long long ldr;
+};
+
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ void cluster_sync() {
+  asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+  asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_alloc2(uint32_t* smem_dst, uint32_t ncols) {
+  asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(smem_dst)), "r"(ncols)
+               : "memory");
+}
+__device__ __forceinline__ void tmem_relinquish2() {
+  asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc2(uint32_t taddr, uint32_t ncols) {
+  asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(ncols) : "memory");
+}
+__device__ __forceinline__ void umma2_bf16_ss(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc,
+                                              uint32_t accumulate) {
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t"
+      "}\n"
+      :
+      : "r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+// arrive (once all previously issued MMAs completed) on the barrier at this offset in BOTH CTAs of the pair
+__device__ __forceinline__ void umma2_commit_mc(uint64_t* bar) {
+  asm volatile(
+      "tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(
+          smem_u32(bar)),
+      "h"(static_cast<uint16_t>(3))
+      : "memory");
+}
+// TMA tile load whose transaction bytes are accounted on the LEADER CTA's mbarrier
+__device__ __forceinline__ void tma2_load_2d(void* smem_dst, const CUtensorMap* m, uint64_t* bar, int c0, int c1) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], "
+      "[%2];"
+      :
+      : "r"(smem_u32(smem_dst)), "l"(reinterpret_cast<uint64_t>(m)), "r"(smem_u32(bar) & kPeerMask), "r"(c0), "r"(c1)
+      : "memory");
+}
+__device__ __forceinline__ void mbar_arrive_leader(uint64_t* bar) {
+  asm volatile("mbarrier.arrive.shared::cluster.b64 _, [%0];" ::"r"(smem_u32(bar) & kPeerMask) : "memory");
+}
+
+template <typename OutT>
+__device__ __forceinline__ void store32(OutT* dst, const float (&v)[32], int ncols_valid);
+template <>
+__device__ __forceinline__ void store32<float>(float* dst, const float (&v)[32], int ncols_valid) {
+#pragma unroll
+  for (int j = 0; j < 8; ++j)
+    if (j * 4 + 4 <= ncols_valid)
+      *reinterpret_cast<float4*>(dst + 4 * j) = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+}
+template <>
+__device__ __forceinline__ void store32<__nv_bfloat16>(__nv_bfloat16* dst, const float (&v)[32], int ncols_valid) {
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    if (j * 8 + 8 <= ncols_valid) {
+      uint4 o;
+      o.x = pack_bf16(v[8 * j + 0], v[8 * j + 1]);
+      o.y = pack_bf16(v[8 * j + 2], v[8 * j + 3]);
+      o.z = pack_bf16(v[8 * j + 4], v[8 * j + 5]);
+      o.w = pack_bf16(v[8 * j + 6], v[8 * j + 7]);
+      *reinterpret_cast<uint4*>(dst + 8 * j) = o;
+    }
+  }
+}
+
+template <bool A_MN, bool B_MN, typename OutT>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
+gemm2sm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const Args args) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* sA = smem;
+  uint8_t* sB = smem + kStages * kABytes;
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + kStages * kStageBytes);  // used on the leader only
+  uint64_t* empty_bar = full_bar + kStages;
+  uint64_t* tmem_full = empty_bar + kStages;
+  uint64_t* tmem_empty = tmem_full + 2;  // used on the leader only
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty + 2);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t cta = cluster_ctarank();
+  const bool leader = cta == 0;
+  const int cluster_id = blockIdx.x >> 1, n_clusters = gridDim.x >> 1;
+
+  const int tiles_m = (args.M + 2 * BM - 1) / (2 * BM);
+  const int tiles_n = (args.N + BN - 1) / BN;
+  const int tiles_mn = tiles_m * tiles_n;
+  const int num_work = tiles_mn * args.splits;
+  const int kb_total = (args.K + BK - 1) / BK;
+
+  if (threadIdx.x == 0) {
+    prefetch_tmap(&tmA);
+    prefetch_tmap(&tmB);
+    for (int i = 0; i < kStages; ++i) {
+      mbar_init(&full_bar[i], 1);
+      mbar_init(&empty_bar[i], 1);
+    }
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(&tmem_full[i], 1);
+      mbar_init(&tmem_empty[i], 8);  // 4 epilogue warps x 2 CTAs
+    }
+    fence_mbar_init();
+  }
+  if (warp == 1) {
+    tmem_alloc2(tmem_slot, 2 * BN);
+    tmem_relinquish2();
+  }
+  tc_fence_before();
+  cluster_sync();  // barriers of both CTAs initialised, TMEM allocated, before any cross-CTA signal
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int w = cluster_id; w < num_work; w += n_clusters) {
+        const int split = w / tiles_mn;
+        const int t = w - split * tiles_mn;
+        const int m0 = (t / tiles_n) * (2 * BM) + cta * BM;   // this CTA's 128 rows of the 256-row tile
+        const int n0 = (t % tiles_n) * BN + cta * BNH;        // this CTA's half of the B tile
+        const int kb0 = split * args.kb_per_split;
+        const int kb1 = min(kb_total, kb0 + args.kb_per_split);
+        for (int kb = kb0; kb < kb1; ++kb) {
+          mbar_wait(&empty_bar[stage], phase ^ 1);
+          if (leader) mbar_expect_tx(&full_bar[stage], 2 * kStageBytes);  // bytes of both CTAs
+          uint8_t* a_dst = sA + stage * kABytes;
+          uint8_t* b_dst = sB + stage * kBBytes;
+          if constexpr (!A_MN) {
+            tma2_load_2d(a_dst, &tmA, &full_bar[stage], kb * BK, m0);
+          } else {
+#pragma unroll
+            for (int b = 0; b < BM / 64; ++b)
+              tma2_load_2d(a_dst + b * (BK * 128), &tmA, &full_bar[stage], m0 + 64 * b, kb * BK);
+          }
+          if constexpr (!B_MN) {
+            tma2_load_2d(b_dst, &tmB, &full_bar[stage], kb * BK, n0);
+          } else {
+#pragma unroll
+            for (int b = 0; b < BNH / 64; ++b)
+              tma2_load_2d(b_dst + b * (BK * 128), &tmB, &full_bar[stage], n0 + 64 * b, kb * BK);
+          }
+          if (++stage == kStages) {
+            stage = 0;
+            phase ^= 1;
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (leader && lane == 0) {
+      constexpr uint32_t idesc = make_idesc_bf16(2 * BM, BN, A_MN, B_MN);
+      int stage = 0;
+      uint32_t phase = 0;
+      int as = 0;
+      uint32_t aphase = 0;
+      for (int w = cluster_id; w < num_work; w += n_clusters) {
+        const int split = w / tiles_mn;
+        const int kb0 = split * args.kb_per_split;
+        const int kb1 = min(kb_total, kb0 + args.kb_per_split);
+        mbar_wait(&tmem_empty[as], aphase ^ 1);
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + as * BN;
+        for (int kb = kb0; kb < kb1; ++kb) {
+          mbar_wait(&full_bar[stage], phase);
+          tc_fence_after();
+          const uint32_t a_base = smem_u32(sA + stage * kABytes);
+          const uint32_t b_base = smem_u32(sB + stage * kBBytes);
+#pragma unroll
+          for (int k = 0; k < BK / 16; ++k) {
+            const uint64_t adesc = A_MN ? make_smem_desc_sw128(a_base + k * 2048, BK * 128, 1024)
+                                        : make_smem_desc_sw128(a_base + k * 32, 0, 1024);
+            const uint64_t bdesc = B_MN ? make_smem_desc_sw128(b_base + k * 2048, BK * 128, 1024)
+                                        : make_smem_desc_sw128(b_base + k * 32, 0, 1024);
+            umma2_bf16_ss(d_tmem, adesc, bdesc, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
+          }
+          umma2_commit_mc(&empty_bar[stage]);  // frees this slot in both CTAs
+          if (++stage == kStages) {
+            stage = 0;
+            phase ^= 1;
+          }
+        }
+        umma2_commit_mc(&tmem_full[as]);  // accumulators of both CTAs complete
+        if (++as == 2) {
+          as = 0;
+          aphase ^= 1;
+        }
+      }
+    }
+  } else {
+    const int q = warp & 3;
+    int as = 0;
+    uint32_t aphase = 0;
+    OutT* out = reinterpret_cast<OutT*>(args.out);
+    for (int w = cluster_id; w < num_work; w += n_clusters) {
+      const int split = w / tiles_mn;
+      const int t = w - split * tiles_mn;
+      const int m0 = (t / tiles_n) * (2 * BM) + cta * BM;
+      const int n0 = (t % tiles_n) * BN;
+      const int row = m0 + q * 32 + lane;
+      mbar_wait(&tmem_full[as], aphase);
+      tc_fence_after();
+      const uint32_t t_addr = tmem_base + as * BN + (static_cast<uint32_t>(q * 32) << 16);
+      OutT* orow = out + split * args.split_stride + static_cast<long long>(row) * args.ldo + n0;
+      const float* rrow = args.residual ? args.residual + static_cast<long long>(row) * args.ldr + n0 : nullptr;
+#pragma unroll 1
+      for (int c = 0; c < BN / 32; ++c) {
+        uint32_t r[32];
+        tmem_ld32(t_addr + c * 32, r);
+        tmem_ld_wait();
+        const int ncols_valid = args.N - (n0 + c * 32);
+        if (row < args.M && ncols_valid > 0) {
+          float v[32];
+#pragma unroll
+          for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
+          if (args.bias) {
+#pragma unroll
+            for (int j = 0; j < 32; ++j)
+              if (j < ncols_valid) v[j] += __ldg(args.bias + n0 + c * 32 + j);
+          }
+          if (rrow) {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+              if (j * 4 + 4 <= ncols_valid) {
+                const float4 rv = *reinterpret_cast<const float4*>(rrow + c * 32 + 4 * j);
+                v[4 * j] += rv.x;
+                v[4 * j + 1] += rv.y;
+                v[4 * j + 2] += rv.z;
+                v[4 * j + 3] += rv.w;
+              }
+            }
+          }
+          store32<OutT>(orow + c * 32, v, ncols_valid);
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive_leader(&tmem_empty[as]);
+      if (++as == 2) {
+        as = 0;
+        aphase ^= 1;
+      }
+    }
+  }
+
+  tc_fence_before();
+  cluster_sync();  // no CTA frees TMEM / exits while its peer may still touch its barriers or shared memory
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc2(tmem_base, 2 * BN);
+  }
+}
+
+template <bool A_MN, bool B_MN, typename OutT>
+static int launch(const CUtensorMap& tmA, const CUtensorMap& tmB, const Args& args, cudaStream_t stream) {
+  auto kfn = gemm2sm_kernel<A_MN, B_MN, OutT>;
+  static bool configured = false;
+  if (!configured) {
+    cudaError_t e = cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem);
+    if (e != cudaSuccess) return static_cast<int>(e);
+    configured = true;
+  }
+  const int work = ((args.M + 2 * BM - 1) / (2 * BM)) * ((args.N + BN - 1) / BN) * args.splits;
+  int clusters = num_sms() / 2;
+  if (work < clusters) clusters = work;
+  kfn<<<(DPFS_COUNT(), 2 * clusters), kThreads, kSmem, stream>>>(tmA, tmB, args);
+  return static_cast<int>(cudaGetLastError());
+}
+
+template <typename OutT>
+static int dispatch(bool a_mn, bool b_mn, const CUtensorMap& tmA, const CUtensorMap& tmB, const Args& args,
+                    cudaStream_t stream) {
+  if (!a_mn && !b_mn) return launch<false, false, OutT>(tmA, tmB, args, stream);
+  if (!a_mn && b_mn) return launch<false, true, OutT>(tmA, tmB, args, stream);
+  if (a_mn && b_mn) return launch<true, true, OutT>(tmA, tmB, args, stream);
+  return launch<true, false, OutT>(tmA, tmB, args, stream);
+}
+
+// fp32 split-K partial sums -> final output (same contract as the 1-SM kernel's reducer)
+template <typename OutT>
+__global__ void splitk_reduce2_kernel(const float* __restrict__ ws, OutT* __restrict__ out, long long ldo,
+                                      const float* __restrict__ bias, int M, int N, int splits) {
+  const long long total4 = static_cast<long long>(M) * N / 4;
+  const long long slab = static_cast<long long>(M) * N;
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total4;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    float4 acc = *reinterpret_cast<const float4*>(ws + i * 4);
+    for (int s = 1; s < splits; ++s) {
+      const float4 p = *reinterpret_cast<const float4*>(ws + s * slab + i * 4);
+      acc.x += p.x;
+      acc.y += p.y;
+      acc.z += p.z;
+      acc.w += p.w;
+    }
+    const long long e = i * 4;
+    const int r = static_cast<int>(e / N), c = static_cast<int>(e % N);
+    if (bias) {
+      acc.x += bias[c];
+      acc.y += bias[c + 1];
+      acc.z += bias[c + 2];
+      acc.w += bias[c + 3];
+    }
+    OutT* o = out + static_cast<long long>(r) * ldo + c;
+    if constexpr (sizeof(OutT) == 4) {
+      *reinterpret_cast<float4*>(o) = acc;
+    } else {
+      uint2 pk;
+      pk.x = pack_bf16(acc.x, acc.y);
+      pk.y = pack_bf16(acc.z, acc.w);
+      *reinterpret_cast<uint2*>(o) = pk;
+    }
+  }
+}
+
+}  // namespace sm2
+}  // namespace dpfs
+
+using namespace dpfs;
+
+// Same contract as dpfs_gemm_bf16 (without the N-tile choice): 256x256 tiles on CTA pairs.
+extern "C" int dpfs_gemm2sm_bf16(const void* A, long long lda, int a_mn_major, const void* B, long long ldb,
+                                 int b_mn_major, void* out, long long ldo, int out_fp32, const float* bias,
+                                 const float* residual, long long ldr, int M, int N, int K, int splits,
+                                 float* workspace, cudaStream_t stream) {
+  using namespace dpfs::sm2;
+  if (M <= 0 || N <= 0 || K <= 0) return 0;
+  if ((N % 8) != 0 || (lda % 8) != 0 || (ldb % 8) != 0 || (ldo % (out_fp32 ? 4 : 8)) != 0) return -10;
+  if (splits < 1) splits = 1;
+  const int kb_total = (K + BK - 1) / BK;
+  if (splits > kb_total) splits = kb_total;
+  const int kb_per_split = (kb_total + splits - 1) / splits;
+  splits = (kb_total + kb_per_split - 1) / kb_per_split;
+  if (splits > 1 && workspace == nullptr) return -11;
+  CUtensorMap tmA, tmB;
+  int rc = !a_mn_major ? make_tmap_bf16_2d(&tmA, A, K, M, lda, 64, BM) : make_tmap_bf16_2d(&tmA, A, M, K, lda, 64, BK);
+  if (rc) return rc;
+  rc = !b_mn_major ? make_tmap_bf16_2d(&tmB, B, K, N, ldb, 64, BNH) : make_tmap_bf16_2d(&tmB, B, N, K, ldb, 64, BK);
+  if (rc) return rc;
+  Args args;
+  args.M = M;
+  args.N = N;
+  args.K = K;
+  args.splits = splits;
+  args.kb_per_split = kb_per_split;
+  args.bias = bias;
+  args.residual = residual;
+  args.ldr = ldr;
+  const bool direct = splits == 1;
+  if (direct) {
+    args.out = out;
+    args.ldo = ldo;
+    args.split_stride = 0;
+  } else {
+    if (residual) return -12;
+    args.out = workspace;
+    args.ldo = N;
+    args.split_stride = static_cast<long long>(M) * N;
+    args.bias = nullptr;
+    args.residual = nullptr;
+  }
+  const bool kernel_fp32 = direct ? (out_fp32 != 0) : true;
+  rc = kernel_fp32 ? dispatch<float>(a_mn_major, b_mn_major, tmA, tmB, args, stream)
+                   : dispatch<__nv_bfloat16>(a_mn_major, b_mn_major, tmA, tmB, args, stream);
+  if (rc) return rc;
+  if (!direct) {
+    const long long total4 = static_cast<long long>(M) * N / 4;
+    int blocks = static_cast<int>((total4 + 255) / 256);
+    if (blocks > num_sms() * 8) blocks = num_sms() * 8;
+    if (out_fp32)
+      splitk_reduce2_kernel<float><<<(DPFS_COUNT(), blocks), 256, 0, stream>>>(
+          workspace, reinterpret_cast<float*>(out), ldo, bias, M, N, splits);
+    else
+      splitk_reduce2_kernel<__nv_bfloat16><<<(DPFS_COUNT(), blocks), 256, 0, stream>>>(
+          workspace, reinterpret_cast<__nv_bfloat16*>(out), ldo, bias, M, N, splits);
+    rc = static_cast<int>(cudaGetLastError());
+  }
+  return rc;
+}

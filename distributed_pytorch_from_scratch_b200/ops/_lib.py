@@ -25,6 +25,8 @@ c_p = ctypes.c_void_p
 SIGS = {
     "dpfs_gemm_bf16": (c_p, c_ll, c_int, c_p, c_ll, c_int, c_p, c_ll, c_int, c_p, c_p, c_ll, c_int, c_int, c_int,
                        c_int, c_p, c_int, c_p),
+    "dpfs_gemm2sm_bf16": (c_p, c_ll, c_int, c_p, c_ll, c_int, c_p, c_ll, c_int, c_p, c_p, c_ll, c_int, c_int, c_int,
+                          c_int, c_p, c_p),
     "dpfs_gemm_allreduce_bf16": (c_p, c_ll, c_p, c_ll, c_int, c_p, c_p, c_p, c_ll, c_int, c_int, c_int, c_p, c_int,
                                  c_int, c_int, c_p),
     "dpfs_allreduce_p2p": (c_p, c_ll, c_ll, c_int, c_p, c_int, c_int, c_p),

@@ -17,6 +17,7 @@ import os
 
 _WS = {}
 _DEFAULT_BN = int(os.environ.get("DPFS_GEMM_BN", "256"))
+_USE_2SM = os.environ.get("DPFS_GEMM_2SM", "1") == "1"
 
 
 def _workspace(device, nfloats: int) -> torch.Tensor:
@@ -40,7 +41,7 @@ def auto_splits(M: int, N: int, K: int, bn: int = 128) -> int:
 def gemm_nt(a: torch.Tensor, b: torch.Tensor, *, a_mn_major: bool = False, b_mn_major: bool = False,
             out: Optional[torch.Tensor] = None, out_dtype: torch.dtype = torch.bfloat16,
             bias: Optional[torch.Tensor] = None, residual: Optional[torch.Tensor] = None,
-            splits: int = 0, bn: int = 0) -> torch.Tensor:
+            splits: int = 0, bn: int = 0, two_sm: Optional[bool] = None) -> torch.Tensor:
     """out[M,N] = A[M,K] @ B[N,K]^T (+bias) (+residual).
 
     a: [M,K] (K-major) or [K,M] (``a_mn_major``); b: [N,K] or [K,N] (``b_mn_major``); 2-D, bf16, last dim
@@ -70,8 +71,25 @@ def gemm_nt(a: torch.Tensor, b: torch.Tensor, *, a_mn_major: bool = False, b_mn_
     if bn == 0:
         # 128x256 tiles halve the smem operand traffic per MMA (measured 5-40% faster than 128x128 on B200)
         bn = _DEFAULT_BN if (_DEFAULT_BN != 256 or N % 256 == 0) else 128
+    user_splits = splits
     if splits == 0:
         splits = auto_splits(M, N, K, bn or 128) if residual is None else 1
+    if two_sm is None:
+        two_sm = _USE_2SM and M >= 256 and N >= 256
+    if two_sm:
+        if user_splits == 0:   # 74 CTA pairs: split K when the 256x256 tiles alone cannot fill them
+            tiles2 = ((M + 255) // 256) * ((N + 255) // 256)
+            kb = (K + 63) // 64
+            splits = 1
+            if residual is None and tiles2 < 60 and kb >= 8:
+                splits = max(1, min(kb // 4, 148 // tiles2))
+        ws = _workspace(a.device, splits * M * N) if splits > 1 else None
+        rc = _lib.lib().dpfs_gemm2sm_bf16(
+            a.data_ptr(), a.stride(0), int(a_mn_major), b.data_ptr(), b.stride(0), int(b_mn_major),
+            out.data_ptr(), out.stride(0), int(out_fp32), _lib.ptr(bias), _lib.ptr(residual),
+            residual.stride(0) if residual is not None else 0, M, N, K, splits, _lib.ptr(ws), _lib.stream())
+        _lib.check(rc, "dpfs_gemm2sm_bf16")
+        return out
     ws = _workspace(a.device, splits * M * N) if splits > 1 else None
     rc = _lib.lib().dpfs_gemm_bf16(
         a.data_ptr(), a.stride(0), int(a_mn_major), b.data_ptr(), b.stride(0), int(b_mn_major),

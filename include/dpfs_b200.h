@@ -31,6 +31,12 @@ int dpfs_gemm_bf16(const void* A, long long lda, int a_mn_major, const void* B, 
                    long long ldr, int M, int N, int K, int splits, float* workspace, int bn,
                    cudaStream_t stream);
 
+/* Same contract on CTA pairs: a 2-CTA cluster computes 256x256 tiles with tcgen05.mma.cta_group::2; each CTA stages
+ * its 128 rows of A and half of the B tile, i.e. 2/3 of the operand traffic of the 128x256 1-SM kernel. */
+int dpfs_gemm2sm_bf16(const void* A, long long lda, int a_mn_major, const void* B, long long ldb, int b_mn_major,
+                      void* out, long long ldo, int out_fp32, const float* bias, const float* residual,
+                      long long ldr, int M, int N, int K, int splits, float* workspace, cudaStream_t stream);
+
 /* Fused GEMM -> all-reduce over NVLink (one kernel): every rank computes its partial out = A_r B_r^T (bf16) into
  * its symmetric buffer `out` ([M][N], row stride N) and the ranks sum the tiles through the NVSwitch with
  * multimem.ld_reduce / multimem.st on `mc_out` (the multicast alias of `out`).  flag_ptrs: HOST array of the n ranks'

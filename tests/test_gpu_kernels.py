@@ -25,7 +25,8 @@ def test_gemm_tcgen05(a_mn, b_mn, shape):
     b_in = B.t().contiguous() if b_mn else B
     scale = ref.abs().max().item()
     for bn in (128, 256):
-        out = gemm_nt(a_in, b_in, a_mn_major=a_mn, b_mn_major=b_mn, out_dtype=torch.float32, bn=bn, splits=1)
+        out = gemm_nt(a_in, b_in, a_mn_major=a_mn, b_mn_major=b_mn, out_dtype=torch.float32, bn=bn, splits=1,
+                      two_sm=False)
         assert (out - ref).abs().max().item() < 2e-3 * scale
         out = gemm_nt(a_in, b_in, a_mn_major=a_mn, b_mn_major=b_mn, out_dtype=torch.bfloat16, bn=bn, bias=bias,
                       residual=res, splits=1)
@@ -33,6 +34,15 @@ def test_gemm_tcgen05(a_mn, b_mn, shape):
         out = gemm_nt(a_in, b_in, a_mn_major=a_mn, b_mn_major=b_mn, out_dtype=torch.float32, bn=bn, bias=bias,
                       splits=3)
         assert (out - (ref + bias)).abs().max().item() < 2e-3 * scale
+    # 2-SM (cta_group::2, 256x256 tiles on CTA pairs)
+    out = gemm_nt(a_in, b_in, a_mn_major=a_mn, b_mn_major=b_mn, out_dtype=torch.float32, two_sm=True, splits=1)
+    assert (out - ref).abs().max().item() < 2e-3 * scale
+    out = gemm_nt(a_in, b_in, a_mn_major=a_mn, b_mn_major=b_mn, out_dtype=torch.bfloat16, two_sm=True, bias=bias,
+                  residual=res, splits=1)
+    assert (out.float() - (ref + bias + res)).abs().max().item() < 2e-2 * scale
+    out = gemm_nt(a_in, b_in, a_mn_major=a_mn, b_mn_major=b_mn, out_dtype=torch.float32, two_sm=True, bias=bias,
+                  splits=2)
+    assert (out - (ref + bias)).abs().max().item() < 2e-3 * scale
 
 
 @pytest.mark.parametrize("B,T,H,HD", [(1, 128, 1, 64), (2, 200, 2, 64), (2, 1000, 2, 64), (2, 333, 2, 128)])

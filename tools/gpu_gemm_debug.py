@@ -27,7 +27,7 @@ def run_variant(name):
     for (M, N, K) in SHAPES:
         if (a_mn and M % 8) or (b_mn and N % 8) or ((not a_mn or not b_mn) and K % 8):
             continue
-        for bn in (128, 256):
+        for bn in ((128, 256, 512) if not os.environ.get("ONLY_2SM") else (512,)):
             for out_dtype in (torch.bfloat16, torch.float32):
                 A = torch.randn(M, K, device=dev).to(torch.bfloat16)
                 B = torch.randn(N, K, device=dev).to(torch.bfloat16)
@@ -37,16 +37,17 @@ def run_variant(name):
                 res = torch.randn(M, N, device=dev)
                 ref = A.float() @ B.float().t()
                 t0 = time.time()
-                out = gemm_nt(a_in, b_in, a_mn_major=a_mn, b_mn_major=b_mn, out_dtype=out_dtype, bn=bn, splits=1)
+                kw = dict(two_sm=True) if bn == 512 else dict(bn=bn, two_sm=False)
+                out = gemm_nt(a_in, b_in, a_mn_major=a_mn, b_mn_major=b_mn, out_dtype=out_dtype, splits=1, **kw)
                 torch.cuda.synchronize()
                 err = (out.float() - ref).abs().max().item()
                 scale = ref.abs().max().item()
-                out2 = gemm_nt(a_in, b_in, a_mn_major=a_mn, b_mn_major=b_mn, out_dtype=out_dtype, bn=bn,
-                               bias=bias, residual=res, splits=1)
+                out2 = gemm_nt(a_in, b_in, a_mn_major=a_mn, b_mn_major=b_mn, out_dtype=out_dtype,
+                               bias=bias, residual=res, splits=1, **kw)
                 torch.cuda.synchronize()
                 err2 = (out2.float() - (ref + bias + res)).abs().max().item()
-                out3 = gemm_nt(a_in, b_in, a_mn_major=a_mn, b_mn_major=b_mn, out_dtype=out_dtype, bn=bn,
-                               bias=bias, splits=3)
+                out3 = gemm_nt(a_in, b_in, a_mn_major=a_mn, b_mn_major=b_mn, out_dtype=out_dtype,
+                               bias=bias, splits=3, **kw)
                 torch.cuda.synchronize()
                 err3 = (out3.float() - (ref + bias)).abs().max().item()
                 tol = (0.02 if out_dtype == torch.bfloat16 else 2e-3) * max(scale, 1.0)
@@ -77,18 +78,19 @@ def run_variant(name):
                                   f"rows equal to row0: {(o == o[0:1]).all(dim=1).sum().item()}/{M}", flush=True)
     # quick timing of the flagship shapes
     for (M, N, K) in [(32000, 1536, 512), (32000, 512, 2048), (32000, 4096, 512), (8192, 8192, 8192)]:
-        for bn in (128, 256):
+        for bn in (128, 256, 512):
+            kw = dict(two_sm=True) if bn == 512 else dict(bn=bn, two_sm=False)
             A = torch.randn(M, K, device=dev).to(torch.bfloat16)
             B = torch.randn(N, K, device=dev).to(torch.bfloat16)
             a_in = A.t().contiguous() if a_mn else A
             b_in = B.t().contiguous() if b_mn else B
             for _ in range(3):
-                gemm_nt(a_in, b_in, a_mn_major=a_mn, b_mn_major=b_mn, bn=bn, splits=1)
+                gemm_nt(a_in, b_in, a_mn_major=a_mn, b_mn_major=b_mn, splits=1, **kw)
             torch.cuda.synchronize()
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             e0.record()
             for _ in range(10):
-                gemm_nt(a_in, b_in, a_mn_major=a_mn, b_mn_major=b_mn, bn=bn, splits=1)
+                gemm_nt(a_in, b_in, a_mn_major=a_mn, b_mn_major=b_mn, splits=1, **kw)
             e1.record()
             torch.cuda.synchronize()
             ms = e0.elapsed_time(e1) / 10
@@ -105,7 +107,7 @@ if __name__ == "__main__":
         for name in VARIANTS:
             try:
                 p = subprocess.run([sys.executable, __file__, "--variant", name], capture_output=True, text=True,
-                                   timeout=240)
+                                   timeout=120)
                 txt = p.stdout + ("\nSTDERR:\n" + p.stderr[-3000:] if p.returncode != 0 else "")
                 txt += f"\n[{name}] exit code {p.returncode}\n"
             except subprocess.TimeoutExpired as e:
