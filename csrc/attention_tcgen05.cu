@@ -26,6 +26,7 @@ namespace dpfs {
 int num_sms();
 
 constexpr int kAttnThreads = 192;
+constexpr int kAttnBwdThreads = 320;  // warp 0 TMA, warp 1 MMA, warps 2-9: two groups of 4 gradient-math warps
 constexpr int kTile = 128;  // q rows and kv rows per tile
 constexpr float kLog2e = 1.4426950408889634f;
 constexpr float kLn2 = 0.6931471805599453f;
@@ -66,11 +67,20 @@ struct FwdCfg {
   static constexpr int kKVBytes = kTile * HD * 2;  // one K or V tile
   static constexpr int kPBytes = kTile * kTile * 2;
   static constexpr int kSmem = kQBytes + kStages * 2 * kKVBytes + kPBytes + 256 + 1024;
-  static constexpr int kTmemCols = 512;  // S0: [0,128), S1: [128,256), O: [256, 256+HD)
+  // hd = 64: two CTAs per SM (112 KB smem, 256 TMEM columns each, <= 168 registers) give the softmax warps of one CTA
+  // something to overlap with: S is single buffered [0,128), O at [128,192).
+  // hd = 128: one CTA per SM (192 KB smem); S is double buffered [0,128),[128,256) and O sits at [256,384) so QK^T of
+  // tile j+1 overlaps the softmax of tile j inside the CTA.
+  // (measured: two CTAs/SM with a single S buffer were 30% SLOWER for hd = 64 — 193 vs 149 us on the flagship shape —
+  //  so both head sizes use one CTA per SM with a double-buffered S; the single-buffer path is kept for experiments)
+  static constexpr int kSBufs = 2;
+  static constexpr int kTmemCols = 512;
+  static constexpr int kOCol = 256;
+  static constexpr int kCtasPerSm = 1;
 };
 
 template <int HD>
-__global__ void __launch_bounds__(kAttnThreads, 1)
+__global__ void __launch_bounds__(kAttnThreads, FwdCfg<HD>::kCtasPerSm)
 attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, __nv_bfloat16* __restrict__ out,
                 float* __restrict__ lse, int T, int H, int Dl, float scale_log2) {
   using C = FwdCfg<HD>;
@@ -119,7 +129,7 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, __nv_bfloat16* __res
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
-  const uint32_t tS = tmem_base, tO = tmem_base + 256;
+  const uint32_t tS = tmem_base, tO = tmem_base + C::kOCol;
 
   if (warp == 0) {
     if (lane == 0) {
@@ -155,20 +165,23 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, __nv_bfloat16* __res
         umma_bf16_ss(tS, desc_kmajor(q_base, kk, kTile * 128), desc_kmajor(smem_u32(sK), kk, kTile * 128), idesc_s,
                      kk > 0);
       umma_commit(&s_full[0]);
+      auto issue_s = [&](int jn) {
+        const int sn = jn & 1;
+        mbar_wait(&k_full[sn], (jn >> 1) & 1);
+        tc_fence_after();
+        const uint32_t k_base = smem_u32(sK + sn * C::kKVBytes);
+        const uint32_t s_buf = tS + (jn % C::kSBufs) * 128;
+#pragma unroll
+        for (int kk = 0; kk < HD / 16; ++kk)
+          umma_bf16_ss(s_buf, desc_kmajor(q_base, kk, kTile * 128), desc_kmajor(k_base, kk, kTile * 128), idesc_s,
+                       kk > 0);
+        umma_commit(&s_full[jn % C::kSBufs]);
+      };
       for (int j = 0; j < n_kv; ++j) {
         const int st = j & 1;
-        if (j + 1 < n_kv) {
-          // S buffer (j+1)&1 was last read by the softmax of tile j-1, which finished before p_full(j-1)
-          const int sn = (j + 1) & 1;
-          mbar_wait(&k_full[sn], ((j + 1) >> 1) & 1);
-          tc_fence_after();
-          const uint32_t k_base = smem_u32(sK + sn * C::kKVBytes);
-#pragma unroll
-          for (int kk = 0; kk < HD / 16; ++kk)
-            umma_bf16_ss(tS + sn * 128, desc_kmajor(q_base, kk, kTile * 128), desc_kmajor(k_base, kk, kTile * 128),
-                         idesc_s, kk > 0);
-          umma_commit(&s_full[sn]);
-        }
+        // double-buffered S: QK^T of tile j+1 goes out before PV(j) (its buffer was drained before p_full(j-1));
+        // single-buffered S: it has to wait until the softmax of tile j has read S, i.e. until p_full(j)
+        if (C::kSBufs == 2 && j + 1 < n_kv) issue_s(j + 1);
         mbar_wait(p_full, j & 1);
         mbar_wait(&v_full[st], (j >> 1) & 1);
         tc_fence_after();
@@ -179,6 +192,7 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, __nv_bfloat16* __res
                        (j > 0 || kk > 0) ? 1u : 0u);
         umma_commit(o_done);
         umma_commit(&kv_empty[st]);
+        if (C::kSBufs == 1 && j + 1 < n_kv) issue_s(j + 1);
       }
     }
   } else {
@@ -188,13 +202,13 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, __nv_bfloat16* __res
     const uint32_t lane_off = static_cast<uint32_t>(q * 32) << 16;
     float m_run = -INFINITY, l_run = 0.f;
     for (int j = 0; j < n_kv; ++j) {
-      mbar_wait(&s_full[j & 1], (j >> 1) & 1);
+      mbar_wait(&s_full[j % C::kSBufs], (j / C::kSBufs) & 1);
       tc_fence_after();
       float s[kTile];
 #pragma unroll
       for (int c = 0; c < 4; ++c) {
         uint32_t tmp[32];
-        tmem_ld32(tS + (j & 1) * 128 + lane_off + c * 32, tmp);
+        tmem_ld32(tS + (j % C::kSBufs) * 128 + lane_off + c * 32, tmp);
         tmem_ld_wait();
 #pragma unroll
         for (int i = 0; i < 32; ++i) s[c * 32 + i] = __uint_as_float(tmp[i]) * scale_log2;
@@ -341,7 +355,7 @@ __device__ __forceinline__ void red_add_v4(float* addr, float a, float b, float 
 }
 
 template <int HD>
-__global__ void __launch_bounds__(kAttnThreads, 1)
+__global__ void __launch_bounds__(kAttnBwdThreads, 1)
 attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constant__ CUtensorMap tm_do,
                 const float* __restrict__ lse, const float* __restrict__ delta, float* __restrict__ dq_acc,
                 __nv_bfloat16* __restrict__ dqkv, int T, int H, int Dl, float scale, float scale_log2) {
@@ -380,9 +394,9 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
       mbar_init(&qdo_empty[i], 1);
     }
     mbar_init(sdp_full, 1);
-    mbar_init(pds_full, 4);
+    mbar_init(pds_full, 8);
     mbar_init(dq_full, 1);
-    mbar_init(s_free, 4);
+    mbar_init(s_free, 8);
     fence_mbar_init();
   }
   if (warp == 1) {
@@ -454,9 +468,13 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
       }
     }
   } else {
-    const int q = warp & 3;
+    // 8 warps: warp group `half` (0/1) owns kv columns [64*half, 64*half+64) of every row; inside a group warp q owns
+    // TMEM lanes (rows) [32q, 32q+32).  Two warps per SM sub-partition hide each other's exp / TMEM latency.
+    const int q = warp & 3;            // the hardware ties a warp to TMEM lanes [32*(warp%4), +32)
+    const int half = (warp - 2) >> 2;  // warps 2-5 -> 0, warps 6-9 -> 1 (each group covers all four lane quarters)
     const int r = q * 32 + lane;
     const uint32_t lane_off = static_cast<uint32_t>(q * 32) << 16;
+    constexpr int kOutChunks = HD / 64;  // 32-column chunks of dQ / dK / dV per warp group
     for (int it = 0; it < n_it; ++it) {
       const int q0 = (jt + it) * kTile;
       const bool row_valid = (q0 + r) < T;
@@ -466,7 +484,7 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
       mbar_wait(sdp_full, it & 1);
       tc_fence_after();
 #pragma unroll 1
-      for (int c = 0; c < 4; ++c) {
+      for (int c = 2 * half; c < 2 * half + 2; ++c) {
         uint32_t sv[32], dv[32];
         tmem_ld32(tS + lane_off + c * 32, sv);
         tmem_ld32(tDP + lane_off + c * 32, dv);
@@ -496,7 +514,7 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
       tc_fence_after();
       float* dq_row = dq_acc + (static_cast<long long>(b) * T + q0 + r) * Dl + h * HD;
 #pragma unroll 1
-      for (int c = 0; c < HD / 32; ++c) {
+      for (int c = half * kOutChunks; c < (half + 1) * kOutChunks; ++c) {
         uint32_t v[32];
         tmem_ld32(tS + lane_off + c * 32, v);
         tmem_ld_wait();
@@ -519,7 +537,7 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
       const uint32_t tsrc = which == 0 ? tDK : tDV;
       __nv_bfloat16* dst = drow + (which + 1) * Dl;
 #pragma unroll 1
-      for (int c = 0; c < HD / 32; ++c) {
+      for (int c = half * kOutChunks; c < (half + 1) * kOutChunks; ++c) {
         uint32_t v[32];
         tmem_ld32(tsrc + lane_off + c * 32, v);
         tmem_ld_wait();
@@ -603,7 +621,7 @@ static int launch_bwd(const CUtensorMap& tm_qkv, const CUtensorMap& tm_do, const
     configured = true;
   }
   dim3 grid((T + kTile - 1) / kTile, H, B);
-  kfn<<<(DPFS_COUNT(), grid), kAttnThreads, C::kSmem, stream>>>(tm_qkv, tm_do, lse, delta, dq_acc,
+  kfn<<<(DPFS_COUNT(), grid), kAttnBwdThreads, C::kSmem, stream>>>(tm_qkv, tm_do, lse, delta, dq_acc,
                                                reinterpret_cast<__nv_bfloat16*>(dqkv), T, H, H * HD, scale,
                                                scale * kLog2e);
   return static_cast<int>(cudaGetLastError());
