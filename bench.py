@@ -182,7 +182,9 @@ def run_ours(args):
         from distributed_pytorch_from_scratch_b200.parallel.symm import try_enable_symm
         try_enable_symm(required=(args.comm == "fused"))
     margs = ModelArgumments()
-    sp = world > 1 and args.sp == "on"
+    # sequence parallelism pays off once the replicated norm / residual work outweighs the extra collectives:
+    # measured 15.9 vs 17.3 ms at TP=8 and 21.9 vs 20.9 ms at TP=2 (profiles/), so "auto" turns it on from TP=8
+    sp = world > 1 and (args.sp == "on" or (args.sp == "auto" and world >= 8))
     model = Transformer(**asdict(margs), sequence_parallel=sp).cuda()
     model.reset_parameters()
     model.compute_dtype = torch.bfloat16
@@ -346,7 +348,7 @@ def main():
     ap.add_argument("--comm", choices=["auto", "fused", "nccl"], default="auto",
                     help="TP collectives: our NVLink kernels over symmetric memory (fused), NCCL, or auto")
     ap.add_argument("--no-graph", action="store_true", help="run eagerly instead of replaying a CUDA graph")
-    ap.add_argument("--sp", choices=["on", "off"], default="off",
+    ap.add_argument("--sp", choices=["on", "off", "auto"], default="auto",
                     help="Megatron sequence parallelism on top of TP (reduce-scatter / all-gather forms)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)

@@ -106,6 +106,31 @@ __global__ void __launch_bounds__(512) reduce_scatter_p2p_kernel(CommCtx c, Peer
   sync_ranks(c, blockIdx.x);  // nobody overwrites its partial matrix while a peer still reads it
 }
 
+
+// NVLS reduce-scatter: rank r pulls ITS block of rows already summed by the NVSwitch (multimem.ld_reduce) into private
+// memory — each GPU receives only S/n bytes.
+__global__ void __launch_bounds__(512) reduce_scatter_nvls_kernel(CommCtx c, const uint8_t* mc_base,
+                                                                  uint4* __restrict__ out, long long units_per_rank) {
+  sync_ranks(c, blockIdx.x);
+  const uint8_t* src = mc_base + static_cast<long long>(c.rank) * units_per_rank * 16;
+  const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
+  for (long long ub = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; ub < units_per_rank;
+       ub += stride * 8) {
+    uint4 v[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      const long long u = ub + k * stride;
+      if (u < units_per_rank) v[k] = multimem_ld_reduce_bf16x8(src + u * 16);
+    }
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      const long long u = ub + k * stride;
+      if (u < units_per_rank) out[u] = v[k];
+    }
+  }
+  sync_ranks(c, blockIdx.x);
+}
+
 // all-gather: rank r broadcasts its `units` 16-byte units into slot r of every rank's buffer with multimem.st
 __global__ void __launch_bounds__(512) allgather_nvls_kernel(CommCtx c, const uint4* __restrict__ src, uint8_t* mc_base,
                                                              long long units) {
@@ -273,7 +298,7 @@ extern "C" int dpfs_allgather_nvls(const void* src, void* mc_dst, long long nbyt
   if (nbytes_per_rank == 0) return 0;
   const long long units = nbytes_per_rank / 16;
   long long blocks = (units + 511) / 512;
-  if (blocks > 32) blocks = 32;
+  if (blocks > 64) blocks = 64;
   CommCtx c = make_ctx(flag_ptrs, rank, n);
   allgather_nvls_kernel<<<(DPFS_COUNT(), static_cast<int>(blocks)), 512, 0, stream>>>(
       c, static_cast<const uint4*>(src), static_cast<uint8_t*>(mc_dst), units);
@@ -305,6 +330,23 @@ extern "C" int dpfs_reduce_scatter_p2p(const unsigned long long* data_ptrs, long
   if (n == 2) return launch_rs_p2p<2>(c, pp, out, units, stream);
   if (n == 4) return launch_rs_p2p<4>(c, pp, out, units, stream);
   return launch_rs_p2p<8>(c, pp, out, units, stream);
+}
+
+
+extern "C" int dpfs_reduce_scatter_nvls(const void* mc_ptr, long long nbytes_total, void* out,
+                                        const unsigned long long* flag_ptrs, int rank, int n, cudaStream_t stream) {
+  if (n < 2 || n > kMaxRanks) return -50;
+  if (nbytes_total % (16ll * n) != 0 || (reinterpret_cast<uintptr_t>(mc_ptr) & 15) ||
+      (reinterpret_cast<uintptr_t>(out) & 15))
+    return -51;
+  if (nbytes_total == 0) return 0;
+  const long long units = nbytes_total / 16 / n;
+  long long blocks = (units + 511) / 512;
+  if (blocks > 64) blocks = 64;
+  CommCtx c = make_ctx(flag_ptrs, rank, n);
+  reduce_scatter_nvls_kernel<<<(DPFS_COUNT(), static_cast<int>(blocks)), 512, 0, stream>>>(
+      c, static_cast<const uint8_t*>(mc_ptr), static_cast<uint4*>(out), units);
+  return static_cast<int>(cudaGetLastError());
 }
 
 extern "C" int dpfs_allgather_p2p(const void* src, const unsigned long long* data_ptrs, long long dst_offset,

@@ -406,7 +406,7 @@ class FusedRuntime:
 def _reduce_scatter_rows(part_bf16):
     """Sum the ranks' partial [M, N] matrices and keep this rank's block of rows -> [M / n, N] bf16."""
     symm = pm.pgm.symm
-    if symm is not None and symm._inside(part_bf16) and symm.n in (2, 4, 8):
+    if symm is not None and symm._inside(part_bf16) and (symm.mode == "nvls" or symm.n in (2, 4, 8)):
         return symm.reduce_scatter_rows(part_bf16)
     import torch.distributed as dist
     M, N = part_bf16.shape

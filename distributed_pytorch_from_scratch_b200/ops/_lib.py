@@ -33,6 +33,7 @@ SIGS = {
     "dpfs_comm_flag_words": (),
     "dpfs_allreduce_nvls": (c_p, c_ll, c_int, c_p, c_int, c_int, c_p),
     "dpfs_reduce_scatter_p2p": (c_p, c_ll, c_ll, c_p, c_p, c_int, c_int, c_p),
+    "dpfs_reduce_scatter_nvls": (c_p, c_ll, c_p, c_p, c_int, c_int, c_p),
     "dpfs_allgather_p2p": (c_p, c_p, c_ll, c_ll, c_p, c_int, c_int, c_p),
     "dpfs_allgather_nvls": (c_p, c_p, c_ll, c_p, c_int, c_int, c_p),
     "dpfs_comm_barrier": (c_p, c_int, c_int, c_p),

@@ -45,7 +45,10 @@ class SymmComm:
         self.ag_bytes = self.gather_off - self.ag_off
         self.closed = False
         # data path of the reduce: "p2p" (plain NVLink loads/stores, rank-ordered fp32 sums) or "nvls" (multimem.*)
-        self.mode = os.environ.get("DPFS_AR_MODE", "p2p")
+        # Measured (profiles/comm_paths_r1.md): P2P wins at TP=2 (100 vs 116 us for 32.8 MB), NVLS wins at TP=8 (123 vs
+        # 143 us; NCCL 158 us) because the switch-side reduction moves S(1+1/n) bytes instead of 2S(n-1)/n.
+        default_mode = "nvls" if (n >= 8 and self.mc_base) else "p2p"
+        self.mode = os.environ.get("DPFS_AR_MODE", default_mode)
         if n not in (2, 4, 8):
             self.mode = "nvls"
         if self.mode == "nvls" and not self.mc_base:
@@ -136,8 +139,8 @@ class SymmComm:
         return view.clone()
 
     def can_fuse_gemm_ar(self, a: torch.Tensor, w: torch.Tensor, b_mn_major: bool = False) -> bool:
-        if self.closed or a.dtype != BF16 or w.dtype != BF16:
-            return False
+        if self.closed or a.dtype != BF16 or w.dtype != BF16 or self.mode != "p2p":
+            return False     # the in-kernel reduce uses the P2P data path; with NVLS the GEMM and the reduce stay split
         M = a.shape[0]
         N = w.shape[1] if b_mn_major else w.shape[0]
         tiles = ((M + 127) // 128) * ((N + 127) // 128)
@@ -162,13 +165,18 @@ class SymmComm:
         """partial: bf16 [M, N] living in the symmetric buffer (each rank's partial sums) -> this rank's reduced block
         of rows, bf16 [M / n, N] in private memory."""
         assert self._inside(partial) and partial.dtype == BF16 and partial.is_contiguous()
-        assert self.n in (2, 4, 8), "the P2P reduce-scatter kernel is instantiated for 2, 4 and 8 ranks"
         M, N = partial.shape
         assert M % self.n == 0
         out = torch.empty((M // self.n, N), dtype=BF16, device=partial.device)
-        rc = _lib.lib().dpfs_reduce_scatter_p2p(self.data_ptrs, partial.data_ptr() - self.base, M * N * 2,
-                                                out.data_ptr(), self.flag_ptrs, self.rank, self.n, _lib.stream())
-        _lib.check(rc, "dpfs_reduce_scatter_p2p")
+        off = partial.data_ptr() - self.base
+        if self.mode == "nvls":
+            rc = _lib.lib().dpfs_reduce_scatter_nvls(self.mc_base + off, M * N * 2, out.data_ptr(), self.flag_ptrs,
+                                                     self.rank, self.n, _lib.stream())
+        else:
+            assert self.n in (2, 4, 8), "the P2P reduce-scatter kernel is instantiated for 2, 4 and 8 ranks"
+            rc = _lib.lib().dpfs_reduce_scatter_p2p(self.data_ptrs, off, M * N * 2, out.data_ptr(), self.flag_ptrs,
+                                                    self.rank, self.n, _lib.stream())
+        _lib.check(rc, "dpfs_reduce_scatter")
         return out
 
     def all_gather_into_buffer(self, local: torch.Tensor) -> torch.Tensor:
@@ -177,9 +185,13 @@ class SymmComm:
         local = local.contiguous()
         nbytes = local.numel() * local.element_size()
         assert nbytes % 16 == 0 and nbytes * self.n <= self.ag_bytes, "all-gather landing zone too small"
-        rc = _lib.lib().dpfs_allgather_p2p(local.data_ptr(), self.data_ptrs, self.ag_off, nbytes, self.flag_ptrs,
-                                           self.rank, self.n, _lib.stream())
-        _lib.check(rc, "dpfs_allgather_p2p")
+        if self.mode == "nvls":
+            rc = _lib.lib().dpfs_allgather_nvls(local.data_ptr(), self.mc_base + self.ag_off, nbytes, self.flag_ptrs,
+                                                self.rank, self.n, _lib.stream())
+        else:
+            rc = _lib.lib().dpfs_allgather_p2p(local.data_ptr(), self.data_ptrs, self.ag_off, nbytes, self.flag_ptrs,
+                                               self.rank, self.n, _lib.stream())
+        _lib.check(rc, "dpfs_allgather")
         shape = (self.n * local.shape[0],) + tuple(local.shape[1:])
         return self.data[self.ag_off:self.ag_off + nbytes * self.n].view(local.dtype).view(shape)
 

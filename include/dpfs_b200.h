@@ -66,6 +66,8 @@ int dpfs_allreduce_p2p(const unsigned long long* data_ptrs, long long offset, lo
  * reference (it has no sequence parallelism; SURVEY §2.3 lists it as a required extension). */
 int dpfs_reduce_scatter_p2p(const unsigned long long* data_ptrs, long long offset, long long nbytes_total, void* out,
                             const unsigned long long* flag_ptrs, int rank, int n, cudaStream_t stream);
+int dpfs_reduce_scatter_nvls(const void* mc_ptr, long long nbytes_total, void* out,
+                             const unsigned long long* flag_ptrs, int rank, int n, cudaStream_t stream);
 int dpfs_allgather_p2p(const void* src, const unsigned long long* data_ptrs, long long dst_offset,
                        long long nbytes_per_rank, const unsigned long long* flag_ptrs, int rank, int n,
                        cudaStream_t stream);
