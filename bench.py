@@ -28,6 +28,27 @@ BATCH, SEQ = 32, 1000          # reference train.py default batch size, ModelArg
 LR, WARMUP_STEPS, MAX_STEPS = 3e-4, 2000, 20000   # reference train.py defaults (OneCycleLR)
 METRIC = "train tokens/sec at TP=N (max over ranks), default train.py transformer"
 
+# BASELINE.json configs 3 and 4 (same step, other shapes); the default (config 2) is the headline the driver runs
+CONFIGS = {
+    "default": None,
+    "gpt2m": dict(name="GPT-2-medium shape (d1024 L24 H16 ffn4096 seq1024 V50304)", batch=8, seq=1024,
+                  model=dict(attn_dim=1024, ffn_dim=4096, num_heads=16, num_layers=24, vocab_size=50304, maxlen=1024)),
+    "1p3b": dict(name="1.3B (d2048 L24 H16 ffn6144 seq2048 V50304)", batch=4, seq=2048,
+                 model=dict(attn_dim=2048, ffn_dim=6144, num_heads=16, num_layers=24, vocab_size=50304, maxlen=2048)),
+}
+
+
+def apply_config(args):
+    """Returns (model kwargs, description) and sets the global batch / sequence length of the run."""
+    global BATCH, SEQ, METRIC
+    from dataclasses import asdict as _asdict
+    cfg = CONFIGS[args.config]
+    if cfg is None:
+        return None, "reference default ModelArgumments (d512 ffn2048 h8 L12 V1024 maxlen1000, 51.5M params)"
+    BATCH, SEQ = cfg["batch"], cfg["seq"]
+    METRIC = f"train tokens/sec at TP=N (max over ranks), {cfg['name']}"
+    return dict(cfg["model"], rope_theta=10000.), cfg["name"]
+
 
 # ------------------------------------------------------------------------------------------------ clocks
 class ClockSampler:
@@ -181,7 +202,8 @@ def run_ours(args):
     if world > 1 and args.comm != "nccl":
         from distributed_pytorch_from_scratch_b200.parallel.symm import try_enable_symm
         try_enable_symm(required=(args.comm == "fused"))
-    margs = ModelArgumments()
+    mk, desc = apply_config(args)
+    margs = ModelArgumments() if mk is None else ModelArgumments(**mk)
     # sequence parallelism pays off once the replicated norm / residual work outweighs the extra collectives:
     # measured 15.9 vs 17.3 ms at TP=8 and 21.9 vs 20.9 ms at TP=2 (profiles/), so "auto" turns it on from TP=8
     sp = world > 1 and (args.sp == "on" or (args.sp == "auto" and world >= 8))
@@ -226,7 +248,7 @@ def run_ours(args):
         "scaling": "strong", "vs_baseline": None, "dtype": "bf16",
         "data": "synthetic tokens (uniform ids, collate_fn layout), random-init weights",
         "impl": "ours",
-        "config": {"model": "reference default ModelArgumments (d512 ffn2048 h8 L12 V1024 maxlen1000, 51.5M params)",
+        "config": {"model": desc,
                    "global_batch": BATCH, "seq_len": SEQ, "parallelism": f"tp{world}" + ("+sp" if sp else ""),
                    "optimizer": "Adam(3e-4) + OneCycleLR (fused, one launch)",
                    "cuda_graph": bool(step.use_graph),
@@ -274,7 +296,8 @@ def run_reference(args):
     torch.cuda.manual_seed_all(0)
     os.environ["DTYPE"] = "bfloat16"               # train.py --bf16 (reference train.py:58-63)
     pm.init_pgm(world)
-    margs = ModelArgumments()
+    mk, desc = apply_config(args)
+    margs = ModelArgumments() if mk is None else ModelArgumments(**mk)
     model = Transformer(**asdict(margs))
     model.cuda()
     model.reset_parameters()
@@ -322,7 +345,7 @@ def run_reference(args):
         "scaling": "strong", "vs_baseline": None, "dtype": "bf16",
         "data": "synthetic tokens (uniform ids, collate_fn layout), random-init weights",
         "impl": "reference",
-        "config": {"model": "reference default ModelArgumments (d512 ffn2048 h8 L12 V1024 maxlen1000, 51.5M params)",
+        "config": {"model": desc,
                    "global_batch": BATCH, "seq_len": SEQ, "parallelism": f"tp{world}",
                    "optimizer": "torch.optim.Adam(3e-4) + OneCycleLR", "cuda_graph": False,
                    "comm": "nccl" if world > 1 else "none",
@@ -345,6 +368,8 @@ def main():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", choices=["ours", "reference"], default="ours")
+    ap.add_argument("--config", choices=list(CONFIGS), default="default",
+                    help="default = the reference's train.py model (the headline); gpt2m / 1p3b = BASELINE.json configs 3 / 4")
     ap.add_argument("--comm", choices=["auto", "fused", "nccl"], default="auto",
                     help="TP collectives: our NVLink kernels over symmetric memory (fused), NCCL, or auto")
     ap.add_argument("--no-graph", action="store_true", help="run eagerly instead of replaying a CUDA graph")
