@@ -178,21 +178,32 @@ __global__ void __launch_bounds__(kNormThreads) rmsnorm_bwd_kernel(
   for (int row = blockIdx.x * wpb + warp; row < M; row += gridDim.x * wpb) {
     const long long off = static_cast<long long>(row) * D;
     const float rstd = rstd_in[row];
-    float xh[NV][4], g[NV][4];
+    float xh[NV][4], g[NV][4], rs[NV][4];
     float dot = 0.f;
+    // every global load of the row (x, dy and the residual-stream gradient) is issued before the first use, so the
+    // row costs ONE memory round trip instead of two
+#pragma unroll
+    for (int i = 0; i < NV; ++i) {
+      const int c = (i * 32 + lane) * 4;
+#pragma unroll
+      for (int j = 0; j < 4; ++j) rs[i][j] = 0.f;
+      if (c < D) {
+        load4<XT>(x + off + c, xh[i]);
+        load4<GT>(dy + off + c, g[i]);
+        if (dres) load4<float>(dres + off + c, rs[i]);
+      }
+    }
 #pragma unroll
     for (int i = 0; i < NV; ++i) {
       const int c = (i * 32 + lane) * 4;
       if (c < D) {
-        float xv[4], dv[4];
-        load4<XT>(x + off + c, xv);
-        load4<GT>(dy + off + c, dv);
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
-          xh[i][j] = xv[j] * rstd;
-          g[i][j] = dv[j] * sc[i][j];
-          ds[i][j] += dv[j] * xh[i][j];
-          dot += g[i][j] * xh[i][j];
+          const float xv = xh[i][j] * rstd, dv = g[i][j];
+          xh[i][j] = xv;
+          g[i][j] = dv * sc[i][j];
+          ds[i][j] += dv * xv;
+          dot += g[i][j] * xv;
         }
       }
     }
@@ -203,13 +214,7 @@ __global__ void __launch_bounds__(kNormThreads) rmsnorm_bwd_kernel(
       if (c < D) {
         float o[4];
 #pragma unroll
-        for (int j = 0; j < 4; ++j) o[j] = rstd * (g[i][j] - xh[i][j] * dot);
-        if (dres) {
-          float r[4];
-          load4<float>(dres + off + c, r);
-#pragma unroll
-          for (int j = 0; j < 4; ++j) o[j] += r[j];
-        }
+        for (int j = 0; j < 4; ++j) o[j] = rstd * (g[i][j] - xh[i][j] * dot) + rs[i][j];
         if (dx) store4<float>(dx + off + c, o);
         if (dx_bf16) store4<__nv_bfloat16>(dx_bf16 + off + c, o);
       }
@@ -563,6 +568,91 @@ __global__ void colsum_partial_kernel(const __nv_bfloat16* __restrict__ x, long 
   *reinterpret_cast<float4*>(o + 4) = make_float4(acc[4], acc[5], acc[6], acc[7]);
 }
 
+
+// --------------------------------------------------------------------------------- fused producers + bias gradients
+// The bias gradient of a linear layer is the column sum of its output gradient.  Instead of re-reading that gradient in
+// a separate colsum pass, the kernels that PRODUCE it keep per-thread column partials (each thread owns a fixed group
+// of 8 columns over a strip of 64 rows), write them to scratch [strips][ncols] and the usual fixed-order second stage
+// finishes the sum.
+
+// dgu = swiglu'(dact, gu) and partial column sums of dgu (= gradient of the gate|up biases)
+__global__ void __launch_bounds__(128) swiglu_bwd_colsum_kernel(const __nv_bfloat16* __restrict__ dact,
+                                                                const __nv_bfloat16* __restrict__ gu,
+                                                                __nv_bfloat16* __restrict__ dgu,
+                                                                float* __restrict__ scratch, int M, int F) {
+  const int cg = blockIdx.x * blockDim.x + threadIdx.x;
+  if (cg * 8 >= F) return;
+  const int r0 = blockIdx.y * kColsumRowsPerBlock;
+  const int r1 = min(M, r0 + kColsumRowsPerBlock);
+  float sg[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f}, su[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+#pragma unroll 4
+  for (int r = r0; r < r1; ++r) {
+    const long long go = static_cast<long long>(r) * 2 * F + cg * 8;
+    const uint4 gv = *reinterpret_cast<const uint4*>(gu + go);
+    const uint4 uv = *reinterpret_cast<const uint4*>(gu + go + F);
+    const uint4 dv = *reinterpret_cast<const uint4*>(dact + static_cast<long long>(r) * F + cg * 8);
+    const uint32_t gw[4] = {gv.x, gv.y, gv.z, gv.w}, uw[4] = {uv.x, uv.y, uv.z, uv.w},
+                   dw[4] = {dv.x, dv.y, dv.z, dv.w};
+    uint32_t og[4], ou[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const float2 g = unpack_bf16(gw[j]), u = unpack_bf16(uw[j]), d = unpack_bf16(dw[j]);
+      const float s0 = 1.f / (1.f + __expf(-g.x)), s1 = 1.f / (1.f + __expf(-g.y));
+      const float dg0 = d.x * u.x * s0 * (1.f + g.x * (1.f - s0));
+      const float dg1 = d.y * u.y * s1 * (1.f + g.y * (1.f - s1));
+      const float du0 = d.x * g.x * s0, du1 = d.y * g.y * s1;
+      og[j] = pack_bf16(dg0, dg1);
+      ou[j] = pack_bf16(du0, du1);
+      // sum what is actually stored (bf16-rounded), like a separate colsum pass over dgu would
+      const float2 rg = unpack_bf16(og[j]), ru = unpack_bf16(ou[j]);
+      sg[2 * j] += rg.x;
+      sg[2 * j + 1] += rg.y;
+      su[2 * j] += ru.x;
+      su[2 * j + 1] += ru.y;
+    }
+    *reinterpret_cast<uint4*>(dgu + go) = make_uint4(og[0], og[1], og[2], og[3]);
+    *reinterpret_cast<uint4*>(dgu + go + F) = make_uint4(ou[0], ou[1], ou[2], ou[3]);
+  }
+  float* o = scratch + static_cast<long long>(blockIdx.y) * 2 * F + cg * 8;
+  *reinterpret_cast<float4*>(o) = make_float4(sg[0], sg[1], sg[2], sg[3]);
+  *reinterpret_cast<float4*>(o + 4) = make_float4(sg[4], sg[5], sg[6], sg[7]);
+  *reinterpret_cast<float4*>(o + F) = make_float4(su[0], su[1], su[2], su[3]);
+  *reinterpret_cast<float4*>(o + F + 4) = make_float4(su[4], su[5], su[6], su[7]);
+}
+
+// y = bf16(x) and partial column sums of y
+constexpr int kCastColsumRows = 16;  // short strips: N is small here (the model width), parallelism comes from M
+__global__ void __launch_bounds__(128) cast_colsum_kernel(const float* __restrict__ x, __nv_bfloat16* __restrict__ y,
+                                                          float* __restrict__ scratch, int M, int N) {
+  const int cg = blockIdx.x * blockDim.x + threadIdx.x;
+  if (cg * 8 >= N) return;
+  const int r0 = blockIdx.y * kCastColsumRows;
+  const int r1 = min(M, r0 + kCastColsumRows);
+  float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+#pragma unroll 4
+  for (int r = r0; r < r1; ++r) {
+    const long long o = static_cast<long long>(r) * N + cg * 8;
+    const float4 a = *reinterpret_cast<const float4*>(x + o);
+    const float4 b = *reinterpret_cast<const float4*>(x + o + 4);
+    uint4 p;
+    p.x = pack_bf16(a.x, a.y);
+    p.y = pack_bf16(a.z, a.w);
+    p.z = pack_bf16(b.x, b.y);
+    p.w = pack_bf16(b.z, b.w);
+    *reinterpret_cast<uint4*>(y + o) = p;
+    const uint32_t w[4] = {p.x, p.y, p.z, p.w};
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const float2 f = unpack_bf16(w[j]);
+      acc[2 * j] += f.x;
+      acc[2 * j + 1] += f.y;
+    }
+  }
+  float* o = scratch + static_cast<long long>(blockIdx.y) * N + cg * 8;
+  *reinterpret_cast<float4*>(o) = make_float4(acc[0], acc[1], acc[2], acc[3]);
+  *reinterpret_cast<float4*>(o + 4) = make_float4(acc[4], acc[5], acc[6], acc[7]);
+}
+
 // --------------------------------------------------------------------------------------------- casts
 __global__ void cast_f32_to_bf16_kernel(const float* __restrict__ x, __nv_bfloat16* __restrict__ y, long long n4) {
   for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < n4;
@@ -795,6 +885,39 @@ extern "C" int dpfs_colsum_bf16(const void* x, long long ld, float* out, int acc
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) return static_cast<int>(e);
   reduce_partials_kernel<<<(DPFS_COUNT(), (N + 31) / 32), 256, 0, stream>>>(scratch, out, strips, N, accumulate);
+  return static_cast<int>(cudaGetLastError());
+}
+
+
+// dgu = swiglu backward; bias_grad[2F] (+)= column sums of dgu.  scratch: dpfs_colsum_scratch_floats(M, 2F) floats.
+extern "C" int dpfs_swiglu_bwd_bias(const void* dact, const void* gu, void* dgu, float* bias_grad, int accumulate,
+                                    float* scratch, int M, int F, cudaStream_t stream) {
+  if (F % 8 != 0) return -21;
+  if (M <= 0) return 0;
+  const int strips = (M + kColsumRowsPerBlock - 1) / kColsumRowsPerBlock;
+  dim3 grid((F / 8 + 127) / 128, strips);
+  swiglu_bwd_colsum_kernel<<<(DPFS_COUNT(), grid), 128, 0, stream>>>((const __nv_bfloat16*)dact,
+                                                                    (const __nv_bfloat16*)gu, (__nv_bfloat16*)dgu,
+                                                                    scratch, M, F);
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return static_cast<int>(e);
+  reduce_partials_kernel<<<(DPFS_COUNT(), (2 * F + 31) / 32), 256, 0, stream>>>(scratch, bias_grad, strips, 2 * F,
+                                                                               accumulate);
+  return static_cast<int>(cudaGetLastError());
+}
+
+// y = bf16(x) for fp32 x [M][N] (contiguous); colsum[N] (+)= column sums of y.  scratch: ceil(M / 16) * N floats.
+extern "C" int dpfs_cast_colsum(const float* x, void* y, float* colsum, int accumulate, float* scratch, int M, int N,
+                                cudaStream_t stream) {
+  if (N % 8 != 0) return -23;
+  if (M <= 0) return 0;
+  const int strips = (M + kCastColsumRows - 1) / kCastColsumRows;
+  const int tpb = N / 8 < 128 ? ((N / 8 + 31) / 32) * 32 : 128;
+  dim3 grid((N / 8 + tpb - 1) / tpb, strips);
+  cast_colsum_kernel<<<(DPFS_COUNT(), grid), tpb, 0, stream>>>(x, (__nv_bfloat16*)y, scratch, M, N);
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return static_cast<int>(e);
+  reduce_partials_kernel<<<(DPFS_COUNT(), (N + 31) / 32), 256, 0, stream>>>(scratch, colsum, strips, N, accumulate);
   return static_cast<int>(cudaGetLastError());
 }
 

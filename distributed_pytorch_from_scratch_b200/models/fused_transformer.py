@@ -227,15 +227,14 @@ class FusedLayerFn(torch.autograd.Function):
         pack, m, rt = ctx.pack, ctx.meta, ctx.rt
         dx3 = dx3.contiguous()
         dx3_b = fused.cast_to_bf16(dx3)
+        fused.colsum(dx3_b, out=pack.g_bd)   # (the fused cast+colsum kernel measured slower than the two passes here)
         # ---- FFN
         dact = gemm_nt(dx3_b, pack.wd, b_mn_major=True, out_dtype=BF16)            # [M, Fl]
         _wgrad(dx3_b, act, pack.g_wd)
-        fused.colsum(dx3_b, out=pack.g_bd)
-        dgu = fused.swiglu_bwd(dact, gu)
+        dgu = fused.swiglu_bwd_bias(dact, gu, pack.g_bgu)   # + gate|up bias grads from the same pass
         del dact
         dh2 = _colpar_dgrad(dgu, pack.wgu)                                            # [M, d]
         _wgrad(dgu, h2, pack.g_wgu)
-        fused.colsum(dgu, out=pack.g_bgu)
         del dgu
         dx2, dx2_b, _ = fused.rmsnorm_bwd(dh2, x2, rstd2, pack.s2, dres=dx3, want_fp32=True, want_bf16=True,
                                           dscale_out=pack.g_s2)
@@ -475,11 +474,10 @@ class FusedLayerSPFn(torch.autograd.Function):
         dact = gemm_nt(dx3, pack.wd, b_mn_major=True, out_dtype=BF16)
         _wgrad(dx3, act, pack.g_wd)
         fused.colsum(dx3, out=pack.g_bd)
-        dgu = fused.swiglu_bwd(dact, gu)
+        dgu = fused.swiglu_bwd_bias(dact, gu, pack.g_bgu)
         del dact
         dh2_l = _rowpar_rs(dgu, pack.wgu, b_mn_major=True)                               # [Ml, d]
         _wgrad(dgu, h2, pack.g_wgu)
-        fused.colsum(dgu, out=pack.g_bgu)
         del dgu
         dx2_l, dx2_lb, _ = fused.rmsnorm_bwd(dh2_l, x2_l, rstd2, pack.s2, dres=dx3_l, want_fp32=True, want_bf16=True,
                                              dscale_out=pack.g_s2)

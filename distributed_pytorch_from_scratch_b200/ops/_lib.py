@@ -47,6 +47,8 @@ SIGS = {
     "dpfs_layernorm_bwd": (c_p, c_int, c_p, c_int, c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_int, c_int, c_p),
     "dpfs_swiglu_fwd": (c_p, c_p, c_int, c_int, c_p),
     "dpfs_swiglu_bwd": (c_p, c_p, c_p, c_int, c_int, c_p),
+    "dpfs_swiglu_bwd_bias": (c_p, c_p, c_p, c_p, c_int, c_p, c_int, c_int, c_p),
+    "dpfs_cast_colsum": (c_p, c_p, c_p, c_int, c_p, c_int, c_int, c_p),
     "dpfs_gelu_fwd": (c_p, c_p, c_ll, c_p),
     "dpfs_gelu_bwd": (c_p, c_p, c_p, c_ll, c_p),
     "dpfs_rope_inplace": (c_p, c_ll, c_p, c_p, c_p, c_int, c_int, c_int, c_int, c_int, c_int, c_p),

@@ -136,6 +136,34 @@ def swiglu_bwd(dact: torch.Tensor, gu: torch.Tensor) -> torch.Tensor:
     return dgu
 
 
+def swiglu_bwd_bias(dact: torch.Tensor, gu: torch.Tensor, bias_grad: torch.Tensor) -> torch.Tensor:
+    """swiglu backward + column sums of dgu into ``bias_grad`` (fp32 [2F]) in the same pass."""
+    M, F2 = gu.shape
+    assert dact.dtype == BF16 and dact.is_contiguous() and dact.shape == (M, F2 // 2)
+    assert bias_grad.dtype == F32 and bias_grad.numel() == F2 and bias_grad.is_contiguous()
+    dgu = torch.empty_like(gu)
+    lib = _lib.lib()
+    scratch = _scratch(gu.device, "colsum", lib.dpfs_colsum_scratch_floats(M, F2))
+    rc = lib.dpfs_swiglu_bwd_bias(dact.data_ptr(), gu.data_ptr(), dgu.data_ptr(), bias_grad.data_ptr(), 0,
+                                  scratch.data_ptr(), M, F2 // 2, _lib.stream())
+    _lib.check(rc, "dpfs_swiglu_bwd_bias")
+    return dgu
+
+
+def cast_colsum(x: torch.Tensor, colsum_out: torch.Tensor) -> torch.Tensor:
+    """bf16(x) for fp32 x [M, N] and the column sums of the result into ``colsum_out`` (fp32 [N]), one pass."""
+    assert x.dtype == F32 and x.dim() == 2 and x.is_contiguous()
+    M, N = x.shape
+    assert colsum_out.dtype == F32 and colsum_out.numel() == N and colsum_out.is_contiguous()
+    y = torch.empty((M, N), dtype=BF16, device=x.device)
+    lib = _lib.lib()
+    scratch = _scratch(x.device, "colsum", ((M + 15) // 16) * N)
+    rc = lib.dpfs_cast_colsum(x.data_ptr(), y.data_ptr(), colsum_out.data_ptr(), 0, scratch.data_ptr(), M, N,
+                              _lib.stream())
+    _lib.check(rc, "dpfs_cast_colsum")
+    return y
+
+
 def gelu_fwd(x: torch.Tensor) -> torch.Tensor:
     assert x.dtype == BF16 and x.is_contiguous()
     y = torch.empty_like(x)

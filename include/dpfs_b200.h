@@ -120,6 +120,10 @@ int dpfs_layernorm_bwd(const void* dy, int dy_bf16, const void* x, int x_bf16, c
  * gu: bf16 [M][2F] = gate | up;  act = silu(gate) * up.  ref: FFN.forward, models/model.py:95. */
 int dpfs_swiglu_fwd(const void* gu, void* act, int M, int F, cudaStream_t stream);
 int dpfs_swiglu_bwd(const void* dact, const void* gu, void* dgu, int M, int F, cudaStream_t stream);
+/* swiglu backward that also produces the gate|up bias gradient (column sums of dgu) from the same pass.
+ * scratch: dpfs_colsum_scratch_floats(M, 2F) floats.  ref: autograd of models/model.py:95 + models/layers.py:96. */
+int dpfs_swiglu_bwd_bias(const void* dact, const void* gu, void* dgu, float* bias_grad, int accumulate,
+                         float* scratch, int M, int F, cudaStream_t stream);
 /* tanh-GELU on bf16, n % 8 == 0 (no counterpart in the reference model; named by the project brief). */
 int dpfs_gelu_fwd(const void* x, void* y, long long n, cudaStream_t stream);
 int dpfs_gelu_bwd(const void* dy, const void* x, void* dx, long long n, cudaStream_t stream);
@@ -138,6 +142,10 @@ int dpfs_colsum_scratch_floats(int M, int N);
 int dpfs_colsum_bf16(const void* x, long long ld, float* out, int accumulate, float* scratch, int M, int N,
                      cudaStream_t stream);
 int dpfs_cast_f32_to_bf16(const float* x, void* y, long long n, cudaStream_t stream);
+/* y = bf16(x) for fp32 x [M][N] plus colsum[N] (+)= column sums of y, one pass (the residual-stream gradient feeds a
+ * GEMM as bf16 and is also the gradient of the replicated row-parallel bias).  scratch: ceil(M / 16) * N floats. */
+int dpfs_cast_colsum(const float* x, void* y, float* colsum, int accumulate, float* scratch, int M, int N,
+                     cudaStream_t stream);
 
 /* Column sum for callers that cannot allocate device memory and have no scratch buffer to lend: a host process whose
  * own allocator already owns the whole GPU (so a cudaMalloc may fail, and would stall the device), or a plain C /

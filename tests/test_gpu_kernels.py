@@ -116,6 +116,14 @@ def test_swiglu_gelu():
     assert (act.float() - ar).abs().max().item() < 0.05
     dgu = fused.swiglu_bwd(dact, gu)
     assert (dgu.float() - gr.grad).abs().max().item() < 0.06
+    bg = torch.empty(2 * F, device=DEV)
+    dgu2 = fused.swiglu_bwd_bias(dact, gu, bg)
+    assert torch.equal(dgu2, dgu)
+    assert torch.allclose(bg, dgu.float().sum(0), atol=2e-2, rtol=1e-3)
+    xf = torch.randn(700, 520, device=DEV)
+    cs = torch.empty(520, device=DEV)
+    yb = fused.cast_colsum(xf, cs)
+    assert torch.equal(yb, xf.to(torch.bfloat16)) and torch.allclose(cs, yb.float().sum(0), atol=1e-2, rtol=1e-4)
     x = _bf(torch.randn(M, F, device=DEV))
     xr = x.float().requires_grad_(True)
     yr = torch.nn.functional.gelu(xr, approximate="tanh")
