@@ -677,7 +677,7 @@ static inline int ew_grid(long long work_items, int threads) {
 
 static inline int norm_grid(int M) {
   int b = (M + 7) / 8;
-  const int cap = num_sms() * 4;
+  const int cap = num_sms() * 8;   // as many resident warps as registers allow: these kernels live on bytes in flight
   return b < cap ? (b < 1 ? 1 : b) : cap;
 }
 

@@ -33,7 +33,8 @@ constexpr int kStages = 6;
 constexpr int kABytes = BM * BK * 2;
 constexpr int kBBytes = BNH * BK * 2;
 constexpr int kStageBytes = kABytes + kBBytes;
-constexpr int kSmem = kStages * kStageBytes + 256 + 1024;
+constexpr int kOutStageBytes = 4 * 2 * 4096;  // 4 epilogue warps x 2 buffers x (32 rows x 128 B) staging for TMA stores
+constexpr int kSmem = kStages * kStageBytes + kOutStageBytes + 256 + 1024;
 constexpr uint32_t kPeerMask = 0xFEFFFFFFu;  // clears the CTA-rank bit of a shared-window address -> leader CTA's copy
 
 struct Args {
@@ -98,6 +99,13 @@ __device__ __forceinline__ void mbar_arrive_leader(uint64_t* bar) {
   asm volatile("mbarrier.arrive.shared::cluster.b64 _, [%0];" ::"r"(smem_u32(bar) & kPeerMask) : "memory");
 }
 
+__device__ __forceinline__ void tma_store_3d(const CUtensorMap* m, const void* smem_src, int c0, int c1, int c2) {
+  asm volatile("cp.async.bulk.tensor.3d.global.shared::cta.tile.bulk_group [%0, {%2, %3, %4}], [%1];"
+               :
+               : "l"(reinterpret_cast<uint64_t>(m)), "r"(smem_u32(smem_src)), "r"(c0), "r"(c1), "r"(c2)
+               : "memory");
+}
+
 template <typename OutT>
 __device__ __forceinline__ void store32(OutT* dst, const float (&v)[32], int ncols_valid);
 template <>
@@ -124,12 +132,14 @@ __device__ __forceinline__ void store32<__nv_bfloat16>(__nv_bfloat16* dst, const
 
 template <bool A_MN, bool B_MN, typename OutT>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
-gemm2sm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const Args args) {
+gemm2sm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+               const __grid_constant__ CUtensorMap tmOut, const Args args) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* sA = smem;
   uint8_t* sB = smem + kStages * kABytes;
-  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + kStages * kStageBytes);  // used on the leader only
+  uint8_t* sOut = smem + kStages * kStageBytes;                                    // TMA-store staging
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(sOut + kOutStageBytes);         // used on the leader only
   uint64_t* empty_bar = full_bar + kStages;
   uint64_t* tmem_full = empty_bar + kStages;
   uint64_t* tmem_empty = tmem_full + 2;  // used on the leader only
@@ -149,6 +159,7 @@ gemm2sm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   if (threadIdx.x == 0) {
     prefetch_tmap(&tmA);
     prefetch_tmap(&tmB);
+    prefetch_tmap(&tmOut);
     for (int i = 0; i < kStages; ++i) {
       mbar_init(&full_bar[i], 1);
       mbar_init(&empty_bar[i], 1);
@@ -246,10 +257,16 @@ gemm2sm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       }
     }
   } else {
+    // Epilogue: TMEM -> registers (bias / residual) -> 128B-swizzled smem slab -> TMA store.  Every thread owns one
+    // output ROW, so direct global stores would touch 32 different rows per instruction (half-filled 32 B sectors);
+    // staging 32 rows x 128 B per warp and letting the TMA unit write them gives full-line, coalesced writes, clips the
+    // M / N edges for free, and takes the store instructions off the epilogue's critical path.
     const int q = warp & 3;
+    uint8_t* stage = sOut + (warp - 2) * 2 * 4096;
+    int sbuf = 0;
     int as = 0;
     uint32_t aphase = 0;
-    OutT* out = reinterpret_cast<OutT*>(args.out);
+    constexpr bool kBf16 = sizeof(OutT) == 2;
     for (int w = cluster_id; w < num_work; w += n_clusters) {
       const int split = w / tiles_mn;
       const int t = w - split * tiles_mn;
@@ -259,7 +276,6 @@ gemm2sm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       mbar_wait(&tmem_full[as], aphase);
       tc_fence_after();
       const uint32_t t_addr = tmem_base + as * BN + (static_cast<uint32_t>(q * 32) << 16);
-      OutT* orow = out + split * args.split_stride + static_cast<long long>(row) * args.ldo + n0;
       const float* rrow = args.residual ? args.residual + static_cast<long long>(row) * args.ldr + n0 : nullptr;
 #pragma unroll 1
       for (int c = 0; c < BN / 32; ++c) {
@@ -267,11 +283,11 @@ gemm2sm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         tmem_ld32(t_addr + c * 32, r);
         tmem_ld_wait();
         const int ncols_valid = args.N - (n0 + c * 32);
-        if (row < args.M && ncols_valid > 0) {
-          float v[32];
+        float v[32];
 #pragma unroll
-          for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
-          if (args.bias) {  // 8 x LDG.128 (broadcast across the warp) instead of 32 scalar loads
+        for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
+        if (ncols_valid > 0) {
+          if (args.bias) {
             const float4* b4 = reinterpret_cast<const float4*>(args.bias + n0 + c * 32);
 #pragma unroll
             for (int j = 0; j < 8; ++j) {
@@ -284,7 +300,7 @@ gemm2sm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
               }
             }
           }
-          if (rrow) {
+          if (rrow && row < args.M) {
 #pragma unroll
             for (int j = 0; j < 8; ++j) {
               if (j * 4 + 4 <= ncols_valid) {
@@ -296,7 +312,37 @@ gemm2sm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
               }
             }
           }
-          store32<OutT>(orow + c * 32, v, ncols_valid);
+        }
+        uint8_t* slab = stage + sbuf * 4096 + lane * 128;
+        if constexpr (kBf16) {
+          // two 32-column chunks share one 64-column (128 B) slab row
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            const int idx = (c & 1) * 4 + j;
+            uint4 o;
+            o.x = pack_bf16(v[8 * j + 0], v[8 * j + 1]);
+            o.y = pack_bf16(v[8 * j + 2], v[8 * j + 3]);
+            o.z = pack_bf16(v[8 * j + 4], v[8 * j + 5]);
+            o.w = pack_bf16(v[8 * j + 6], v[8 * j + 7]);
+            *reinterpret_cast<uint4*>(slab + ((idx ^ (lane & 7)) << 4)) = o;
+          }
+        } else {
+#pragma unroll
+          for (int j = 0; j < 8; ++j)
+            *reinterpret_cast<float4*>(slab + ((j ^ (lane & 7)) << 4)) =
+                make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+        }
+        if (!kBf16 || (c & 1)) {
+          fence_proxy_async_smem();
+          __syncwarp();
+          if (lane == 0) {
+            const int col0 = n0 + (kBf16 ? (c - 1) : c) * 32;
+            if (col0 < args.N) tma_store_3d(&tmOut, stage + sbuf * 4096, col0, m0 + q * 32, split);
+            tma_store_commit();
+            tma_store_wait_read<1>();  // the OTHER buffer's previous store has finished reading its slab
+          }
+          __syncwarp();
+          sbuf ^= 1;
         }
       }
       tc_fence_before();
@@ -307,6 +353,7 @@ gemm2sm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         aphase ^= 1;
       }
     }
+    if (lane == 0) tma_store_wait<0>();  // all output tiles have landed before the CTA exits
   }
 
   tc_fence_before();
@@ -317,8 +364,44 @@ gemm2sm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   }
 }
 
+static PFN_cuTensorMapEncodeTiled_v12000 encode_fn2() {
+  static PFN_cuTensorMapEncodeTiled_v12000 fn = nullptr;
+  if (!fn) {
+    cudaDriverEntryPointQueryResult q;
+    void* p = nullptr;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) != cudaSuccess ||
+        q != cudaDriverEntryPointSuccess)
+      return nullptr;
+    fn = reinterpret_cast<PFN_cuTensorMapEncodeTiled_v12000>(p);
+  }
+  return fn;
+}
+
+// 3-D store map over out[splits][M][ldo] (N valid columns): box = 128 bytes of a row x 32 rows x 1 slab, 128B swizzle
+static int make_out_tmap(CUtensorMap* tm, void* out, bool fp32, int M, int N, long long ldo, int splits,
+                         long long split_stride) {
+  auto fn = encode_fn2();
+  if (!fn) return -1;
+  const cuuint64_t es = fp32 ? 4 : 2;
+  cuuint64_t dims[3] = {static_cast<cuuint64_t>(N), static_cast<cuuint64_t>(M), static_cast<cuuint64_t>(splits)};
+  cuuint64_t strides[2] = {static_cast<cuuint64_t>(ldo) * es,
+                           (splits > 1 ? static_cast<cuuint64_t>(split_stride) : static_cast<cuuint64_t>(M) * ldo) * es};
+  cuuint32_t box[3] = {static_cast<cuuint32_t>(128 / es), 32, 1};
+  cuuint32_t estr[3] = {1, 1, 1};
+  CUresult r = fn(tm, fp32 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, out, dims, strides,
+                  box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                  CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  return r == CUDA_SUCCESS ? 0 : -2;
+}
+
 template <bool A_MN, bool B_MN, typename OutT>
 static int launch(const CUtensorMap& tmA, const CUtensorMap& tmB, const Args& args, cudaStream_t stream) {
+  CUtensorMap tmOut;
+  {
+    const int rc = make_out_tmap(&tmOut, args.out, sizeof(OutT) == 4, args.M, args.N, args.ldo, args.splits,
+                                 args.split_stride);
+    if (rc) return rc;
+  }
   auto kfn = gemm2sm_kernel<A_MN, B_MN, OutT>;
   static bool configured = false;
   if (!configured) {
@@ -329,7 +412,7 @@ static int launch(const CUtensorMap& tmA, const CUtensorMap& tmB, const Args& ar
   const int work = ((args.M + 2 * BM - 1) / (2 * BM)) * ((args.N + BN - 1) / BN) * args.splits;
   int clusters = num_sms() / 2;
   if (work < clusters) clusters = work;
-  kfn<<<(DPFS_COUNT(), 2 * clusters), kThreads, kSmem, stream>>>(tmA, tmB, args);
+  kfn<<<(DPFS_COUNT(), 2 * clusters), kThreads, kSmem, stream>>>(tmA, tmB, tmOut, args);
   return static_cast<int>(cudaGetLastError());
 }
 

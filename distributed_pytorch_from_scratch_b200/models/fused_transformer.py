@@ -174,11 +174,13 @@ def _rowpar_residual(a_bf16, w_bf16, bias, residual, norm_scale=None, eps=1e-5):
     summed through the NVSwitch as they complete), then residual + bias + norm are one fused pass."""
     n = pm.pgm.tp_size
     if n == 1:
-        x_out = gemm_nt(a_bf16, w_bf16, bias=bias, residual=residual, out_dtype=F32)
         if norm_scale is None:
-            return x_out, None, None
-        h, rstd = fused.rmsnorm_fwd(x_out, norm_scale, eps)
-        return x_out, h, rstd
+            # residual + bias ride in the GEMM epilogue
+            return gemm_nt(a_bf16, w_bf16, bias=bias, residual=residual, out_dtype=F32), None, None
+        # a norm follows: bf16 GEMM output through the TMA-store epilogue, then residual + bias + norm in ONE pass
+        # (measured 25 + 50 us vs 78 us residual-epilogue GEMM + 23 us norm for the wo projection)
+        y = gemm_nt(a_bf16, w_bf16, out_dtype=BF16)
+        return fused.add_rmsnorm_fwd(residual, y, bias, norm_scale, eps)
     symm = pm.pgm.symm
     if symm is not None and symm.can_fuse_gemm_ar(a_bf16, w_bf16):
         y = symm.gemm_allreduce(a_bf16, w_bf16)
