@@ -29,6 +29,25 @@ def _comm_worker(rank, world):
     ref = torch.empty(world, 1000, 4, device="cuda")
     dist.all_gather_into_tensor(ref.view(-1), st.view(-1))
     assert torch.equal(g, ref)
+    # both data paths of the sequence-parallel halves and of the all-reduce (P2P loads/stores vs NVLS multimem)
+    part_ref = torch.randn(2048, 512, device="cuda").to(torch.bfloat16)
+    full = part_ref.float().clone()
+    dist.all_reduce(full)
+    loc = torch.randn(2048 // world, 256, device="cuda").to(torch.bfloat16)
+    ag_ref = torch.empty(2048, 256, device="cuda", dtype=torch.bfloat16)
+    dist.all_gather_into_tensor(ag_ref, loc)
+    for mode in (["p2p", "nvls"] if symm.mc_base else ["p2p"]):
+        symm.mode = mode
+        buf = symm.buffer((2048, 512), torch.bfloat16)
+        buf.copy_(part_ref)
+        rs = symm.reduce_scatter_rows(buf)
+        rows = 2048 // world
+        assert (rs.float() - full[rank * rows:(rank + 1) * rows]).abs().max().item() < 0.07, mode
+        assert torch.equal(symm.all_gather_into_buffer(loc), ag_ref), mode
+        buf.copy_(part_ref)
+        ar = symm.all_reduce(buf, out=buf)
+        assert (ar.float() - full).abs().max().item() < 0.07, mode
+    symm.mode = "p2p"
     for (M, N, K, bmn) in [(1000, 512, 256, False), (4096, 512, 768, True)]:
         a = torch.randn(M, K, device="cuda").to(torch.bfloat16)
         w = (torch.randn(K, N, device="cuda") if bmn else torch.randn(N, K, device="cuda")).to(torch.bfloat16)
