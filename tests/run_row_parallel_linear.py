@@ -1,0 +1,23 @@
+"""Script-style entry point with the reference's CLI (its tests/test_row_parallel_linear.py is run as
+`python tests/test_row_parallel_linear.py --tp_size N`): spawns N ranks (gloo on CPU; the multi-GPU NCCL variants live in tests/test_gpu_tp.py) and runs the same
+assertions as the pytest suite.  Unlike the reference, a failing assertion makes the process exit non-zero."""
+import argparse
+import os
+import sys
+
+sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+
+from dist_utils import run_distributed  # noqa: E402
+from test_parallel_layers import _row_worker  # noqa: E402
+
+if __name__ == "__main__":
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--master_addr", type=str, default="127.0.0.1")
+    ap.add_argument("--master_port", type=str, default="25555")
+    ap.add_argument("--random_seed", type=int, default=42)
+    ap.add_argument("--tp_size", type=int, default=2)
+    ap.add_argument("--backend", type=str, default="gloo", choices=["gloo"])
+    a = ap.parse_args()
+    run_distributed(_row_worker, a.tp_size, int(a.master_port), backend=a.backend)
+    print(f"OK: row_parallel_linear at TP={a.tp_size} ({a.backend})")
