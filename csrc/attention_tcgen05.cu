@@ -26,6 +26,7 @@ namespace dpfs {
 int num_sms();
 
 constexpr int kAttnThreads = 192;
+constexpr int kAttnFwdThreads = 320;  // warp 0 TMA, warp 1 MMA, warps 2-9: two softmax warps per SM sub-partition
 constexpr int kAttnBwdThreads = 320;  // warp 0 TMA, warp 1 MMA, warps 2-9: two groups of 4 gradient-math warps
 constexpr int kTile = 128;  // q rows and kv rows per tile
 constexpr float kLog2e = 1.4426950408889634f;
@@ -66,13 +67,11 @@ struct FwdCfg {
   static constexpr int kQBytes = kTile * HD * 2;
   static constexpr int kKVBytes = kTile * HD * 2;  // one K or V tile
   static constexpr int kPBytes = kTile * kTile * 2;
-  static constexpr int kSmem = kQBytes + kStages * 2 * kKVBytes + kPBytes + 256 + 1024;
-  // hd = 64: two CTAs per SM (112 KB smem, 256 TMEM columns each, <= 168 registers) give the softmax warps of one CTA
-  // something to overlap with: S is single buffered [0,128), O at [128,192).
-  // hd = 128: one CTA per SM (192 KB smem); S is double buffered [0,128),[128,256) and O sits at [256,384) so QK^T of
-  // tile j+1 overlaps the softmax of tile j inside the CTA.
-  // (measured: two CTAs/SM with a single S buffer were 30% SLOWER for hd = 64 — 193 vs 149 us on the flagship shape —
-  //  so both head sizes use one CTA per SM with a double-buffered S; the single-buffer path is kept for experiments)
+  static constexpr int kXchgBytes = 2 * 2 * kTile * 4;  // row-max / row-sum exchange between the two column halves
+  static constexpr int kSmem = kQBytes + kStages * 2 * kKVBytes + kPBytes + 256 + kXchgBytes + 1024;
+  // One CTA per SM; S is double buffered in TMEM [0,128),[128,256) and O sits at [256,256+HD), so QK^T of tile j+1
+  // overlaps the softmax of tile j inside the CTA.  (Measured: two CTAs/SM with a single S buffer were 30% SLOWER for
+  // hd = 64 — 193 vs 149 us on the flagship shape; the single-buffer path is kept for experiments.)
   static constexpr int kSBufs = 2;
   static constexpr int kTmemCols = 512;
   static constexpr int kOCol = 256;
@@ -80,7 +79,7 @@ struct FwdCfg {
 };
 
 template <int HD>
-__global__ void __launch_bounds__(kAttnThreads, FwdCfg<HD>::kCtasPerSm)
+__global__ void __launch_bounds__(kAttnFwdThreads, FwdCfg<HD>::kCtasPerSm)
 attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, __nv_bfloat16* __restrict__ out,
                 float* __restrict__ lse, int T, int H, int Dl, float scale_log2) {
   using C = FwdCfg<HD>;
@@ -99,6 +98,7 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, __nv_bfloat16* __res
   uint64_t* p_full = bars + 9;
   uint64_t* o_done = bars + 10;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 11);
+  float* s_xchg = reinterpret_cast<float*>(bars + 12);  // [2 parities][2 halves][128 rows] row-max / row-sum exchange
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int nq = (T + kTile - 1) / kTile;
@@ -117,7 +117,7 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, __nv_bfloat16* __res
     }
     mbar_init(&s_full[0], 1);
     mbar_init(&s_full[1], 1);
-    mbar_init(p_full, 4);
+    mbar_init(p_full, 8);
     mbar_init(o_done, 1);
     fence_mbar_init();
   }
@@ -196,41 +196,67 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, __nv_bfloat16* __res
       }
     }
   } else {
-    // ------------------------------------------------------------------ softmax warps: one thread per q row
+    // ------------------------------------------------------------------ softmax warps: TWO threads per q row
+    // Warp group `half` (warps 2-5 / 6-9) owns kv columns [64*half, 64*half+64) of every row; inside a group warp q
+    // owns TMEM lanes (rows) [32q, 32q+32).  Two warps per SM sub-partition double the issue rate of the exp / FMA
+    // chains (the forward kernel is bound by exactly that).  The two halves of a row agree on the running max through
+    // a double-buffered smem slot + one named barrier per tile; each keeps a partial row sum, combined at the end.
     const int q = warp & 3;
-    const int r = q * 32 + lane;  // row inside the tile == TMEM lane
+    const int half = (warp - 2) >> 2;
+    const int r = q * 32 + lane;
     const uint32_t lane_off = static_cast<uint32_t>(q * 32) << 16;
+    constexpr int kOChunks = HD / 64;  // 32-column chunks of O per half
     float m_run = -INFINITY, l_run = 0.f;
     for (int j = 0; j < n_kv; ++j) {
       mbar_wait(&s_full[j % C::kSBufs], (j / C::kSBufs) & 1);
       tc_fence_after();
-      float s[kTile];
+      float s[64];
 #pragma unroll
-      for (int c = 0; c < 4; ++c) {
+      for (int c = 0; c < 2; ++c) {
         uint32_t tmp[32];
-        tmem_ld32(tS + (j % C::kSBufs) * 128 + lane_off + c * 32, tmp);
+        tmem_ld32(tS + (j % C::kSBufs) * 128 + lane_off + (2 * half + c) * 32, tmp);
         tmem_ld_wait();
 #pragma unroll
         for (int i = 0; i < 32; ++i) s[c * 32 + i] = __uint_as_float(tmp[i]) * scale_log2;
       }
       if (j == qt) {  // diagonal tile: mask kv > q
 #pragma unroll
-        for (int i = 0; i < kTile; ++i)
-          if (i > r) s[i] = -INFINITY;
+        for (int i = 0; i < 64; ++i)
+          if (half * 64 + i > r) s[i] = -INFINITY;
       }
-      float mx = m_run;
+      float m4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};   // 4 independent chains instead of one of 64
 #pragma unroll
-      for (int i = 0; i < kTile; ++i) mx = fmaxf(mx, s[i]);
+      for (int i = 0; i < 64; i += 4) {
+        m4[0] = fmaxf(m4[0], s[i]);
+        m4[1] = fmaxf(m4[1], s[i + 1]);
+        m4[2] = fmaxf(m4[2], s[i + 2]);
+        m4[3] = fmaxf(m4[3], s[i + 3]);
+      }
+      const float mloc = fmaxf(fmaxf(m4[0], m4[1]), fmaxf(m4[2], m4[3]));
+      float* xb = s_xchg + (j & 1) * 256;
+      xb[half * 128 + r] = mloc;
+      asm volatile("bar.sync 1, 256;" ::: "memory");
+      const float mcand = fmaxf(mloc, xb[(half ^ 1) * 128 + r]);   // column 0 is never masked: finite
+      // Lazy rescaling: the reference max only moves when the new row max exceeds it by more than 8 (log2 domain), so
+      // P stays below 2^8 and the TMEM round trip that rescales O is skipped on almost every tile.  O and l are
+      // accumulated against the same reference, so the final O / l and the LSE are exact.
+      const float mx = (mcand > m_run + 8.f) ? mcand : m_run;
       const float alpha = fast_exp2(m_run - mx);
       m_run = mx;
-      float sum = 0.f;
-      uint32_t packed[kTile / 2];
+      float s4[4] = {0.f, 0.f, 0.f, 0.f};
+      uint32_t packed[32];
 #pragma unroll
-      for (int i = 0; i < kTile; i += 2) {
+      for (int i = 0; i < 64; i += 4) {
         const float p0 = fast_exp2(s[i] - mx), p1 = fast_exp2(s[i + 1] - mx);
-        sum += p0 + p1;
+        const float p2 = fast_exp2(s[i + 2] - mx), p3 = fast_exp2(s[i + 3] - mx);
+        s4[0] += p0;
+        s4[1] += p1;
+        s4[2] += p2;
+        s4[3] += p3;
         packed[i >> 1] = pack_bf16(p0, p1);
+        packed[(i >> 1) + 1] = pack_bf16(p2, p3);
       }
+      const float sum = (s4[0] + s4[1]) + (s4[2] + s4[3]);
       l_run = l_run * alpha + sum;
       if (j > 0) {
         // previous PV must be complete before O is rescaled and P is overwritten
@@ -238,7 +264,7 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, __nv_bfloat16* __res
         tc_fence_after();
         if (__any_sync(0xffffffffu, alpha != 1.f)) {
 #pragma unroll
-          for (int c = 0; c < HD / 32; ++c) {
+          for (int c = half * kOChunks; c < (half + 1) * kOChunks; ++c) {
             uint32_t o[32];
             tmem_ld32(tO + lane_off + c * 32, o);
             tmem_ld_wait();
@@ -250,25 +276,29 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, __nv_bfloat16* __res
         }
       }
 #pragma unroll
-      for (int c = 0; c < 4; ++c) {
+      for (int c = 0; c < 2; ++c) {
         uint32_t chunk[16];
 #pragma unroll
         for (int i = 0; i < 16; ++i) chunk[i] = packed[c * 16 + i];
-        st_tile_row32(sP, r, c * 32, chunk);
+        st_tile_row32(sP, r, half * 64 + c * 32, chunk);
       }
       fence_proxy_async_smem();
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(p_full);
     }
-    // epilogue: O / l -> bf16, lse
+    // epilogue: combine the two partial row sums, O / l -> bf16, lse
+    float* xb = s_xchg + (n_kv & 1) * 256;
+    xb[half * 128 + r] = l_run;
+    asm volatile("bar.sync 1, 256;" ::: "memory");
+    const float l_tot = l_run + xb[(half ^ 1) * 128 + r];
     mbar_wait(o_done, (n_kv - 1) & 1);
     tc_fence_after();
-    const float inv_l = 1.f / l_run;
+    const float inv_l = 1.f / l_tot;
     const bool valid = (q0 + r) < T;
     __nv_bfloat16* orow = out + (static_cast<long long>(b) * T + q0 + r) * Dl + h * HD;
 #pragma unroll
-    for (int c = 0; c < HD / 32; ++c) {
+    for (int c = half * kOChunks; c < (half + 1) * kOChunks; ++c) {
       uint32_t o[32];
       tmem_ld32(tO + lane_off + c * 32, o);
       tmem_ld_wait();
@@ -284,7 +314,7 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, __nv_bfloat16* __res
         }
       }
     }
-    if (valid && lse) lse[(static_cast<long long>(b) * H + h) * T + q0 + r] = (m_run + log2f(l_run)) * kLn2;
+    if (half == 0 && valid && lse) lse[(static_cast<long long>(b) * H + h) * T + q0 + r] = (m_run + log2f(l_tot)) * kLn2;
   }
 
   tc_fence_before();
@@ -346,7 +376,11 @@ struct BwdCfg {
   static constexpr int kTileBytes = kTile * HD * 2;  // K, V, Q or dO tile
   static constexpr int kPBytes = kTile * kTile * 2;
   static constexpr int kSmem = 2 * kTileBytes + kStages * 2 * kTileBytes + 2 * kPBytes + 256 + 1024;
-  static constexpr int kTmemCols = 512;  // S/dQ [0,128), dP [128,256), dV [256,256+HD), dK [256+HD, 256+2HD)
+  // S [0,128), dP [128,256), dV [256,256+HD), dK [256+HD,256+2HD); dQ has its own columns [384,448) when hd = 64
+  // (the next tile's S / dP MMAs then overlap the dQ drain) and aliases S when hd = 128 (all 512 columns are taken)
+  static constexpr int kTmemCols = 512;
+  static constexpr bool kDqAliasesS = (HD != 64);
+  static constexpr int kDqCol = kDqAliasesS ? 0 : 384;
 };
 
 __device__ __forceinline__ void red_add_v4(float* addr, float a, float b, float c, float d) {
@@ -408,6 +442,7 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
   const uint32_t tS = tmem_base, tDP = tmem_base + 128, tDV = tmem_base + 256, tDK = tmem_base + 256 + HD;
+  const uint32_t tDQ = tmem_base + C::kDqCol;
 
   if (warp == 0) {
     if (lane == 0) {
@@ -441,7 +476,7 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
         const int st = it % C::kStages;
         const uint32_t q_base = smem_u32(sQ + st * C::kTileBytes), do_base = smem_u32(sDO + st * C::kTileBytes);
         mbar_wait(&qdo_full[st], (it / C::kStages) & 1);
-        if (it > 0) mbar_wait(s_free, (it - 1) & 1);
+        if (C::kDqAliasesS && it > 0) mbar_wait(s_free, (it - 1) & 1);   // dQ(it-1) drained out of the S columns
         tc_fence_after();
 #pragma unroll
         for (int kk = 0; kk < HD / 16; ++kk)
@@ -461,9 +496,13 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
           umma_bf16_ss(tDK, desc_mnmajor(ds_base, kk, kAtom), desc_mnmajor(q_base, kk, kAtom), idesc_kv,
                        (it > 0 || kk > 0) ? 1u : 0u);
         umma_commit(&qdo_empty[st]);
+        if (!C::kDqAliasesS && it > 0) {
+          mbar_wait(s_free, (it - 1) & 1);   // previous dQ tile drained out of its own columns
+          tc_fence_after();
+        }
 #pragma unroll
         for (int kk = 0; kk < kTile / 16; ++kk)  // dQ = dS K   (reduction over the 128 kv rows)
-          umma_bf16_ss(tS, desc_kmajor(ds_base, kk, kAtom), desc_mnmajor(k_base, kk, kAtom), idesc_q, kk > 0);
+          umma_bf16_ss(tDQ, desc_kmajor(ds_base, kk, kAtom), desc_mnmajor(k_base, kk, kAtom), idesc_q, kk > 0);
         umma_commit(dq_full);
       }
     }
@@ -516,7 +555,7 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
 #pragma unroll 1
       for (int c = half * kOutChunks; c < (half + 1) * kOutChunks; ++c) {
         uint32_t v[32];
-        tmem_ld32(tS + lane_off + c * 32, v);
+        tmem_ld32(tDQ + lane_off + c * 32, v);
         tmem_ld_wait();
         if (row_valid) {
 #pragma unroll
@@ -604,7 +643,7 @@ static int launch_fwd(const CUtensorMap& tm, void* out, float* lse, int B, int T
     configured = true;
   }
   dim3 grid((T + kTile - 1) / kTile, H, B);
-  kfn<<<(DPFS_COUNT(), grid), kAttnThreads, C::kSmem, stream>>>(tm, reinterpret_cast<__nv_bfloat16*>(out), lse, T, H, H * HD,
+  kfn<<<(DPFS_COUNT(), grid), kAttnFwdThreads, C::kSmem, stream>>>(tm, reinterpret_cast<__nv_bfloat16*>(out), lse, T, H, H * HD,
                                                scale * kLog2e);
   return static_cast<int>(cudaGetLastError());
 }
