@@ -20,6 +20,7 @@
 #include "dpfs_b200.h"
 
 #include <cudaTypedefs.h>
+#include <stdlib.h>
 
 namespace dpfs {
 
@@ -315,6 +316,280 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, __nv_bfloat16* __res
       }
     }
     if (half == 0 && valid && lse) lse[(static_cast<long long>(b) * H + h) * T + q0 + r] = (m_run + log2f(l_tot)) * kLn2;
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, C::kTmemCols);
+  }
+}
+
+// ================================================================================================= forward, persistent
+// Same math as attn_fwd_kernel, but ONE CTA per SM walks a heavy-first list of (q tile, head, batch) work items.  The
+// per-CTA fixed costs of the one-item-per-CTA kernel (TMEM allocation, barrier setup, the cold Q / K / V loads and the
+// pipeline fill and drain — ~14 CTAs ran back to back on every SM with nothing overlapping between them) are paid once;
+// the loader and the MMA warp run ahead into the next item while the softmax warps finish the current one.
+template <int HD>
+struct FwdPCfg {
+  static constexpr int kStages = 2;
+  static constexpr int kQBufs = (HD == 64) ? 2 : 1;  // hd = 128: 2 x 32 KB of Q would not fit next to K / V / P
+  static constexpr int kQBytes = kTile * HD * 2;
+  static constexpr int kKVBytes = kTile * HD * 2;
+  static constexpr int kPBytes = kTile * kTile * 2;
+  static constexpr int kXchgBytes = 2 * 2 * kTile * 4;
+  static constexpr int kSmem = kQBufs * kQBytes + kStages * 2 * kKVBytes + kPBytes + 256 + kXchgBytes + 1024;
+  static constexpr int kTmemCols = 512;  // S0 [0,128), S1 [128,256), O [256, 256+HD)
+  static constexpr int kOCol = 256;
+};
+
+template <int HD>
+__global__ void __launch_bounds__(kAttnFwdThreads, 1)
+attn_fwd_persistent_kernel(const __grid_constant__ CUtensorMap tm_qkv, __nv_bfloat16* __restrict__ out,
+                           float* __restrict__ lse, int B, int T, int H, int Dl, float scale_log2) {
+  using C = FwdPCfg<HD>;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* sQ = smem;                                 // [kQBufs]
+  uint8_t* sK = sQ + C::kQBufs * C::kQBytes;         // [stage]
+  uint8_t* sV = sK + C::kStages * C::kKVBytes;       // [stage]
+  uint8_t* sP = sV + C::kStages * C::kKVBytes;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sP + C::kPBytes);
+  uint64_t* q_full = bars;        // [2]
+  uint64_t* q_empty = bars + 2;   // [2]
+  uint64_t* k_full = bars + 4;    // [2]
+  uint64_t* v_full = bars + 6;    // [2]
+  uint64_t* kv_empty = bars + 8;  // [2]
+  uint64_t* s_full = bars + 10;   // [2]
+  uint64_t* p_full = bars + 12;
+  uint64_t* o_done = bars + 13;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 14);
+  float* s_xchg = reinterpret_cast<float*>(bars + 16);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int nq = (T + kTile - 1) / kTile;
+  const int HB = H * B;
+  const int n_items = nq * HB;
+
+  if (threadIdx.x == 0) {
+    prefetch_tmap(&tm_qkv);
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(&q_full[i], 1);
+      mbar_init(&q_empty[i], 1);
+      mbar_init(&k_full[i], 1);
+      mbar_init(&v_full[i], 1);
+      mbar_init(&kv_empty[i], 1);
+      mbar_init(&s_full[i], 1);
+    }
+    mbar_init(p_full, 8);
+    mbar_init(o_done, 1);
+    fence_mbar_init();
+  }
+  if (warp == 1) {
+    tmem_alloc(tmem_slot, C::kTmemCols);
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  const uint32_t tS = tmem_base, tO = tmem_base + C::kOCol;
+
+  // work item w (heavy q tiles first): qt = nq-1 - w / HB, h = (w % HB) % H, b = (w % HB) / H
+  if (warp == 0) {
+    if (lane == 0) {
+      int g = 0, it = 0;
+      for (int w = blockIdx.x; w < n_items; w += gridDim.x, ++it) {
+        const int qt = nq - 1 - w / HB, rem = w % HB, h = rem % H, b = rem / H;
+        const int qb = it % C::kQBufs;
+        mbar_wait(&q_empty[qb], ((it / C::kQBufs) & 1) ^ 1);
+        mbar_expect_tx(&q_full[qb], C::kQBytes);
+#pragma unroll
+        for (int a = 0; a < HD / 64; ++a)
+          tma_load_3d(sQ + qb * C::kQBytes + a * (kTile * 128), &tm_qkv, &q_full[qb], h * HD + a * 64, qt * kTile, b);
+        for (int j = 0; j <= qt; ++j, ++g) {
+          const int st = g & 1;
+          mbar_wait(&kv_empty[st], ((g >> 1) & 1) ^ 1);
+          mbar_expect_tx(&k_full[st], C::kKVBytes);
+#pragma unroll
+          for (int a = 0; a < HD / 64; ++a)
+            tma_load_3d(sK + st * C::kKVBytes + a * (kTile * 128), &tm_qkv, &k_full[st], Dl + h * HD + a * 64,
+                        j * kTile, b);
+          mbar_expect_tx(&v_full[st], C::kKVBytes);
+#pragma unroll
+          for (int a = 0; a < HD / 64; ++a)
+            tma_load_3d(sV + st * C::kKVBytes + a * (kTile * 128), &tm_qkv, &v_full[st], 2 * Dl + h * HD + a * 64,
+                        j * kTile, b);
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      constexpr uint32_t idesc_s = make_idesc_bf16(kTile, kTile, false, false);
+      constexpr uint32_t idesc_o = make_idesc_bf16(kTile, HD, false, true);
+      const uint32_t p_base = smem_u32(sP);
+      // S(tile g) = Q(item) K(g)^T into S buffer g & 1; commits "Q buffer free" after the last S of an item
+      auto issue_s = [&](int g, int it, bool first_of_item, bool last_of_item) {
+        const int qb = it % C::kQBufs;
+        if (first_of_item) mbar_wait(&q_full[qb], (it / C::kQBufs) & 1);
+        const int sn = g & 1;
+        mbar_wait(&k_full[sn], (g >> 1) & 1);
+        tc_fence_after();
+        const uint32_t q_base = smem_u32(sQ + qb * C::kQBytes);
+        const uint32_t k_base = smem_u32(sK + sn * C::kKVBytes);
+#pragma unroll
+        for (int kk = 0; kk < HD / 16; ++kk)
+          umma_bf16_ss(tS + sn * 128, desc_kmajor(q_base, kk, kTile * 128), desc_kmajor(k_base, kk, kTile * 128),
+                       idesc_s, kk > 0);
+        umma_commit(&s_full[sn]);
+        if (last_of_item) umma_commit(&q_empty[qb]);
+      };
+      int g = 0, it = 0;
+      for (int w = blockIdx.x; w < n_items; w += gridDim.x, ++it) {
+        const int n_kv = nq - w / HB;  // qt + 1
+        if (it == 0) issue_s(0, 0, true, n_kv == 1);
+        for (int j = 0; j < n_kv; ++j, ++g) {
+          // look one tile ahead (possibly into the next work item) so QK^T overlaps this tile's softmax
+          if (j + 1 < n_kv) {
+            issue_s(g + 1, it, false, j + 2 == n_kv);
+          } else if (w + static_cast<int>(gridDim.x) < n_items) {
+            const int n_kv_next = nq - (w + static_cast<int>(gridDim.x)) / HB;
+            issue_s(g + 1, it + 1, true, n_kv_next == 1);
+          }
+          const int st = g & 1;
+          mbar_wait(p_full, g & 1);
+          mbar_wait(&v_full[st], (g >> 1) & 1);
+          tc_fence_after();
+          const uint32_t v_base = smem_u32(sV + st * C::kKVBytes);
+#pragma unroll
+          for (int kk = 0; kk < kTile / 16; ++kk)
+            umma_bf16_ss(tO, desc_kmajor(p_base, kk, kTile * 128), desc_mnmajor(v_base, kk, kTile * 128), idesc_o,
+                         (j > 0 || kk > 0) ? 1u : 0u);
+          umma_commit(o_done);
+          umma_commit(&kv_empty[st]);
+        }
+      }
+    }
+  } else {
+    const int q = warp & 3;
+    const int half = (warp - 2) >> 2;
+    const int r = q * 32 + lane;
+    const uint32_t lane_off = static_cast<uint32_t>(q * 32) << 16;
+    constexpr int kOChunks = HD / 64;
+    int g = 0, xc = 0;
+    for (int w = blockIdx.x; w < n_items; w += gridDim.x) {
+      const int qt = nq - 1 - w / HB, rem = w % HB, h = rem % H, b = rem / H;
+      const int q0 = qt * kTile;
+      float m_run = -INFINITY, l_run = 0.f;
+      for (int j = 0; j <= qt; ++j, ++g) {
+        mbar_wait(&s_full[g & 1], (g >> 1) & 1);
+        tc_fence_after();
+        float s[64];
+#pragma unroll
+        for (int c = 0; c < 2; ++c) {
+          uint32_t tmp[32];
+          tmem_ld32(tS + (g & 1) * 128 + lane_off + (2 * half + c) * 32, tmp);
+          tmem_ld_wait();
+#pragma unroll
+          for (int i = 0; i < 32; ++i) s[c * 32 + i] = __uint_as_float(tmp[i]) * scale_log2;
+        }
+        if (j == qt) {
+#pragma unroll
+          for (int i = 0; i < 64; ++i)
+            if (half * 64 + i > r) s[i] = -INFINITY;
+        }
+        float m4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
+#pragma unroll
+        for (int i = 0; i < 64; i += 4) {
+          m4[0] = fmaxf(m4[0], s[i]);
+          m4[1] = fmaxf(m4[1], s[i + 1]);
+          m4[2] = fmaxf(m4[2], s[i + 2]);
+          m4[3] = fmaxf(m4[3], s[i + 3]);
+        }
+        const float mloc = fmaxf(fmaxf(m4[0], m4[1]), fmaxf(m4[2], m4[3]));
+        float* xb = s_xchg + (xc & 1) * 256;
+        ++xc;
+        xb[half * 128 + r] = mloc;
+        asm volatile("bar.sync 1, 256;" ::: "memory");
+        const float mcand = fmaxf(mloc, xb[(half ^ 1) * 128 + r]);
+        const float mx = (mcand > m_run + 8.f) ? mcand : m_run;  // lazy rescaling (see attn_fwd_kernel)
+        const float alpha = fast_exp2(m_run - mx);
+        m_run = mx;
+        float s4[4] = {0.f, 0.f, 0.f, 0.f};
+        uint32_t packed[32];
+#pragma unroll
+        for (int i = 0; i < 64; i += 4) {
+          const float p0 = fast_exp2(s[i] - mx), p1 = fast_exp2(s[i + 1] - mx);
+          const float p2 = fast_exp2(s[i + 2] - mx), p3 = fast_exp2(s[i + 3] - mx);
+          s4[0] += p0;
+          s4[1] += p1;
+          s4[2] += p2;
+          s4[3] += p3;
+          packed[i >> 1] = pack_bf16(p0, p1);
+          packed[(i >> 1) + 1] = pack_bf16(p2, p3);
+        }
+        l_run = l_run * alpha + ((s4[0] + s4[1]) + (s4[2] + s4[3]));
+        if (j > 0) {
+          mbar_wait(o_done, (g - 1) & 1);  // PV of the previous tile: O may be rescaled, P may be overwritten
+          tc_fence_after();
+          if (__any_sync(0xffffffffu, alpha != 1.f)) {
+#pragma unroll
+            for (int c = half * kOChunks; c < (half + 1) * kOChunks; ++c) {
+              uint32_t o[32];
+              tmem_ld32(tO + lane_off + c * 32, o);
+              tmem_ld_wait();
+#pragma unroll
+              for (int i = 0; i < 32; ++i) o[i] = __float_as_uint(__uint_as_float(o[i]) * alpha);
+              tmem_st32(tO + lane_off + c * 32, o);
+            }
+            tmem_st_wait();
+          }
+        }
+#pragma unroll
+        for (int c = 0; c < 2; ++c) {
+          uint32_t chunk[16];
+#pragma unroll
+          for (int i = 0; i < 16; ++i) chunk[i] = packed[c * 16 + i];
+          st_tile_row32(sP, r, half * 64 + c * 32, chunk);
+        }
+        fence_proxy_async_smem();
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(p_full);
+      }
+      // item epilogue (the previous item's P / O are free again once this returns: the next p_full needs us)
+      float* xb = s_xchg + (xc & 1) * 256;
+      ++xc;
+      xb[half * 128 + r] = l_run;
+      asm volatile("bar.sync 1, 256;" ::: "memory");
+      const float l_tot = l_run + xb[(half ^ 1) * 128 + r];
+      mbar_wait(o_done, (g - 1) & 1);
+      tc_fence_after();
+      const float inv_l = 1.f / l_tot;
+      const bool valid = (q0 + r) < T;
+      __nv_bfloat16* orow = out + (static_cast<long long>(b) * T + q0 + r) * Dl + h * HD;
+#pragma unroll
+      for (int c = half * kOChunks; c < (half + 1) * kOChunks; ++c) {
+        uint32_t o[32];
+        tmem_ld32(tO + lane_off + c * 32, o);
+        tmem_ld_wait();
+        if (valid) {
+#pragma unroll
+          for (int v8 = 0; v8 < 4; ++v8) {
+            uint4 wv;
+            wv.x = pack_bf16(__uint_as_float(o[8 * v8 + 0]) * inv_l, __uint_as_float(o[8 * v8 + 1]) * inv_l);
+            wv.y = pack_bf16(__uint_as_float(o[8 * v8 + 2]) * inv_l, __uint_as_float(o[8 * v8 + 3]) * inv_l);
+            wv.z = pack_bf16(__uint_as_float(o[8 * v8 + 4]) * inv_l, __uint_as_float(o[8 * v8 + 5]) * inv_l);
+            wv.w = pack_bf16(__uint_as_float(o[8 * v8 + 6]) * inv_l, __uint_as_float(o[8 * v8 + 7]) * inv_l);
+            *reinterpret_cast<uint4*>(orow + c * 32 + v8 * 8) = wv;
+          }
+        }
+      }
+      if (half == 0 && valid && lse)
+        lse[(static_cast<long long>(b) * H + h) * T + q0 + r] = (m_run + log2f(l_tot)) * kLn2;
+      tc_fence_before();   // the O reads above are ordered before the next item's first PV (via p_full)
+    }
   }
 
   tc_fence_before();
@@ -649,6 +924,24 @@ static int launch_fwd(const CUtensorMap& tm, void* out, float* lse, int B, int T
 }
 
 template <int HD>
+static int launch_fwd_persistent(const CUtensorMap& tm, void* out, float* lse, int B, int T, int H, float scale,
+                                 cudaStream_t stream) {
+  using C = FwdPCfg<HD>;
+  auto kfn = attn_fwd_persistent_kernel<HD>;
+  static bool configured = false;
+  if (!configured) {
+    cudaError_t e = cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmem);
+    if (e != cudaSuccess) return static_cast<int>(e);
+    configured = true;
+  }
+  const int items = ((T + kTile - 1) / kTile) * H * B;
+  const int grid = items < num_sms() ? items : num_sms();
+  kfn<<<(DPFS_COUNT(), grid), kAttnFwdThreads, C::kSmem, stream>>>(tm, reinterpret_cast<__nv_bfloat16*>(out), lse, B, T,
+                                                                  H, H * HD, scale * kLog2e);
+  return static_cast<int>(cudaGetLastError());
+}
+
+template <int HD>
 static int launch_bwd(const CUtensorMap& tm_qkv, const CUtensorMap& tm_do, const float* lse, const float* delta,
                       float* dq_acc, void* dqkv, int B, int T, int H, float scale, cudaStream_t stream) {
   using C = BwdCfg<HD>;
@@ -677,6 +970,14 @@ extern "C" int dpfs_attn_fwd(const void* qkv, void* out, float* lse, int B, int 
   CUtensorMap tm;
   int rc = make_tmap_rows3d(&tm, qkv, 3 * H * HD, T, B, 3LL * H * HD);
   if (rc) return rc;
+  static int persistent = -1;
+  if (persistent < 0) {
+    const char* e = getenv("DPFS_ATTN_PERSISTENT");
+    persistent = e ? atoi(e) : 1;
+  }
+  if (persistent)
+    return HD == 64 ? launch_fwd_persistent<64>(tm, out, lse, B, T, H, scale, stream)
+                    : launch_fwd_persistent<128>(tm, out, lse, B, T, H, scale, stream);
   return HD == 64 ? launch_fwd<64>(tm, out, lse, B, T, H, scale, stream)
                   : launch_fwd<128>(tm, out, lse, B, T, H, scale, stream);
 }
