@@ -651,6 +651,11 @@ struct BwdCfg {
   static constexpr int kTileBytes = kTile * HD * 2;  // K, V, Q or dO tile
   static constexpr int kPBytes = kTile * kTile * 2;
   static constexpr int kSmem = 2 * kTileBytes + kStages * 2 * kTileBytes + 2 * kPBytes + 256 + 1024;
+  // persistent variant: K / V double-buffered across work items when they fit (hd = 64: 192 KB)
+  static constexpr int kKvBufs = (HD == 64) ? 2 : 1;
+  static constexpr int kDqSlabBytes = 8 * 4096;  // one 32x32 fp32 block per math warp
+  static constexpr int kSmemPersistent = kSmem + (kKvBufs - 1) * 2 * kTileBytes + kDqSlabBytes;
+  static_assert(kSmemPersistent <= 232448, "persistent backward does not fit in shared memory");
   // S [0,128), dP [128,256), dV [256,256+HD), dK [256+HD,256+2HD); dQ has its own columns [384,448) when hd = 64
   // (the next tile's S / dP MMAs then overlap the dQ drain) and aliases S when hd = 128 (all 512 columns are taken)
   static constexpr int kTmemCols = 512;
@@ -878,6 +883,275 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
   }
 }
 
+template <int HD>
+__global__ void __launch_bounds__(kAttnBwdThreads, 1)
+attn_bwd_persistent_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constant__ CUtensorMap tm_do,
+                const __grid_constant__ CUtensorMap tm_dq, const __grid_constant__ CUtensorMap tm_dkv,
+                const float* __restrict__ lse, const float* __restrict__ delta,
+                __nv_bfloat16* __restrict__ dqkv, int B, int T, int H, int Dl, float scale, float scale_log2) {
+  using C = BwdCfg<HD>;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* sKV = smem;                               // [kv buffer]{K, V}
+  uint8_t* sQ = sKV + C::kKvBufs * 2 * C::kTileBytes;  // [stage]
+  uint8_t* sDO = sQ + C::kStages * C::kTileBytes;    // [stage]
+  uint8_t* sP = sDO + C::kStages * C::kTileBytes;
+  uint8_t* sDS = sP + C::kPBytes;
+  uint8_t* sDQ = sDS + C::kPBytes;                   // [math warp] 32 rows x 32 fp32, 128B-swizzled (TMA reduce source)
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sDQ + C::kDqSlabBytes);
+  uint64_t* kv_full = bars;        // [2]
+  uint64_t* qdo_full = bars + 2;   // [2]
+  uint64_t* qdo_empty = bars + 4;  // [2]
+  uint64_t* sdp_full = bars + 6;
+  uint64_t* pds_full = bars + 7;
+  uint64_t* dq_full = bars + 8;
+  uint64_t* s_free = bars + 9;
+  uint64_t* kv_empty = bars + 10;  // [2]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 12);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int nq = (T + kTile - 1) / kTile;
+  const int HB = H * B;
+  const int n_items = nq * HB;  // work item w: kv tile jt = w / HB (tile 0 has the most q tiles -> first), h, b
+
+  if (threadIdx.x == 0) {
+    prefetch_tmap(&tm_qkv);
+    prefetch_tmap(&tm_do);
+    prefetch_tmap(&tm_dq);
+    prefetch_tmap(&tm_dkv);
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(&kv_full[i], 1);
+      mbar_init(&kv_empty[i], 1);
+      mbar_init(&qdo_full[i], 1);
+      mbar_init(&qdo_empty[i], 1);
+    }
+    mbar_init(sdp_full, 1);
+    mbar_init(pds_full, 8);
+    mbar_init(dq_full, 1);
+    mbar_init(s_free, 8);
+    fence_mbar_init();
+  }
+  if (warp == 1) {
+    tmem_alloc(tmem_slot, C::kTmemCols);
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  const uint32_t tS = tmem_base, tDP = tmem_base + 128, tDV = tmem_base + 256, tDK = tmem_base + 256 + HD;
+  const uint32_t tDQ = tmem_base + C::kDqCol;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      int gs = 0, item = 0;
+      for (int w = blockIdx.x; w < n_items; w += gridDim.x, ++item) {
+        const int jt = w / HB, rem = w % HB, h = rem % H, b = rem / H;
+        const int kv0 = jt * kTile, n_it = nq - jt;
+        const int kb = item % C::kKvBufs;
+        uint8_t* sK = sKV + kb * 2 * C::kTileBytes;
+        uint8_t* sV = sK + C::kTileBytes;
+        mbar_wait(&kv_empty[kb], ((item / C::kKvBufs) & 1) ^ 1);   // the MMAs that read this K / V buffer are done
+        mbar_expect_tx(&kv_full[kb], 2 * C::kTileBytes);
+#pragma unroll
+        for (int a = 0; a < HD / 64; ++a) {
+          tma_load_3d(sK + a * (kTile * 128), &tm_qkv, &kv_full[kb], Dl + h * HD + a * 64, kv0, b);
+          tma_load_3d(sV + a * (kTile * 128), &tm_qkv, &kv_full[kb], 2 * Dl + h * HD + a * 64, kv0, b);
+        }
+        for (int it = 0; it < n_it; ++it, ++gs) {
+          const int st = gs % C::kStages;
+          const int q0 = (jt + it) * kTile;
+          mbar_wait(&qdo_empty[st], ((gs / C::kStages) & 1) ^ 1);
+          mbar_expect_tx(&qdo_full[st], 2 * C::kTileBytes);
+#pragma unroll
+          for (int a = 0; a < HD / 64; ++a) {
+            tma_load_3d(sQ + st * C::kTileBytes + a * (kTile * 128), &tm_qkv, &qdo_full[st], h * HD + a * 64, q0, b);
+            tma_load_3d(sDO + st * C::kTileBytes + a * (kTile * 128), &tm_do, &qdo_full[st], h * HD + a * 64, q0, b);
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      constexpr uint32_t idesc_s = make_idesc_bf16(kTile, kTile, false, false);   // S, dP
+      constexpr uint32_t idesc_kv = make_idesc_bf16(kTile, HD, true, true);       // dV, dK
+      constexpr uint32_t idesc_q = make_idesc_bf16(kTile, HD, false, true);       // dQ
+      const uint32_t p_base = smem_u32(sP), ds_base = smem_u32(sDS);
+      constexpr uint32_t kAtom = kTile * 128;
+      int gs = 0, item = 0;
+      for (int w = blockIdx.x; w < n_items; w += gridDim.x, ++item) {
+        const int n_it = nq - w / HB;
+        const int kb = item % C::kKvBufs;
+        const uint32_t k_base = smem_u32(sKV + kb * 2 * C::kTileBytes), v_base = k_base + C::kTileBytes;
+        mbar_wait(&kv_full[kb], (item / C::kKvBufs) & 1);
+        for (int it = 0; it < n_it; ++it, ++gs) {
+          const int st = gs % C::kStages;
+          const uint32_t q_base = smem_u32(sQ + st * C::kTileBytes), do_base = smem_u32(sDO + st * C::kTileBytes);
+          mbar_wait(&qdo_full[st], (gs / C::kStages) & 1);
+          if (C::kDqAliasesS && gs > 0) mbar_wait(s_free, (gs - 1) & 1);   // dQ(gs-1) drained out of the S columns
+          tc_fence_after();
+#pragma unroll
+          for (int kk = 0; kk < HD / 16; ++kk)
+            umma_bf16_ss(tS, desc_kmajor(q_base, kk, kAtom), desc_kmajor(k_base, kk, kAtom), idesc_s, kk > 0);
+#pragma unroll
+          for (int kk = 0; kk < HD / 16; ++kk)
+            umma_bf16_ss(tDP, desc_kmajor(do_base, kk, kAtom), desc_kmajor(v_base, kk, kAtom), idesc_s, kk > 0);
+          umma_commit(sdp_full);
+          mbar_wait(pds_full, gs & 1);
+          tc_fence_after();
+          if (!C::kDqAliasesS && gs > 0) {
+            mbar_wait(s_free, (gs - 1) & 1);   // previous dQ tile drained out of its own columns
+            tc_fence_after();
+          }
+          // dQ first: the math warps drain it (smem slab + TMA reduce) while dV / dK accumulate
+#pragma unroll
+          for (int kk = 0; kk < kTile / 16; ++kk)  // dQ = dS K   (reduction over the 128 kv rows)
+            umma_bf16_ss(tDQ, desc_kmajor(ds_base, kk, kAtom), desc_mnmajor(k_base, kk, kAtom), idesc_q, kk > 0);
+          umma_commit(dq_full);
+#pragma unroll
+          for (int kk = 0; kk < kTile / 16; ++kk)  // dV += P^T dO   (reduction over the 128 q rows)
+            umma_bf16_ss(tDV, desc_mnmajor(p_base, kk, kAtom), desc_mnmajor(do_base, kk, kAtom), idesc_kv,
+                         (it > 0 || kk > 0) ? 1u : 0u);
+#pragma unroll
+          for (int kk = 0; kk < kTile / 16; ++kk)  // dK += dS^T Q
+            umma_bf16_ss(tDK, desc_mnmajor(ds_base, kk, kAtom), desc_mnmajor(q_base, kk, kAtom), idesc_kv,
+                         (it > 0 || kk > 0) ? 1u : 0u);
+          umma_commit(&qdo_empty[st]);
+        }
+        umma_commit(&kv_empty[kb]);   // K / V of this item are no longer read
+      }
+    }
+  } else {
+    // 8 warps: warp group `half` (0/1) owns kv columns [64*half, 64*half+64) of every row; inside a group warp q owns
+    // TMEM lanes (rows) [32q, 32q+32).  Two warps per SM sub-partition hide each other's exp / TMEM latency.
+    const int q = warp & 3;            // the hardware ties a warp to TMEM lanes [32*(warp%4), +32)
+    const int half = (warp - 2) >> 2;  // warps 2-5 -> 0, warps 6-9 -> 1 (each group covers all four lane quarters)
+    const int r = q * 32 + lane;
+    const uint32_t lane_off = static_cast<uint32_t>(q * 32) << 16;
+    constexpr int kOutChunks = HD / 64;  // 32-column chunks of dQ / dK / dV per warp group
+    // row statistics of step (w, it); loaded one step ahead so the global-load latency hides behind the dQ drain
+    auto load_stats = [&](int w, int it, float& l2, float& dl) {
+      const int jt_ = w / HB, rem_ = w % HB;
+      const int row = (jt_ + it) * kTile + r;
+      l2 = 0.f;
+      dl = 0.f;
+      if (w < n_items && row < T) {
+        const long long idx = (static_cast<long long>(rem_ / H) * H + rem_ % H) * T + row;
+        l2 = lse[idx] * kLog2e;
+        dl = delta[idx];
+      }
+    };
+    int gs = 0, item = 0;
+    float lse2_nx, dlt_nx;
+    load_stats(blockIdx.x, 0, lse2_nx, dlt_nx);
+    for (int w = blockIdx.x; w < n_items; w += gridDim.x, ++item) {
+    const int jt = w / HB, rem = w % HB, h = rem % H, b = rem / H;
+    const int kv0 = jt * kTile, n_it = nq - jt;
+    for (int it = 0; it < n_it; ++it, ++gs) {
+      const int q0 = (jt + it) * kTile;
+      const bool row_valid = (q0 + r) < T;
+      const float lse2 = lse2_nx, dlt = dlt_nx;
+      mbar_wait(sdp_full, gs & 1);
+      tc_fence_after();
+#pragma unroll 1
+      for (int c = 2 * half; c < 2 * half + 2; ++c) {
+        uint32_t sv[32], dv[32];
+        tmem_ld32(tS + lane_off + c * 32, sv);
+        tmem_ld32(tDP + lane_off + c * 32, dv);
+        tmem_ld_wait();
+        uint32_t pp[16], dd[16];
+#pragma unroll
+        for (int i = 0; i < 32; i += 2) {
+          float p0 = fast_exp2(__uint_as_float(sv[i]) * scale_log2 - lse2);
+          float p1 = fast_exp2(__uint_as_float(sv[i + 1]) * scale_log2 - lse2);
+          const int col = c * 32 + i;
+          if (!row_valid || (it == 0 && col > r)) p0 = 0.f;
+          if (!row_valid || (it == 0 && col + 1 > r)) p1 = 0.f;
+          const float d0 = p0 * (__uint_as_float(dv[i]) - dlt) * scale;
+          const float d1 = p1 * (__uint_as_float(dv[i + 1]) - dlt) * scale;
+          pp[i >> 1] = pack_bf16(p0, p1);
+          dd[i >> 1] = pack_bf16(d0, d1);
+        }
+        st_tile_row32(sP, r, c * 32, pp);
+        st_tile_row32(sDS, r, c * 32, dd);
+      }
+      fence_proxy_async_smem();
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(pds_full);
+      if (it + 1 < n_it) load_stats(w, it + 1, lse2_nx, dlt_nx);
+      else load_stats(w + gridDim.x, 0, lse2_nx, dlt_nx);
+      // dQ tile -> this warp's smem slab -> one TMA reduce-add per 32x32 fp32 block (rows past T are clipped by the
+      // tensor map); the L2 does the accumulation in 128-byte lines while the warp goes on with the next tile
+      mbar_wait(dq_full, gs & 1);
+      tc_fence_after();
+      uint8_t* slab = sDQ + (warp - 2) * 4096;
+#pragma unroll 1
+      for (int c = half * kOutChunks; c < (half + 1) * kOutChunks; ++c) {
+        uint32_t v[32];
+        tmem_ld32(tDQ + lane_off + c * 32, v);
+        tmem_ld_wait();
+        if (lane == 0) tma_store_wait_read<0>();   // the previous reduce has finished reading the slab
+        __syncwarp();
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+          *reinterpret_cast<uint4*>(slab + lane * 128 + ((j ^ (lane & 7)) << 4)) =
+              make_uint4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+        fence_proxy_async_smem();
+        __syncwarp();
+        if (lane == 0) {
+          tma_reduce_add_3d(&tm_dq, slab, h * HD + c * 32, q0 + q * 32, b);
+          tma_store_commit();
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(s_free);
+    }
+    // dV / dK of this item are complete once every MMA of the item has retired (the K / V release barrier)
+    mbar_wait(&kv_empty[item % C::kKvBufs], (item / C::kKvBufs) & 1);
+    tc_fence_after();
+    uint8_t* slab = sDQ + (warp - 2) * 4096;
+#pragma unroll 1
+    for (int which = 0; which < 2; ++which) {  // 0: dK -> segment 1, 1: dV -> segment 2
+      const uint32_t tsrc = which == 0 ? tDK : tDV;
+#pragma unroll 1
+      for (int c = half * kOutChunks; c < (half + 1) * kOutChunks; ++c) {
+        uint32_t v[32];
+        tmem_ld32(tsrc + lane_off + c * 32, v);
+        tmem_ld_wait();
+        if (lane == 0) tma_store_wait_read<0>();   // the slab's previous contents have been read out
+        __syncwarp();
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {   // 32 rows x 64 B, 64B-swizzled: 16-byte chunk j of row l at j ^ ((l >> 1) & 3)
+          uint4 o;
+          o.x = pack_bf16(__uint_as_float(v[8 * j + 0]), __uint_as_float(v[8 * j + 1]));
+          o.y = pack_bf16(__uint_as_float(v[8 * j + 2]), __uint_as_float(v[8 * j + 3]));
+          o.z = pack_bf16(__uint_as_float(v[8 * j + 4]), __uint_as_float(v[8 * j + 5]));
+          o.w = pack_bf16(__uint_as_float(v[8 * j + 6]), __uint_as_float(v[8 * j + 7]));
+          *reinterpret_cast<uint4*>(slab + lane * 64 + ((j ^ ((lane >> 1) & 3)) << 4)) = o;
+        }
+        fence_proxy_async_smem();
+        __syncwarp();
+        if (lane == 0) {   // rows past T are clipped by the tensor map
+          tma_store_3d(&tm_dkv, slab, (which + 1) * Dl + h * HD + c * 32, kv0 + q * 32, b);
+          tma_store_commit();
+        }
+      }
+    }
+    tc_fence_before();   // dK / dV reads are ordered before the next item's first MMAs (via pds_full)
+    }
+    if (lane == 0) tma_store_wait<0>();
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, C::kTmemCols);
+  }
+}
+
 // ------------------------------------------------------------------------------------------------- host
 static PFN_cuTensorMapEncodeTiled_v12000 encode_fn() {
   static PFN_cuTensorMapEncodeTiled_v12000 fn = nullptr;
@@ -902,6 +1176,34 @@ static int make_tmap_rows3d(CUtensorMap* tm, const void* ptr, int cols, int T, i
   cuuint32_t estr[3] = {1, 1, 1};
   CUresult r = fn(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<void*>(ptr), dims, strides, box, estr,
                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  return r == CUDA_SUCCESS ? 0 : -2;
+}
+
+// 3-D fp32 map over the dQ accumulator [B][T][Dl]: box = 32 cols (128 B, swizzled) x 32 rows x 1 batch.
+static int make_tmap_dq(CUtensorMap* tm, const void* ptr, int Dl, int T, int B) {
+  auto fn = encode_fn();
+  if (!fn) return -1;
+  cuuint64_t dims[3] = {static_cast<cuuint64_t>(Dl), static_cast<cuuint64_t>(T), static_cast<cuuint64_t>(B)};
+  cuuint64_t strides[2] = {static_cast<cuuint64_t>(Dl) * 4, static_cast<cuuint64_t>(Dl) * 4 * T};
+  cuuint32_t box[3] = {32, 32, 1};
+  cuuint32_t estr[3] = {1, 1, 1};
+  CUresult r = fn(tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, const_cast<void*>(ptr), dims, strides, box, estr,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  return r == CUDA_SUCCESS ? 0 : -2;
+}
+
+// 3-D bf16 map over dqkv [B][T][3*Dl] for the dK / dV stores: box = 32 cols (64 B, swizzled) x 32 rows x 1 batch.
+static int make_tmap_dkv(CUtensorMap* tm, const void* ptr, int cols, int T, int B) {
+  auto fn = encode_fn();
+  if (!fn) return -1;
+  cuuint64_t dims[3] = {static_cast<cuuint64_t>(cols), static_cast<cuuint64_t>(T), static_cast<cuuint64_t>(B)};
+  cuuint64_t strides[2] = {static_cast<cuuint64_t>(cols) * 2, static_cast<cuuint64_t>(cols) * 2 * T};
+  cuuint32_t box[3] = {32, 32, 1};
+  cuuint32_t estr[3] = {1, 1, 1};
+  CUresult r = fn(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<void*>(ptr), dims, strides, box, estr,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_64B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   return r == CUDA_SUCCESS ? 0 : -2;
 }
@@ -959,6 +1261,26 @@ static int launch_bwd(const CUtensorMap& tm_qkv, const CUtensorMap& tm_do, const
   return static_cast<int>(cudaGetLastError());
 }
 
+template <int HD>
+static int launch_bwd_persistent(const CUtensorMap& tm_qkv, const CUtensorMap& tm_do, const CUtensorMap& tm_dq,
+                                 const CUtensorMap& tm_dkv,                                 const float* lse, const float* delta, void* dqkv, int B, int T, int H, float scale,
+                                 cudaStream_t stream) {
+  using C = BwdCfg<HD>;
+  auto kfn = attn_bwd_persistent_kernel<HD>;
+  static bool configured = false;
+  if (!configured) {
+    cudaError_t e = cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmemPersistent);
+    if (e != cudaSuccess) return static_cast<int>(e);
+    configured = true;
+  }
+  const int items = ((T + kTile - 1) / kTile) * H * B;
+  const int grid = items < num_sms() ? items : num_sms();
+  kfn<<<(DPFS_COUNT(), grid), kAttnBwdThreads, C::kSmemPersistent, stream>>>(tm_qkv, tm_do, tm_dq, tm_dkv, lse, delta,
+                                                                  reinterpret_cast<__nv_bfloat16*>(dqkv), B, T, H,
+                                                                  H * HD, scale, scale * kLog2e);
+  return static_cast<int>(cudaGetLastError());
+}
+
 }  // namespace dpfs
 
 using namespace dpfs;
@@ -1004,8 +1326,24 @@ extern "C" int dpfs_attn_bwd(const void* qkv, const void* out, const void* d_out
         reinterpret_cast<const __nv_bfloat16*>(out), reinterpret_cast<const __nv_bfloat16*>(d_out), delta, B, T, H,
         HD);
   }
-  rc = HD == 64 ? launch_bwd<64>(tm_qkv, tm_do, lse, delta, dq_acc, dqkv, B, T, H, scale, stream)
-                : launch_bwd<128>(tm_qkv, tm_do, lse, delta, dq_acc, dqkv, B, T, H, scale, stream);
+  static int persistent = -1;
+  if (persistent < 0) {
+    const char* e = getenv("DPFS_ATTN_PERSISTENT");
+    persistent = e ? atoi(e) : 1;
+  }
+  if (persistent) {
+    CUtensorMap tm_dq;
+    rc = make_tmap_dq(&tm_dq, dq_acc, Dl, T, B);
+    if (rc) return rc;
+    CUtensorMap tm_dkv;
+    rc = make_tmap_dkv(&tm_dkv, dqkv, 3 * Dl, T, B);
+    if (rc) return rc;
+    rc = HD == 64
+             ? launch_bwd_persistent<64>(tm_qkv, tm_do, tm_dq, tm_dkv, lse, delta, dqkv, B, T, H, scale, stream)
+             : launch_bwd_persistent<128>(tm_qkv, tm_do, tm_dq, tm_dkv, lse, delta, dqkv, B, T, H, scale, stream);
+  } else
+    rc = HD == 64 ? launch_bwd<64>(tm_qkv, tm_do, lse, delta, dq_acc, dqkv, B, T, H, scale, stream)
+                  : launch_bwd<128>(tm_qkv, tm_do, lse, delta, dq_acc, dqkv, B, T, H, scale, stream);
   if (rc) return rc;
   {
     const long long total = M * (Dl / 4);
