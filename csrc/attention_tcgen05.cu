@@ -604,44 +604,51 @@ attn_fwd_persistent_kernel(const __grid_constant__ CUtensorMap tm_qkv, __nv_bflo
 // delta[b][h][i] = sum_c dO[i][c] * O[i][c]   (one warp per (row, head))
 __global__ void attn_delta_kernel(const __nv_bfloat16* __restrict__ o, const __nv_bfloat16* __restrict__ d_o,
                                   float* __restrict__ delta, int B, int T, int H, int HD) {
-  const int warps = (blockDim.x >> 5) * gridDim.x;
-  const int lane = threadIdx.x & 31;
-  const long long total = static_cast<long long>(B) * T * H;
+  // one 16-byte vector (8 bf16) of O and dO per thread; the HD/8 consecutive lanes of a head reduce by shuffle
   const int Dl = H * HD;
-  for (long long w = static_cast<long long>(blockIdx.x) * (blockDim.x >> 5) + (threadIdx.x >> 5); w < total;
-       w += warps) {
-    const long long row = w / H;
-    const int h = static_cast<int>(w % H);
-    const __nv_bfloat16* po = o + row * Dl + h * HD;
-    const __nv_bfloat16* pd = d_o + row * Dl + h * HD;
+  const int vec = Dl >> 3, grp = HD >> 3;  // grp = 8 (hd 64) or 16 (hd 128): divides the warp
+  const long long total = static_cast<long long>(B) * T * vec;
+  const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
+  const long long rounds = (total + stride - 1) / stride;
+  long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x;
+  for (long long it = 0; it < rounds; ++it, i += stride) {
     float acc = 0.f;
-    for (int c = lane * 2; c < HD; c += 64) {
-      const float2 a = unpack_bf16(*reinterpret_cast<const uint32_t*>(po + c));
-      const float2 g = unpack_bf16(*reinterpret_cast<const uint32_t*>(pd + c));
-      acc += a.x * g.x + a.y * g.y;
+    const bool live = i < total;
+    if (live) {
+      const uint4 a = __ldg(reinterpret_cast<const uint4*>(o) + i);
+      const uint4 g = __ldg(reinterpret_cast<const uint4*>(d_o) + i);
+      const uint32_t aw[4] = {a.x, a.y, a.z, a.w}, gw[4] = {g.x, g.y, g.z, g.w};
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        const float2 x = unpack_bf16(aw[q]), y = unpack_bf16(gw[q]);
+        acc += x.x * y.x + x.y * y.y;
+      }
     }
-    acc = warp_sum(acc);
-    if (lane == 0) {
+    for (int off = grp >> 1; off > 0; off >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, off);
+    if (live && (i % grp) == 0) {
+      const long long row = i / vec;
+      const int h = static_cast<int>(i % vec) / grp;
       const long long bb = row / T, tt = row % T;
       delta[(bb * H + h) * T + tt] = acc;
     }
   }
 }
-
-// dq fp32 [M][Dl] -> bf16 into dqkv[:, 0:Dl]
 __global__ void attn_dq_convert_kernel(const float* __restrict__ dq, __nv_bfloat16* __restrict__ dqkv, long long M,
                                        int Dl) {
-  const int vec = Dl / 4;
+  const int vec = Dl / 8;
   const long long total = M * vec;
   for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
        i += static_cast<long long>(gridDim.x) * blockDim.x) {
     const long long row = i / vec;
-    const int c = static_cast<int>(i % vec) * 4;
-    const float4 v = *reinterpret_cast<const float4*>(dq + row * Dl + c);
-    uint2 o;
-    o.x = pack_bf16(v.x, v.y);
-    o.y = pack_bf16(v.z, v.w);
-    *reinterpret_cast<uint2*>(dqkv + row * 3 * Dl + c) = o;
+    const int c = static_cast<int>(i % vec) * 8;
+    const float4 v0 = __ldcs(reinterpret_cast<const float4*>(dq + row * Dl + c));
+    const float4 v1 = __ldcs(reinterpret_cast<const float4*>(dq + row * Dl + c + 4));
+    uint4 o;
+    o.x = pack_bf16(v0.x, v0.y);
+    o.y = pack_bf16(v0.z, v0.w);
+    o.z = pack_bf16(v1.x, v1.y);
+    o.w = pack_bf16(v1.z, v1.w);
+    *reinterpret_cast<uint4*>(dqkv + row * 3 * Dl + c) = o;
   }
 }
 
@@ -1319,8 +1326,8 @@ extern "C" int dpfs_attn_bwd(const void* qkv, const void* out, const void* d_out
   if (rc) return rc;
   cudaMemsetAsync(dq_acc, 0, sizeof(float) * M * Dl, stream);
   {
-    const long long warps = M * H;
-    long long blocks = (warps + 7) / 8;
+    const long long vecs = M * (Dl / 8);
+    long long blocks = (vecs + 255) / 256;
     if (blocks > num_sms() * 16LL) blocks = num_sms() * 16LL;
     attn_delta_kernel<<<(DPFS_COUNT(), static_cast<int>(blocks)), 256, 0, stream>>>(
         reinterpret_cast<const __nv_bfloat16*>(out), reinterpret_cast<const __nv_bfloat16*>(d_out), delta, B, T, H,
@@ -1346,7 +1353,7 @@ extern "C" int dpfs_attn_bwd(const void* qkv, const void* out, const void* d_out
                   : launch_bwd<128>(tm_qkv, tm_do, lse, delta, dq_acc, dqkv, B, T, H, scale, stream);
   if (rc) return rc;
   {
-    const long long total = M * (Dl / 4);
+    const long long total = M * (Dl / 8);
     long long blocks = (total + 255) / 256;
     if (blocks > num_sms() * 16LL) blocks = num_sms() * 16LL;
     attn_dq_convert_kernel<<<(DPFS_COUNT(), static_cast<int>(blocks)), 256, 0, stream>>>(
