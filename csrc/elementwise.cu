@@ -159,7 +159,9 @@ __global__ void __launch_bounds__(kNormThreads) add_rmsnorm_fwd_kernel(
 // dx = dres + rstd * (g - xhat * mean(g * xhat)),  g = dy * scale, xhat = x * rstd;  dscale = sum_rows dy * xhat.
 // Each block writes one row of per-block dscale partials into `scratch` [gridDim.x][D]; a second kernel sums them
 // in a fixed order (deterministic).
-template <typename XT, typename GT, int NV>
+// CS: also emit per-block column sums of the produced dx (the bias gradient of the row-parallel linear whose output
+// this residual-stream gradient is) as a second row of partials: scratch is then [gridDim.x][2 * D].
+template <typename XT, typename GT, int NV, bool CS = false>
 __global__ void __launch_bounds__(kNormThreads) rmsnorm_bwd_kernel(
     const GT* __restrict__ dy, const XT* __restrict__ x, const float* __restrict__ rstd_in,
     const float* __restrict__ scale, const float* __restrict__ dres, float* __restrict__ dx,
@@ -167,12 +169,16 @@ __global__ void __launch_bounds__(kNormThreads) rmsnorm_bwd_kernel(
   __shared__ float red[kNormThreads / 32][32 * 4];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int wpb = kNormThreads / 32;
-  float sc[NV][4], ds[NV][4];
+  const int ldp = CS ? 2 * D : D;  // row pitch of the partials
+  float sc[NV][4], ds[NV][4], cs[CS ? NV : 1][4];
 #pragma unroll
   for (int i = 0; i < NV; ++i) {
     const int c = (i * 32 + lane) * 4;
 #pragma unroll
-    for (int j = 0; j < 4; ++j) ds[i][j] = 0.f;
+    for (int j = 0; j < 4; ++j) {
+      ds[i][j] = 0.f;
+      if (CS) cs[i][j] = 0.f;
+    }
     if (c < D) load4<float>(scale + c, sc[i]);
   }
   for (int row = blockIdx.x * wpb + warp; row < M; row += gridDim.x * wpb) {
@@ -217,6 +223,10 @@ __global__ void __launch_bounds__(kNormThreads) rmsnorm_bwd_kernel(
         for (int j = 0; j < 4; ++j) o[j] = rstd * (g[i][j] - xh[i][j] * dot) + rs[i][j];
         if (dx) store4<float>(dx + off + c, o);
         if (dx_bf16) store4<__nv_bfloat16>(dx_bf16 + off + c, o);
+        if (CS) {
+#pragma unroll
+          for (int j = 0; j < 4; ++j) cs[i][j] += o[j];
+        }
       }
     }
   }
@@ -234,39 +244,65 @@ __global__ void __launch_bounds__(kNormThreads) rmsnorm_bwd_kernel(
         for (int w = 0; w < wpb; ++w)
 #pragma unroll
           for (int j = 0; j < 4; ++j) o[j] += red[w][lane * 4 + j];
-        store4<float>(scratch + static_cast<long long>(blockIdx.x) * D + c, o);
+        store4<float>(scratch + static_cast<long long>(blockIdx.x) * ldp + c, o);
+      }
+    }
+  }
+  if (CS) {
+#pragma unroll
+    for (int i = 0; i < NV; ++i) {
+      __syncthreads();
+#pragma unroll
+      for (int j = 0; j < 4; ++j) red[warp][lane * 4 + j] = cs[i][j];
+      __syncthreads();
+      if (warp == 0) {
+        const int c = (i * 32 + lane) * 4;
+        if (c < D) {
+          float o[4] = {0.f, 0.f, 0.f, 0.f};
+          for (int w = 0; w < wpb; ++w)
+#pragma unroll
+            for (int j = 0; j < 4; ++j) o[j] += red[w][lane * 4 + j];
+          store4<float>(scratch + static_cast<long long>(blockIdx.x) * ldp + D + c, o);
+        }
       }
     }
   }
 }
 
-// out[c] = sum_b partial[b][c].  Block = 32 columns x 8 row-groups: each warp sums a strided subset of the rows of
-// its 32 columns (coalesced 128-byte reads), the 8 partial sums meet in shared memory in a fixed order.
-__global__ void __launch_bounds__(256) reduce_partials_kernel(const float* __restrict__ partial,
-                                                              float* __restrict__ out, int nblocks, int D,
-                                                              int accumulate) {
-  __shared__ float sm[8][33];
+// out[c] = sum_b partial[b][c].  Block = 32 columns x 32 row-groups: each warp sums a strided subset of the rows of
+// its 32 columns (coalesced 128-byte reads, 8 independent loads in flight: the kernel is pure L2 latency), the 32
+// partial sums meet in shared memory in a fixed order.  Columns [split, D) (if any) go to out1[c - split] and are
+// never accumulated.
+constexpr int kReduceGroups = 32;
+__global__ void __launch_bounds__(kReduceGroups * 32) reduce_partials_kernel(const float* __restrict__ partial,
+                                                                             float* __restrict__ out, int nblocks,
+                                                                             int D, int accumulate,
+                                                                             float* __restrict__ out1 = nullptr,
+                                                                             int split = 0x7fffffff) {
+  __shared__ float sm[kReduceGroups][33];
   const int lane = threadIdx.x & 31, grp = threadIdx.x >> 5;
   const int c = blockIdx.x * 32 + lane;
   float s = 0.f;
   if (c < D) {
+    constexpr int G = kReduceGroups;
+    const float* p = partial + c;
     int b = grp;
-    for (; b + 24 < nblocks; b += 32) {  // 4 independent loads in flight
-      const float a0 = partial[static_cast<long long>(b) * D + c];
-      const float a1 = partial[static_cast<long long>(b + 8) * D + c];
-      const float a2 = partial[static_cast<long long>(b + 16) * D + c];
-      const float a3 = partial[static_cast<long long>(b + 24) * D + c];
-      s += (a0 + a1) + (a2 + a3);
+    for (; b + 7 * G < nblocks; b += 8 * G) {
+      float a[8];
+#pragma unroll
+      for (int u = 0; u < 8; ++u) a[u] = p[static_cast<long long>(b + u * G) * D];
+      s += ((a[0] + a[1]) + (a[2] + a[3])) + ((a[4] + a[5]) + (a[6] + a[7]));
     }
-    for (; b < nblocks; b += 8) s += partial[static_cast<long long>(b) * D + c];
+    for (; b < nblocks; b += G) s += p[static_cast<long long>(b) * D];
   }
   sm[grp][lane] = s;
   __syncthreads();
   if (grp == 0 && c < D) {
     float t = 0.f;
 #pragma unroll
-    for (int g = 0; g < 8; ++g) t += sm[g][lane];
-    out[c] = accumulate ? out[c] + t : t;
+    for (int g = 0; g < kReduceGroups; ++g) t += sm[g][lane];
+    if (c >= split) out1[c - split] = t;
+    else out[c] = accumulate ? out[c] + t : t;
   }
 }
 
@@ -744,31 +780,57 @@ extern "C" int dpfs_add_rmsnorm_fwd(const float* x, const void* y_bf16, const fl
   return static_cast<int>(cudaGetLastError());
 }
 
-extern "C" int dpfs_rmsnorm_bwd(const void* dy, int dy_bf16, const void* x, int x_bf16, const float* rstd,
-                                const float* scale, const float* dres, float* dx, void* dx_bf16, float* dscale,
-                                int dscale_accumulate, float* scratch, int M, int D, cudaStream_t stream) {
+template <bool CS>
+static int rmsnorm_bwd_launch(const void* dy, int dy_bf16, const void* x, int x_bf16, const float* rstd,
+                              const float* scale, const float* dres, float* dx, void* dx_bf16, float* dscale,
+                              int dscale_accumulate, float* dbias, float* scratch, int M, int D,
+                              cudaStream_t stream) {
   if (D % 4 != 0 || D > 128 * kMaxNV) return -20;
   if (M <= 0) return 0;
   const int grid = norm_grid(M);
   DISPATCH_NV(D, {
     if (dy_bf16 && !x_bf16)
-      rmsnorm_bwd_kernel<float, __nv_bfloat16, NV><<<(DPFS_COUNT(), grid), kNormThreads, 0, stream>>>(
+      rmsnorm_bwd_kernel<float, __nv_bfloat16, NV, CS><<<(DPFS_COUNT(), grid), kNormThreads, 0, stream>>>(
           (const __nv_bfloat16*)dy, (const float*)x, rstd, scale, dres, dx, (__nv_bfloat16*)dx_bf16, scratch, M, D);
     else if (dy_bf16 && x_bf16)
-      rmsnorm_bwd_kernel<__nv_bfloat16, __nv_bfloat16, NV><<<(DPFS_COUNT(), grid), kNormThreads, 0, stream>>>(
+      rmsnorm_bwd_kernel<__nv_bfloat16, __nv_bfloat16, NV, CS><<<(DPFS_COUNT(), grid), kNormThreads, 0, stream>>>(
           (const __nv_bfloat16*)dy, (const __nv_bfloat16*)x, rstd, scale, dres, dx, (__nv_bfloat16*)dx_bf16, scratch,
           M, D);
     else if (!dy_bf16 && !x_bf16)
-      rmsnorm_bwd_kernel<float, float, NV><<<(DPFS_COUNT(), grid), kNormThreads, 0, stream>>>(
+      rmsnorm_bwd_kernel<float, float, NV, CS><<<(DPFS_COUNT(), grid), kNormThreads, 0, stream>>>(
           (const float*)dy, (const float*)x, rstd, scale, dres, dx, (__nv_bfloat16*)dx_bf16, scratch, M, D);
     else
-      rmsnorm_bwd_kernel<__nv_bfloat16, float, NV><<<(DPFS_COUNT(), grid), kNormThreads, 0, stream>>>(
+      rmsnorm_bwd_kernel<__nv_bfloat16, float, NV, CS><<<(DPFS_COUNT(), grid), kNormThreads, 0, stream>>>(
           (const float*)dy, (const __nv_bfloat16*)x, rstd, scale, dres, dx, (__nv_bfloat16*)dx_bf16, scratch, M, D);
   });
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) return static_cast<int>(e);
-  reduce_partials_kernel<<<(DPFS_COUNT(), (D + 31) / 32), 256, 0, stream>>>(scratch, dscale, grid, D, dscale_accumulate);
+  if (CS)
+    reduce_partials_kernel<<<(DPFS_COUNT(), (2 * D + 31) / 32), kReduceGroups * 32, 0, stream>>>(scratch, dscale, grid, 2 * D,
+                                                                                 dscale_accumulate, dbias, D);
+  else
+    reduce_partials_kernel<<<(DPFS_COUNT(), (D + 31) / 32), kReduceGroups * 32, 0, stream>>>(scratch, dscale, grid, D,
+                                                                             dscale_accumulate);
   return static_cast<int>(cudaGetLastError());
+}
+
+extern "C" int dpfs_rmsnorm_bwd(const void* dy, int dy_bf16, const void* x, int x_bf16, const float* rstd,
+                                const float* scale, const float* dres, float* dx, void* dx_bf16, float* dscale,
+                                int dscale_accumulate, float* scratch, int M, int D, cudaStream_t stream) {
+  return rmsnorm_bwd_launch<false>(dy, dy_bf16, x, x_bf16, rstd, scale, dres, dx, dx_bf16, dscale, dscale_accumulate,
+                                   nullptr, scratch, M, D, stream);
+}
+
+// Same, plus dbias[c] = sum_rows dx[r][c] (overwritten): the residual-stream gradient this kernel produces is the
+// output gradient of the row-parallel linear in front of it, so that layer's bias gradient needs no pass of its own.
+// scratch: dpfs_norm_bwd_blocks(M) * 2 * D floats.
+extern "C" int dpfs_rmsnorm_bwd_bias(const void* dy, int dy_bf16, const void* x, int x_bf16, const float* rstd,
+                                     const float* scale, const float* dres, float* dx, void* dx_bf16, float* dscale,
+                                     int dscale_accumulate, float* dbias, float* scratch, int M, int D,
+                                     cudaStream_t stream) {
+  if (!dbias) return -21;
+  return rmsnorm_bwd_launch<true>(dy, dy_bf16, x, x_bf16, rstd, scale, dres, dx, dx_bf16, dscale, dscale_accumulate,
+                                  dbias, scratch, M, D, stream);
 }
 
 extern "C" int dpfs_layernorm_fwd(const void* x, int x_bf16, const float* gamma, const float* beta, void* y,
@@ -817,7 +879,7 @@ extern "C" int dpfs_layernorm_bwd(const void* dy, int dy_bf16, const void* x, in
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) return static_cast<int>(e);
   // partial rows are [dgamma(D) | dbeta(D)]: reduce as one 2D-wide vector into a strided pair of outputs
-  reduce_partials_kernel<<<(DPFS_COUNT(), (2 * D + 31) / 32), 256, 0, stream>>>(scratch, scratch + (long long)grid * 2 * D, grid,
+  reduce_partials_kernel<<<(DPFS_COUNT(), (2 * D + 31) / 32), kReduceGroups * 32, 0, stream>>>(scratch, scratch + (long long)grid * 2 * D, grid,
                                                                   2 * D, 0);
   e = cudaGetLastError();
   if (e != cudaSuccess) return static_cast<int>(e);
@@ -884,7 +946,7 @@ extern "C" int dpfs_colsum_bf16(const void* x, long long ld, float* out, int acc
   colsum_partial_kernel<<<(DPFS_COUNT(), grid), 128, 0, stream>>>((const __nv_bfloat16*)x, ld, scratch, M, N);
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) return static_cast<int>(e);
-  reduce_partials_kernel<<<(DPFS_COUNT(), (N + 31) / 32), 256, 0, stream>>>(scratch, out, strips, N, accumulate);
+  reduce_partials_kernel<<<(DPFS_COUNT(), (N + 31) / 32), kReduceGroups * 32, 0, stream>>>(scratch, out, strips, N, accumulate);
   return static_cast<int>(cudaGetLastError());
 }
 
@@ -901,7 +963,7 @@ extern "C" int dpfs_swiglu_bwd_bias(const void* dact, const void* gu, void* dgu,
                                                                     scratch, M, F);
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) return static_cast<int>(e);
-  reduce_partials_kernel<<<(DPFS_COUNT(), (2 * F + 31) / 32), 256, 0, stream>>>(scratch, bias_grad, strips, 2 * F,
+  reduce_partials_kernel<<<(DPFS_COUNT(), (2 * F + 31) / 32), kReduceGroups * 32, 0, stream>>>(scratch, bias_grad, strips, 2 * F,
                                                                                accumulate);
   return static_cast<int>(cudaGetLastError());
 }
@@ -917,7 +979,7 @@ extern "C" int dpfs_cast_colsum(const float* x, void* y, float* colsum, int accu
   cast_colsum_kernel<<<(DPFS_COUNT(), grid), tpb, 0, stream>>>(x, (__nv_bfloat16*)y, scratch, M, N);
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) return static_cast<int>(e);
-  reduce_partials_kernel<<<(DPFS_COUNT(), (N + 31) / 32), 256, 0, stream>>>(scratch, colsum, strips, N, accumulate);
+  reduce_partials_kernel<<<(DPFS_COUNT(), (N + 31) / 32), kReduceGroups * 32, 0, stream>>>(scratch, colsum, strips, N, accumulate);
   return static_cast<int>(cudaGetLastError());
 }
 
@@ -990,7 +1052,7 @@ extern "C" int dpfs_colsum_bf16_static(const void* x, long long ld, float* out, 
   colsum_partial_kernel<<<(DPFS_COUNT(), grid), 128, 0, stream>>>((const __nv_bfloat16*)x, ld, scratch, M, N);
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) return static_cast<int>(e);
-  reduce_partials_kernel<<<(DPFS_COUNT(), (N + 31) / 32), 256, 0, stream>>>(scratch, out, static_cast<int>(strips),
+  reduce_partials_kernel<<<(DPFS_COUNT(), (N + 31) / 32), kReduceGroups * 32, 0, stream>>>(scratch, out, static_cast<int>(strips),
                                                                              N, accumulate);
   return static_cast<int>(cudaGetLastError());
 }

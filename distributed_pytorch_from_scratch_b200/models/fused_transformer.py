@@ -228,8 +228,12 @@ class FusedLayerFn(torch.autograd.Function):
         x, pos, h1, rstd1, qkv, attn, lse, x2, h2, rstd2, gu, act = ctx.saved_tensors
         pack, m, rt = ctx.pack, ctx.meta, ctx.rt
         dx3 = dx3.contiguous()
-        dx3_b = fused.cast_to_bf16(dx3)
-        fused.colsum(dx3_b, out=pack.g_bd)   # (the fused cast+colsum kernel measured slower than the two passes here)
+        dx3_b = rt.take_stash(dx3)
+        if dx3_b is None:
+            # dx3 did not come from the fused RMSNorm backward above us (e.g. the module-path head): cast it and take
+            # the down_proj bias gradient with a pass of its own
+            dx3_b = fused.cast_to_bf16(dx3)
+            fused.colsum(dx3_b, out=pack.g_bd)
         # ---- FFN
         dact = gemm_nt(dx3_b, pack.wd, b_mn_major=True, out_dtype=BF16)            # [M, Fl]
         _wgrad(dx3_b, act, pack.g_wd)
@@ -238,19 +242,25 @@ class FusedLayerFn(torch.autograd.Function):
         dh2 = _colpar_dgrad(dgu, pack.wgu)                                            # [M, d]
         _wgrad(dgu, h2, pack.g_wgu)
         del dgu
+        # dx2 is the output gradient of wo's residual add: its column sums are the wo bias gradient (same pass)
         dx2, dx2_b, _ = fused.rmsnorm_bwd(dh2, x2, rstd2, pack.s2, dres=dx3, want_fp32=True, want_bf16=True,
-                                          dscale_out=pack.g_s2)
+                                          dscale_out=pack.g_s2, dbias_out=pack.g_bo)
         # ---- attention
         dattn = gemm_nt(dx2_b, pack.wo, b_mn_major=True, out_dtype=BF16)              # [M, Dl]
         _wgrad(dx2_b, attn, pack.g_wo)
-        fused.colsum(dx2_b, out=pack.g_bo)
         dqkv = attn_bwd(qkv, attn, dattn, lse, m.B, m.T, m.Hl, m.hd, m.scale)
         fused.rope_inplace(dqkv, pos, rt.cos_half, rt.sin_half, 2, m.Dl, m.Hl, m.hd, inverse=True)
         dh1 = _colpar_dgrad(dqkv, pack.wqkv)
         _wgrad(dqkv, h1, pack.g_wqkv)
         fused.colsum(dqkv, out=pack.g_bqkv)
-        dx, _, _ = fused.rmsnorm_bwd(dh1, x, rstd1, pack.s1, dres=dx2, want_fp32=True, want_bf16=False,
-                                     dscale_out=pack.g_s1)
+        if pack.prev is not None:
+            # dx is the output gradient of the layer below: hand it its bf16 copy and its down_proj bias gradient
+            dx, dx_b, _ = fused.rmsnorm_bwd(dh1, x, rstd1, pack.s1, dres=dx2, want_fp32=True, want_bf16=True,
+                                            dscale_out=pack.g_s1, dbias_out=pack.prev.g_bd)
+            rt.put_stash(dx, dx_b)
+        else:
+            dx, _, _ = fused.rmsnorm_bwd(dh1, x, rstd1, pack.s1, dres=dx2, want_fp32=True, want_bf16=False,
+                                         dscale_out=pack.g_s1)
         return (dx, None, None, None, None) + (None,) * len(pack.params)
 
 
@@ -321,7 +331,9 @@ class FusedHeadLossFn(torch.autograd.Function):
         dh = _colpar_dgrad(dlogits, rt.wlm)
         _wgrad(dlogits, h, rt.g_wlm)
         fused.colsum(dlogits, out=rt.g_blm)
-        dx, _, _ = fused.rmsnorm_bwd(dh, x, rstd, rt.sN, dres=None, want_fp32=True, dscale_out=rt.g_sN)
+        dx, dx_b, _ = fused.rmsnorm_bwd(dh, x, rstd, rt.sN, dres=None, want_fp32=True, want_bf16=True,
+                                        dscale_out=rt.g_sN, dbias_out=rt.packs[-1].g_bd)
+        rt.put_stash(dx, dx_b)
         return (dx, None, None, None) + (None,) * 3
 
 
@@ -340,6 +352,9 @@ class FusedRuntime:
         self.arena = ParamArena(model)
         A = self.arena
         self.packs: List[LayerPack] = [LayerPack(A, layer, d, self.Dl, self.Fl) for layer in model.layers]
+        for i, pack in enumerate(self.packs):
+            pack.prev = self.packs[i - 1] if i > 0 else None
+        self._stash = None
         head, emb = model.lm_head, model.embedding
         Vl = head.odim_partition
         self.wlm, self.g_wlm = A.view(A.shadow, head.weight, Vl, d), A.view(A.grads, head.weight, Vl, d)
@@ -354,11 +369,24 @@ class FusedRuntime:
     def valid(self) -> bool:
         return self.arena.valid() and self.n == pm.pgm.tp_size
 
+    # The fused RMSNorm backward of one block produces, in the same pass, the bf16 copy of the residual-stream gradient
+    # and the down_proj bias gradient that the block below needs.  They travel outside autograd (which only carries the
+    # fp32 gradient); the consumer checks that the gradient it received is the very tensor the stash was made for.
+    def put_stash(self, dx: torch.Tensor, dx_bf16: torch.Tensor) -> None:
+        self._stash = (dx, dx_bf16)
+
+    def take_stash(self, dx: torch.Tensor) -> Optional[torch.Tensor]:
+        st, self._stash = self._stash, None
+        if st is not None and st[0].data_ptr() == dx.data_ptr() and st[0].shape == dx.shape:
+            return st[1]
+        return None
+
     # ---------------------------------------------------------------------------------------------- forward
     def forward_hidden(self, input_ids: torch.Tensor, position_ids: torch.Tensor) -> torch.Tensor:
         assert input_ids.dim() == 2
         B, T = input_ids.shape
         self.arena.sync_shadow()
+        self._stash = None
         if torch.is_grad_enabled():
             self.arena.reattach_grads()
         meta = Meta(B, T, self.d, self.Hl, self.hd, self.Fl, self.n)

@@ -43,6 +43,8 @@ SIGS = {
     "dpfs_norm_bwd_blocks": (c_int,),
     "dpfs_rmsnorm_fwd": (c_p, c_int, c_p, c_p, c_int, c_p, c_int, c_int, c_f, c_p),
     "dpfs_rmsnorm_bwd": (c_p, c_int, c_p, c_int, c_p, c_p, c_p, c_p, c_p, c_p, c_int, c_p, c_int, c_int, c_p),
+    "dpfs_rmsnorm_bwd_bias": (c_p, c_int, c_p, c_int, c_p, c_p, c_p, c_p, c_p, c_p, c_int, c_p, c_p, c_int, c_int,
+                              c_p),
     "dpfs_layernorm_fwd": (c_p, c_int, c_p, c_p, c_p, c_int, c_p, c_p, c_int, c_int, c_f, c_p),
     "dpfs_layernorm_bwd": (c_p, c_int, c_p, c_int, c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_int, c_int, c_p),
     "dpfs_swiglu_fwd": (c_p, c_p, c_int, c_int, c_p),

@@ -65,8 +65,12 @@ def add_rmsnorm_fwd(x: torch.Tensor, y: torch.Tensor, bias: Optional[torch.Tenso
 
 def rmsnorm_bwd(dy: torch.Tensor, x: torch.Tensor, rstd: torch.Tensor, scale: torch.Tensor,
                 dres: Optional[torch.Tensor] = None, want_fp32: bool = True, want_bf16: bool = False,
-                dscale_out: Optional[torch.Tensor] = None, accumulate: bool = False):
-    """Returns (dx fp32 | None, dx bf16 | None, dscale fp32 [D]).  dx = dres + rmsnorm'(dy)."""
+                dscale_out: Optional[torch.Tensor] = None, accumulate: bool = False,
+                dbias_out: Optional[torch.Tensor] = None):
+    """Returns (dx fp32 | None, dx bf16 | None, dscale fp32 [D]).  dx = dres + rmsnorm'(dy).
+
+    dbias_out (fp32 [D], overwritten): column sums of dx, i.e. the bias gradient of the row-parallel linear whose
+    output gradient dx is (ref models/layers.py:51-54) -- produced by the same pass instead of a colsum of its own."""
     D = x.shape[-1]
     x2, dy2 = x.reshape(-1, D), dy.reshape(-1, D)
     assert x2.is_contiguous() and dy2.is_contiguous()
@@ -75,10 +79,18 @@ def rmsnorm_bwd(dy: torch.Tensor, x: torch.Tensor, rstd: torch.Tensor, scale: to
     dxb = torch.empty((M, D), dtype=BF16, device=x.device) if want_bf16 else None
     dscale = dscale_out if dscale_out is not None else torch.empty(D, dtype=F32, device=x.device)
     lib = _lib.lib()
-    scratch = _scratch(x.device, "norm", lib.dpfs_norm_bwd_blocks(M) * D)
+    scratch = _scratch(x.device, "norm", lib.dpfs_norm_bwd_blocks(M) * D * (2 if dbias_out is not None else 1))
     if dres is not None:
         dres = dres.reshape(-1, D)
         assert dres.dtype == F32 and dres.is_contiguous()
+    if dbias_out is not None:
+        assert dbias_out.dtype == F32 and dbias_out.numel() == D and dbias_out.is_contiguous()
+        rc = lib.dpfs_rmsnorm_bwd_bias(dy2.data_ptr(), _is_bf16(dy2), x2.data_ptr(), _is_bf16(x2), rstd.data_ptr(),
+                                       scale.data_ptr(), _lib.ptr(dres), _lib.ptr(dx), _lib.ptr(dxb),
+                                       dscale.data_ptr(), int(accumulate), dbias_out.data_ptr(), scratch.data_ptr(),
+                                       M, D, _lib.stream())
+        _lib.check(rc, "dpfs_rmsnorm_bwd_bias")
+        return dx, dxb, dscale
     rc = lib.dpfs_rmsnorm_bwd(dy2.data_ptr(), _is_bf16(dy2), x2.data_ptr(), _is_bf16(x2), rstd.data_ptr(),
                               scale.data_ptr(), _lib.ptr(dres), _lib.ptr(dx), _lib.ptr(dxb), dscale.data_ptr(),
                               int(accumulate), scratch.data_ptr(), M, D, _lib.stream())

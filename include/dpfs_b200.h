@@ -109,6 +109,12 @@ int dpfs_add_rmsnorm_fwd(const float* x, const void* y_bf16, const float* bias /
 int dpfs_rmsnorm_bwd(const void* dy, int dy_bf16, const void* x, int x_bf16, const float* rstd, const float* scale,
                      const float* dres /*nullable*/, float* dx, void* dx_bf16, float* dscale, int dscale_accumulate,
                      float* scratch, int M, int D, cudaStream_t stream);
+/* Same, plus dbias[D] = column sums of the produced dx (overwritten): dx is the output gradient of the row-parallel
+ * linear in front of the norm (wo / down_proj, ref models/layers.py:51-54), so its bias gradient comes out of this
+ * pass.  scratch: dpfs_norm_bwd_blocks(M) * 2 * D floats. */
+int dpfs_rmsnorm_bwd_bias(const void* dy, int dy_bf16, const void* x, int x_bf16, const float* rstd,
+                          const float* scale, const float* dres /*nullable*/, float* dx, void* dx_bf16, float* dscale,
+                          int dscale_accumulate, float* dbias, float* scratch, int M, int D, cudaStream_t stream);
 int dpfs_layernorm_fwd(const void* x, int x_bf16, const float* gamma, const float* beta /*nullable*/, void* y,
                        int y_bf16, float* mean, float* rstd, int M, int D, float eps, cudaStream_t stream);
 /* scratch: (dpfs_norm_bwd_blocks(M) + 1) * 2 * D floats. */

@@ -84,6 +84,12 @@ def test_rmsnorm_fwd_bwd(D):
     assert torch.allclose(dscale, sr.grad, atol=2e-2, rtol=2e-3)
     y32, _ = fused.rmsnorm_fwd(x, scale, 1e-5, out_dtype=torch.float32)
     assert torch.allclose(y32, yr, atol=1e-5)
+    # same pass + column sums of dx (bias gradient of the linear in front of the norm); other outputs unchanged
+    dbias = torch.full((D,), 7.0, device=DEV)
+    dx2, dxb2, dscale2 = fused.rmsnorm_bwd(_bf(dy), x, rstd, scale, dres=dres, want_fp32=True, want_bf16=True,
+                                           dbias_out=dbias)
+    assert torch.equal(dx2, dx) and torch.equal(dxb2, dxb) and torch.equal(dscale2, dscale)
+    assert torch.allclose(dbias, (xr.grad + dres).sum(0), atol=2e-3, rtol=1e-4)
 
 
 def test_layernorm_fwd_bwd():
