@@ -28,13 +28,24 @@ constexpr int BM = 128;   // rows per CTA (256 per cluster)
 constexpr int BNH = 128;  // B rows staged per CTA (half of the 256-wide tile)
 constexpr int BN = 256;
 constexpr int BK = 64;
-constexpr int kThreads = 192;
-constexpr int kStages = 6;
 constexpr int kABytes = BM * BK * 2;
 constexpr int kBBytes = BNH * BK * 2;
 constexpr int kStageBytes = kABytes + kBBytes;
-constexpr int kOutStageBytes = 4 * 2 * 4096;  // 4 epilogue warps x 2 buffers x (32 rows x 128 B) staging for TMA stores
-constexpr int kSmem = kStages * kStageBytes + kOutStageBytes + 256 + 1024;
+// TMA-store staging: kOutBufs slabs of 32 rows x 128 B per epilogue warp (a ring of 4 measured no faster).
+constexpr int kOutBufs = 2;
+// Two shapes of the same kernel.  EW = 4: four epilogue warps, six operand stages -- for long K, where the epilogue
+// hides behind the next tile's main loop.  EW = 8: two warps per TMEM lane quarter (each takes half of the tile's
+// columns), five stages -- for short K (<= 1024), where a 256x256 tile's main loop (2.2 us at K = 512) is shorter
+// than one warp set's epilogue and the epilogue paces the kernel.  (10 warps put 3 on one SM sub-partition, so the
+// compiler caps that shape at 168 registers: 16384 / 3 per warp.)
+template <int EW>
+struct Cfg {
+  static constexpr int kStages = EW == 8 ? 5 : 6;
+  static constexpr int kThreads = 64 + EW * 32;
+  static constexpr int kOutStageBytes = EW * kOutBufs * 4096;
+  static constexpr int kSmem = kStages * kStageBytes + kOutStageBytes + 256 + 1024;
+  static_assert(kSmem <= 232448, "exceeds the 227 KB shared-memory limit");
+};
 constexpr uint32_t kPeerMask = 0xFEFFFFFFu;  // clears the CTA-rank bit of a shared-window address -> leader CTA's copy
 
 struct Args {
@@ -123,10 +134,12 @@ __device__ __forceinline__ void store32<__nv_bfloat16>(__nv_bfloat16* dst, const
   }
 }
 
-template <bool A_MN, bool B_MN, typename OutT>
-__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
+template <bool A_MN, bool B_MN, typename OutT, int EW>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(Cfg<EW>::kThreads, 1)
 gemm2sm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                const __grid_constant__ CUtensorMap tmOut, const Args args) {
+  constexpr int kStages = Cfg<EW>::kStages;
+  constexpr int kOutStageBytes = Cfg<EW>::kOutStageBytes;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* sA = smem;
@@ -159,7 +172,7 @@ gemm2sm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     }
     for (int i = 0; i < 2; ++i) {
       mbar_init(&tmem_full[i], 1);
-      mbar_init(&tmem_empty[i], 8);  // 4 epilogue warps x 2 CTAs
+      mbar_init(&tmem_empty[i], 2 * EW);  // EW epilogue warps x 2 CTAs
     }
     fence_mbar_init();
   }
@@ -254,26 +267,74 @@ gemm2sm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     // output ROW, so direct global stores would touch 32 different rows per instruction (half-filled 32 B sectors);
     // staging 32 rows x 128 B per warp and letting the TMA unit write them gives full-line, coalesced writes, clips the
     // M / N edges for free, and takes the store instructions off the epilogue's critical path.
-    const int q = warp & 3;
-    uint8_t* stage = sOut + (warp - 2) * 2 * 4096;
+    const int q = warp & 3;   // the hardware ties a warp to TMEM lanes [32 * (warp % 4), +32)
+    // EW = 8: warps 2-5 take columns [0, 128) of the tile, warps 6-9 take [128, 256)
+    const int c_begin = (EW == 8) ? ((warp - 2) >> 2) * (BN / 64) : 0;
+    const int c_end = (EW == 8) ? c_begin + BN / 64 : BN / 32;
+    uint8_t* stage = sOut + (warp - 2) * kOutBufs * 4096;
     int sbuf = 0;
     int as = 0;
     uint32_t aphase = 0;
     constexpr bool kBf16 = sizeof(OutT) == 2;
+    // The residual is read by row (every thread its own 128-byte segments), which leaves few bytes in flight per SM:
+    // its lines are pulled into L2 one whole tile ahead (prefetch, no registers), and the register loads run one
+    // 32-column chunk ahead of the TMEM read they are added to.
+    auto residual_row = [&](int w) -> const float* {
+      if (!args.residual || w >= num_work) return nullptr;
+      const int t = w % tiles_mn;
+      const int row = (t / tiles_n) * (2 * BM) + cta * BM + q * 32 + lane;
+      return row < args.M ? args.residual + static_cast<long long>(row) * args.ldr + (t % tiles_n) * BN : nullptr;
+    };
+    auto prefetch_row = [&](int w) {
+      const float* p = residual_row(w);
+      if (!p) return;
+      const int n0 = (w % tiles_mn % tiles_n) * BN;
+#pragma unroll
+      for (int j = 0; j < BN / 32; ++j)
+        if (n0 + j * 32 < args.N) asm volatile("prefetch.global.L2 [%0];" ::"l"(p + j * 32));
+    };
+    prefetch_row(cluster_id);
     for (int w = cluster_id; w < num_work; w += n_clusters) {
       const int split = w / tiles_mn;
       const int t = w - split * tiles_mn;
       const int m0 = (t / tiles_n) * (2 * BM) + cta * BM;
       const int n0 = (t % tiles_n) * BN;
       const int row = m0 + q * 32 + lane;
+      const float* rrow = (args.residual && row < args.M)
+                              ? args.residual + static_cast<long long>(row) * args.ldr + n0
+                              : nullptr;
+      float4 rnext[8], bnext[8];
+      auto load_res = [&](int c) {
+        const int valid = args.N - (n0 + c * 32);
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+          rnext[j] = (rrow && c < c_end && j * 4 + 4 <= valid)
+                         ? *reinterpret_cast<const float4*>(rrow + c * 32 + 4 * j)
+                         : make_float4(0.f, 0.f, 0.f, 0.f);
+      };
+      // the bias segment of a chunk is a first touch (an L2 round trip) for every tile: fetch it one chunk ahead too
+      auto load_bias = [&](int c) {
+        const int valid = args.N - (n0 + c * 32);
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+          bnext[j] = (args.bias && c < c_end && j * 4 + 4 <= valid)
+                         ? __ldg(reinterpret_cast<const float4*>(args.bias + n0 + c * 32) + j)
+                         : make_float4(0.f, 0.f, 0.f, 0.f);
+      };
+      load_res(c_begin);
+      load_bias(c_begin);
+      prefetch_row(w + n_clusters);
       mbar_wait(&tmem_full[as], aphase);
       tc_fence_after();
       const uint32_t t_addr = tmem_base + as * BN + (static_cast<uint32_t>(q * 32) << 16);
-      const float* rrow = args.residual ? args.residual + static_cast<long long>(row) * args.ldr + n0 : nullptr;
 #pragma unroll 1
-      for (int c = 0; c < BN / 32; ++c) {
+      for (int c = c_begin; c < c_end; ++c) {
         uint32_t r[32];
         tmem_ld32(t_addr + c * 32, r);
+        float4 bcur[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) bcur[j] = bnext[j];
+        if (args.bias) load_bias(c + 1);
         tmem_ld_wait();
         const int ncols_valid = args.N - (n0 + c * 32);
         float v[32];
@@ -281,31 +342,25 @@ gemm2sm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
         if (ncols_valid > 0) {
           if (args.bias) {
-            const float4* b4 = reinterpret_cast<const float4*>(args.bias + n0 + c * 32);
 #pragma unroll
-            for (int j = 0; j < 8; ++j) {
-              if (j * 4 + 4 <= ncols_valid) {
-                const float4 bv = __ldg(b4 + j);
-                v[4 * j] += bv.x;
-                v[4 * j + 1] += bv.y;
-                v[4 * j + 2] += bv.z;
-                v[4 * j + 3] += bv.w;
-              }
+            for (int j = 0; j < 8; ++j) {   // (zeros where the column group is out of range)
+              v[4 * j] += bcur[j].x;
+              v[4 * j + 1] += bcur[j].y;
+              v[4 * j + 2] += bcur[j].z;
+              v[4 * j + 3] += bcur[j].w;
             }
           }
-          if (rrow && row < args.M) {
+          if (rrow) {
 #pragma unroll
-            for (int j = 0; j < 8; ++j) {
-              if (j * 4 + 4 <= ncols_valid) {
-                const float4 rv = *reinterpret_cast<const float4*>(rrow + c * 32 + 4 * j);
-                v[4 * j] += rv.x;
-                v[4 * j + 1] += rv.y;
-                v[4 * j + 2] += rv.z;
-                v[4 * j + 3] += rv.w;
-              }
+            for (int j = 0; j < 8; ++j) {   // (zeros where the column group is out of range)
+              v[4 * j] += rnext[j].x;
+              v[4 * j + 1] += rnext[j].y;
+              v[4 * j + 2] += rnext[j].z;
+              v[4 * j + 3] += rnext[j].w;
             }
           }
         }
+        if (rrow) load_res(c + 1);   // (registers are tight: the residual runs the rest of this chunk ahead, not a full one)
         uint8_t* slab = stage + sbuf * 4096 + lane * 128;
         if constexpr (kBf16) {
           // two 32-column chunks share one 64-column (128 B) slab row
@@ -332,10 +387,10 @@ gemm2sm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             const int col0 = n0 + (kBf16 ? (c - 1) : c) * 32;
             if (col0 < args.N) tma_store_3d(&tmOut, stage + sbuf * 4096, col0, m0 + q * 32, split);
             tma_store_commit();
-            tma_store_wait_read<1>();  // the OTHER buffer's previous store has finished reading its slab
+            tma_store_wait_read<kOutBufs - 1>();  // the slab written next has been read out by its previous store
           }
           __syncwarp();
-          sbuf ^= 1;
+          sbuf = (sbuf + 1) % kOutBufs;
         }
       }
       tc_fence_before();
@@ -395,17 +450,36 @@ static int launch(const CUtensorMap& tmA, const CUtensorMap& tmB, const Args& ar
                                  args.split_stride);
     if (rc) return rc;
   }
-  auto kfn = gemm2sm_kernel<A_MN, B_MN, OutT>;
-  static bool configured = false;
-  if (!configured) {
-    cudaError_t e = cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem);
-    if (e != cudaSuccess) return static_cast<int>(e);
-    configured = true;
-  }
   const int work = ((args.M + 2 * BM - 1) / (2 * BM)) * ((args.N + BN - 1) / BN) * args.splits;
   int clusters = num_sms() / 2;
   if (work < clusters) clusters = work;
-  kfn<<<(DPFS_COUNT(), 2 * clusters), kThreads, kSmem, stream>>>(tmA, tmB, tmOut, args);
+  // short reductions per tile are epilogue-paced: use the 8-epilogue-warp shape (DPFS_GEMM_EPI8=0/1 forces a shape)
+  static int force = -2;
+  if (force == -2) {
+    const char* e = getenv("DPFS_GEMM_EPI8");
+    force = e ? atoi(e) : -1;
+  }
+  const int k_per_tile = args.kb_per_split * BK < args.K ? args.kb_per_split * BK : args.K;
+  const bool epi8 = force >= 0 ? force != 0 : k_per_tile <= 1024;
+  if (epi8) {
+    auto kfn = gemm2sm_kernel<A_MN, B_MN, OutT, 8>;
+    static bool configured = false;
+    if (!configured) {
+      cudaError_t e = cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg<8>::kSmem);
+      if (e != cudaSuccess) return static_cast<int>(e);
+      configured = true;
+    }
+    kfn<<<(DPFS_COUNT(), 2 * clusters), Cfg<8>::kThreads, Cfg<8>::kSmem, stream>>>(tmA, tmB, tmOut, args);
+  } else {
+    auto kfn = gemm2sm_kernel<A_MN, B_MN, OutT, 4>;
+    static bool configured = false;
+    if (!configured) {
+      cudaError_t e = cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg<4>::kSmem);
+      if (e != cudaSuccess) return static_cast<int>(e);
+      configured = true;
+    }
+    kfn<<<(DPFS_COUNT(), 2 * clusters), Cfg<4>::kThreads, Cfg<4>::kSmem, stream>>>(tmA, tmB, tmOut, args);
+  }
   return static_cast<int>(cudaGetLastError());
 }
 
