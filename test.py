@@ -17,6 +17,7 @@ import tqdm
 import process_manager as pm
 from constants import BOS_TOKEN, EOS_TOKEN, IGNORE_INDEX, ModelArgumments
 from dataset import get_dataloader
+from distributed_pytorch_from_scratch_b200.models.generation import greedy_generate
 from distributed_pytorch_from_scratch_b200.utils.checkpoint import CKPT_RE, list_checkpoints, load_checkpoint
 from distributed_pytorch_from_scratch_b200.utils.logging import make_summary_writer
 from models.model import Transformer
@@ -63,6 +64,9 @@ def get_test_args(argv=None):
     group = parser.add_argument_group("decode")
     group.add_argument("--max_decode_len", type=int, default=128)
     group.add_argument("--skip_decode", action='store_true')
+    group.add_argument("--no_kv_cache", action='store_true',
+                       help="decode like the reference: re-run the whole prefix for every new token "
+                            "(default: incremental decoding with a per-layer K/V cache, same tokens)")
 
     group = parser.add_argument_group("other")
     group.add_argument("--random_seed", type=int, default=0)
@@ -164,7 +168,10 @@ def test(rank, args):
             t = t.strip()
             tokens = torch.tensor(tokenizer.encode(t).ids, dtype=torch.long, device=device).view(1, -1)
             tokens = F.pad(tokens, (1, 0), mode="constant", value=bos_id)
-            tokens, hit_eos = greedy_decode(model, tokens, eos_id, args.max_decode_len, dtype, device)
+            if args.no_kv_cache:
+                tokens, hit_eos = greedy_decode(model, tokens, eos_id, args.max_decode_len, dtype, device)
+            else:
+                tokens, hit_eos = greedy_generate(model, tokens, eos_id, args.max_decode_len, dtype=dtype)
             if not hit_eos:
                 print(f"[TP Rank {pm.pgm.tp_rank}]: Maximum length reached. Stop decoding.")
             trans = tokenizer.decode(tokens[0, 1:].tolist()).strip()      # drop BOS

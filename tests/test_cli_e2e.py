@@ -43,3 +43,11 @@ def test_train_then_test_cli(tmp_path):
     assert "Nice to meet you, it's ->" in rep
     rep1 = open(os.path.join(save, "val", "tprank-1_val.txt")).read()
     assert rep.split("Input texts")[1] == rep1.split("Input texts")[1]     # every rank decodes the same text
+    # the default decode keeps a K/V cache; the reference-style full re-forward must produce the same text
+    kv_text = rep.split("Input texts")[1]
+    os.remove(os.path.join(save, "val", "tprank-0_val.txt"))
+    _run(["test.py", "--tp_size", "2", "--ckpt_dir", save, "-d", data, "-t", "tokenizer/tokenizer.json",
+          "--max_decode_len", "12", "--fp32", "--no_kv_cache", "--backend", "gloo", "--master_port",
+          str(free_port())] + MODEL)
+    rep = open(os.path.join(save, "val", "tprank-0_val.txt")).read()
+    assert rep.split("Input texts")[1] == kv_text
