@@ -70,6 +70,15 @@ def test_checkpoint_format_rotation_reshard(tmp_path):
     assert all(torch.equal(merged[k], full[k]) for k in full)
     out = C.reshard_checkpoint(d, str(tmp_path / "tp2"), 30, 1, 2)
     assert len(out) == 2 and os.path.basename(out[1]) == "tprank-1_iter-30_loss-2.3457.pth"
+    # the CLI wrapper picks the newest iteration on its own and round-trips back to TP=1
+    import subprocess
+    import sys
+    r = subprocess.run([sys.executable, os.path.join(REPO, "tools", "reshard_checkpoint.py"), "--src",
+                        str(tmp_path / "tp2"), "--dst", str(tmp_path / "tp1"), "--src_tp", "2", "--dst_tp", "1"],
+                       capture_output=True, text=True, timeout=120)
+    assert r.returncode == 0, r.stderr
+    back = torch.load(r.stdout.strip().splitlines()[-1], map_location="cpu", weights_only=True)
+    assert all(torch.equal(back[k], full[k]) for k in full)
 
 
 def test_checkpoint_interchange_with_reference(tmp_path):
