@@ -156,6 +156,72 @@ __device__ __forceinline__ void reduce_region_p2p(const PeerPtrs& peers, long lo
   }
 }
 
+// Reduce-scatter flavour: sum the NR ranks' copies of rows [0, rows) x (cpr x 16 B) of a bf16 region (row pitch
+// ld_bytes, byte offset off0 inside every rank's buffer) in fp32, rank order, and write the bf16 result ONLY to this
+// rank's private output `dst` (row pitch dst_ld_bytes).
+template <int NR, int INFLIGHT = 8>
+__device__ __forceinline__ void reduce_region_to_local_p2p(const PeerPtrs& peers, long long off0, long long ld_bytes,
+                                                           uint8_t* dst, long long dst_ld_bytes, int rows, int cpr,
+                                                           int tid, int nthreads) {
+  constexpr int KC = INFLIGHT / NR > 0 ? INFLIGHT / NR : 1;
+  const int total = rows * cpr;
+  for (int base = tid; base < total; base += nthreads * KC) {
+    uint4 v[KC][NR];
+    long long doff[KC];
+#pragma unroll
+    for (int k = 0; k < KC; ++k) {
+      const int idx = base + k * nthreads;
+      const int r_ = idx / cpr, cc = idx - r_ * cpr;
+      doff[k] = r_ * dst_ld_bytes + cc * 16;
+      if (idx < total) {
+        const long long off = off0 + r_ * ld_bytes + cc * 16;
+#pragma unroll
+        for (int r = 0; r < NR; ++r) v[k][r] = ld_peer_16B(peers.p[r] + off);
+      }
+    }
+#pragma unroll
+    for (int k = 0; k < KC; ++k) {
+      if (base + k * nthreads < total) {
+        float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+        for (int r = 0; r < NR; ++r) {
+          const uint32_t w[4] = {v[k][r].x, v[k][r].y, v[k][r].z, v[k][r].w};
+#pragma unroll
+          for (int i = 0; i < 4; ++i) {
+            const float2 f = unpack_bf16(w[i]);
+            acc[2 * i] += f.x;
+            acc[2 * i + 1] += f.y;
+          }
+        }
+        *reinterpret_cast<uint4*>(dst + doff[k]) =
+            make_uint4(pack_bf16(acc[0], acc[1]), pack_bf16(acc[2], acc[3]), pack_bf16(acc[4], acc[5]),
+                       pack_bf16(acc[6], acc[7]));
+      }
+    }
+  }
+}
+// Same through the switch: one multimem.ld_reduce returns the fp32-accumulated sum of all ranks' copies.
+template <int INFLIGHT = 4>
+__device__ __forceinline__ void reduce_region_to_local_nvls(const uint8_t* mc_base, long long off0, long long ld_bytes,
+                                                            uint8_t* dst, long long dst_ld_bytes, int rows, int cpr,
+                                                            int tid, int nthreads) {
+  const int total = rows * cpr;
+  for (int base = tid; base < total; base += nthreads * INFLIGHT) {
+    uint4 v[INFLIGHT];
+    long long doff[INFLIGHT];
+#pragma unroll
+    for (int k = 0; k < INFLIGHT; ++k) {
+      const int idx = base + k * nthreads;
+      const int r_ = idx / cpr, cc = idx - r_ * cpr;
+      doff[k] = r_ * dst_ld_bytes + cc * 16;
+      if (idx < total) v[k] = multimem_ld_reduce_bf16x8(mc_base + off0 + r_ * ld_bytes + cc * 16);
+    }
+#pragma unroll
+    for (int k = 0; k < INFLIGHT; ++k)
+      if (base + k * nthreads < total) *reinterpret_cast<uint4*>(dst + doff[k]) = v[k];
+  }
+}
+
 // fp32 variant (4 floats per 16-byte unit)
 template <int NR>
 __device__ __forceinline__ void reduce_region_p2p_f32(const PeerPtrs& peers, long long off0, long long units, int tid,

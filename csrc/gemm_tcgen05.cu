@@ -41,7 +41,32 @@ struct GemmArgs {
   PeerPtrs peers;    // every rank's `out` (P2P reduce path)
   int debug;         // bring-up only: bit0 skip tile signals, bit1 skip tile waits, bit2 skip the reduce traffic
   CommCtx comm;
+  // fused reduce-scatter (FUSE_AR kernels with rs_out != nullptr): rank r keeps rows [r * rs_rows, (r + 1) * rs_rows)
+  // of the sum in its private rs_out (bf16 [rs_rows][N]) instead of every rank receiving everything
+  __nv_bfloat16* rs_out;
+  int rs_rows;
 };
+
+// ---- tile order / ownership of the fused reduce-scatter -------------------------------------------------------------
+// A row-block (BM rows) has a *primary* owner: the rank whose row range holds the block's first row.  Blocks are
+// computed in rounds -- the j-th block of owner 0, of owner 1, ... -- by every rank in the same order, so every
+// owner's comm warps get finished tiles at an even rate from the start (with the natural order owner 0 would be served
+// first and owner n-1 would reduce its whole share after the GEMM).  A block that straddles two row ranges is flagged
+// to both owners.
+__device__ __forceinline__ int rs_first_blk(int o, int rs_rows) { return (o * rs_rows + BM - 1) / BM; }
+__device__ __forceinline__ int rs_block_of(int wb, int n, int rs_rows) {  // wb-th block in compute order -> m_blk
+  int cmin = 0x7fffffff;
+  for (int o = 0; o < n; ++o) cmin = min(cmin, rs_first_blk(o + 1, rs_rows) - rs_first_blk(o, rs_rows));
+  if (wb < cmin * n) return rs_first_blk(wb % n, rs_rows) + wb / n;
+  int idx = wb - cmin * n;  // the owners that have one more block than the others, in rank order
+  for (int o = 0; o < n; ++o) {
+    if (rs_first_blk(o + 1, rs_rows) - rs_first_blk(o, rs_rows) > cmin) {
+      if (idx == 0) return rs_first_blk(o, rs_rows) + cmin;
+      --idx;
+    }
+  }
+  return 0;  // unreachable
+}
 
 template <int BN>
 struct GemmSmem {
@@ -110,6 +135,13 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   const int tiles_mn = tiles_m * tiles_n;
   const int num_work = tiles_mn * args.splits;
   const int kb_total = (args.K + BK - 1) / BK;
+  // work index -> tile id: identity, except for the fused reduce-scatter (see rs_block_of)
+  auto tile_of = [&](int wt) -> int {
+    if constexpr (FUSE_AR) {
+      if (args.rs_out) return rs_block_of(wt / tiles_n, args.comm.n, args.rs_rows) * tiles_n + wt % tiles_n;
+    }
+    return wt;
+  };
 
   if (threadIdx.x == 0) {
     prefetch_tmap(&tmA);
@@ -140,7 +172,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       uint32_t phase = 0;
       for (int w = blockIdx.x; w < num_work; w += gridDim.x) {
         const int split = w / tiles_mn;
-        const int t = w - split * tiles_mn;
+        const int t = tile_of(w - split * tiles_mn);
         const int m0 = (t / tiles_n) * BM;
         const int n0 = (t % tiles_n) * BN;
         const int kb0 = split * args.kb_per_split;
@@ -223,7 +255,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     OutT* out = reinterpret_cast<OutT*>(args.out);
     for (int w = blockIdx.x; w < num_work; w += gridDim.x) {
       const int split = w / tiles_mn;
-      const int t = w - split * tiles_mn;
+      const int t = tile_of(w - split * tiles_mn);
       const int m0 = (t / tiles_n) * BM;
       const int n0 = (t % tiles_n) * BN;
       const int row = m0 + q * 32 + lane;
@@ -282,9 +314,16 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         asm volatile("bar.sync 1, 128;" ::: "memory");
         if (threadIdx.x == 64 && !(args.debug & 1)) {
           const int m_blk = t / tiles_n;
-          const int owner = m_blk % args.comm.n;
           __threadfence_system();
-          put_signal(args.comm.flags[owner] + (kMaxBlocks + t) * kMaxRanks + args.comm.rank);
+          if (args.rs_out) {
+            const int o_lo = m0 / args.rs_rows;
+            const int o_hi = (min(m0 + BM, args.M) - 1) / args.rs_rows;
+            put_signal(args.comm.flags[o_lo] + (kMaxBlocks + t) * kMaxRanks + args.comm.rank);
+            if (o_hi != o_lo) put_signal(args.comm.flags[o_hi] + (kMaxBlocks + t) * kMaxRanks + args.comm.rank);
+          } else {
+            const int owner = m_blk % args.comm.n;
+            put_signal(args.comm.flags[owner] + (kMaxBlocks + t) * kMaxRanks + args.comm.rank);
+          }
         }
       }
     }
@@ -296,6 +335,42 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       // every rank's buffer — while warps 0-5 of this CTA are still computing other tiles.
       const int ct = threadIdx.x - kGemmThreads;
       const int n = args.comm.n, rank = args.comm.rank;
+      if (args.rs_out) {
+        // ---- reduce-scatter: the blocks that intersect this rank's rows, primary blocks in compute order first, the
+        // leading straddler (primary owner rank - 1, computed in that owner's last round) last
+        const int rpr = args.rs_rows;
+        const int row_lo = rank * rpr, row_hi = row_lo + rpr;
+        const int b_first = rs_first_blk(rank, rpr);          // first primary block
+        const int b_lo = row_lo / BM, b_hi = (row_hi - 1) / BM;
+        const int n_primary = b_hi - b_first + 1;
+        const int n_blk_owned = b_hi - b_lo + 1;               // n_primary (+ 1 with a leading straddler)
+        uint8_t* dst_base = reinterpret_cast<uint8_t*>(args.rs_out);
+        for (int k = blockIdx.x; k < n_blk_owned * tiles_n; k += gridDim.x) {
+          const int i = k / tiles_n, n_blk = k % tiles_n;
+          const int m_blk = i < n_primary ? b_first + i : b_lo;
+          const int t = m_blk * tiles_n + n_blk;
+          if (ct < n && !(args.debug & 2)) wait_signal(args.comm.flags[rank] + (kMaxBlocks + t) * kMaxRanks + ct);
+          asm volatile("bar.sync 2, 256;" ::: "memory");
+          if (args.debug & 4) continue;
+          const int m0 = m_blk * BM, n0 = n_blk * BN;
+          const int r0 = max(m0, row_lo), r1 = min(min(m0 + BM, row_hi), args.M);
+          const int cpr = min(BN, args.N - n0) / 8;  // 16-byte chunks per row
+          const long long off0 = (static_cast<long long>(r0) * args.ldo + n0) * 2;
+          const long long ldb = args.ldo * 2;
+          uint8_t* dst = dst_base + (static_cast<long long>(r0 - row_lo) * args.N + n0) * 2;
+          const long long dst_ld = static_cast<long long>(args.N) * 2;
+          if (args.mc_out) {
+            // args.mc_out is the multicast alias of this rank's `out`: offsets are relative to the buffer start
+            reduce_region_to_local_nvls<4>(args.mc_out, off0, ldb, dst, dst_ld, r1 - r0, cpr, ct, kCommThreads);
+          } else if (n == 2) {
+            reduce_region_to_local_p2p<2, 8>(args.peers, off0, ldb, dst, dst_ld, r1 - r0, cpr, ct, kCommThreads);
+          } else if (n == 4) {
+            reduce_region_to_local_p2p<4, 8>(args.peers, off0, ldb, dst, dst_ld, r1 - r0, cpr, ct, kCommThreads);
+          } else {
+            reduce_region_to_local_p2p<8, 8>(args.peers, off0, ldb, dst, dst_ld, r1 - r0, cpr, ct, kCommThreads);
+          }
+        }
+      } else {
       const int owned_rows = (tiles_m - rank + n - 1) / n;  // row-blocks m_blk = rank, rank + n, ...
       const int n_owned = owned_rows * tiles_n;
       for (int k = blockIdx.x; k < n_owned; k += gridDim.x) {
@@ -319,6 +394,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             reduce_region_p2p<8, 8>(args.peers, off0, ldb, rows, cpr, ct, kCommThreads);
           }
         }
+      }
       }
     }
   }
@@ -489,6 +565,8 @@ extern "C" int dpfs_gemm_bf16(const void* A, long long lda, int a_mn_major, cons
 
   GemmArgs args;
   args.mc_out = nullptr;
+  args.rs_out = nullptr;
+  args.rs_rows = 0;
   args.debug = 0;
   for (int i = 0; i < kMaxRanks; ++i) args.peers.p[i] = nullptr;
   args.comm.rank = 0;
@@ -543,14 +621,14 @@ extern "C" unsigned long long dpfs_launch_count(void) { return dpfs::g_launches;
 
 // Fused GEMM -> all-reduce: out (bf16 [M][N], row stride N) must be this rank's symmetric buffer and mc_out the
 // multicast alias of the same offset; on return every rank's `out` holds sum_r A_r B_r^T.
-extern "C" int dpfs_gemm_allreduce_bf16(const void* A, long long lda, const void* B, long long ldb, int b_mn_major,
-                                        void* out, void* mc_out, const unsigned long long* data_ptrs,
-                                        long long out_offset, int M, int N, int K,
-                                        const unsigned long long* flag_ptrs, int rank, int n, int bn,
-                                        cudaStream_t stream) {
+static int gemm_fused_collective(const void* A, long long lda, const void* B, long long ldb, int b_mn_major,
+                                 void* out, void* mc_out, const unsigned long long* data_ptrs, long long out_offset,
+                                 void* rs_out, int M, int N, int K, const unsigned long long* flag_ptrs, int rank,
+                                 int n, int bn, cudaStream_t stream) {
   if (M <= 0 || N <= 0 || K <= 0) return 0;
   if (n < 2 || n > kMaxRanks) return -50;
   if (n != 2 && n != 4 && n != 8) return -50;  // the in-kernel reduce is templated on the rank count
+  if (rs_out && (M % n != 0 || M / n < BM)) return -53;  // a row-block may straddle at most two owners
   if ((N % 8) != 0 || (lda % 8) != 0 || (ldb % 8) != 0) return -10;
   if (bn != 256) bn = 128;
   CUtensorMap tmA, tmB;
@@ -574,6 +652,8 @@ extern "C" int dpfs_gemm_allreduce_bf16(const void* A, long long lda, const void
   args.residual = nullptr;
   args.ldr = 0;
   args.mc_out = static_cast<uint8_t*>(mc_out);
+  args.rs_out = static_cast<__nv_bfloat16*>(rs_out);
+  args.rs_rows = rs_out ? M / n : 0;
   {
     const char* e = getenv("DPFS_FUSE_DEBUG");
     args.debug = e ? atoi(e) : 0;
@@ -588,4 +668,29 @@ extern "C" int dpfs_gemm_allreduce_bf16(const void* A, long long lda, const void
                       : launch_gemm_ar<256, false>(tmA, tmB, args, stream);
   return b_mn_major ? launch_gemm_ar<128, true>(tmA, tmB, args, stream)
                     : launch_gemm_ar<128, false>(tmA, tmB, args, stream);
+}
+
+extern "C" int dpfs_gemm_allreduce_bf16(const void* A, long long lda, const void* B, long long ldb, int b_mn_major,
+                                        void* out, void* mc_out, const unsigned long long* data_ptrs,
+                                        long long out_offset, int M, int N, int K,
+                                        const unsigned long long* flag_ptrs, int rank, int n, int bn,
+                                        cudaStream_t stream) {
+  return gemm_fused_collective(A, lda, B, ldb, b_mn_major, out, mc_out, data_ptrs, out_offset, nullptr, M, N, K,
+                               flag_ptrs, rank, n, bn, stream);
+}
+
+// Fused GEMM -> reduce-scatter over rows (sequence-parallel form of the row-parallel linear): `partial` (bf16 [M][N])
+// is this rank's symmetric scratch for the partial products, `rs_out` (bf16 [M / n][N], private memory) receives rows
+// [rank * M / n, (rank + 1) * M / n) of sum_r A_r B_r^T.  mc_partial != nullptr selects the NVLS data path
+// (multimem.ld_reduce through the switch), otherwise the partials are pulled from the peers (data_ptrs) and summed in
+// rank order.  Requires M % n == 0 and M / n >= 128.
+extern "C" int dpfs_gemm_reduce_scatter_bf16(const void* A, long long lda, const void* B, long long ldb,
+                                             int b_mn_major, void* partial, void* mc_partial,
+                                             const unsigned long long* data_ptrs, long long partial_offset,
+                                             void* rs_out, int M, int N, int K,
+                                             const unsigned long long* flag_ptrs, int rank, int n, int bn,
+                                             cudaStream_t stream) {
+  if (!rs_out) return -54;
+  return gemm_fused_collective(A, lda, B, ldb, b_mn_major, partial, mc_partial, data_ptrs, partial_offset, rs_out, M,
+                               N, K, flag_ptrs, rank, n, bn, stream);
 }

@@ -23,6 +23,7 @@ does five per layer, defect D7).
 from __future__ import annotations
 
 import math
+import os
 from typing import List, Optional
 
 import torch
@@ -466,10 +467,18 @@ def _partial_out(M, N):
     return torch.empty((M, N), dtype=BF16, device=torch.device("cuda", torch.cuda.current_device()))
 
 
+# GEMM -> reduce-scatter as ONE kernel (csrc/gemm_tcgen05.cu, rs mode).  Opt-in: the split path (2-SM GEMM + NVLS
+# reduce-scatter kernel) is the measured default until the fused kernel has been timed against it at TP=8.
+_FUSE_RS = os.environ.get("DPFS_FUSE_RS", "0") == "1"
+
+
 def _rowpar_rs(a_bf16, w_bf16, b_mn_major=False):
     """reduce_scatter_rows(a @ W^T)  (or a @ W when b_mn_major)."""
     M = a_bf16.shape[0]
     N = w_bf16.shape[1] if b_mn_major else w_bf16.shape[0]
+    symm = pm.pgm.symm
+    if _FUSE_RS and symm is not None and symm.can_fuse_gemm_rs(a_bf16, w_bf16, b_mn_major):
+        return symm.gemm_reduce_scatter(a_bf16, w_bf16, b_mn_major=b_mn_major)
     part = _partial_out(M, N)
     gemm_nt(a_bf16, w_bf16, b_mn_major=b_mn_major, out=part)
     return _reduce_scatter_rows(part)

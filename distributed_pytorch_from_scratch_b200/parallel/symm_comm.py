@@ -9,6 +9,8 @@ kernels (csrc/comm.cu, the FUSE_AR variant in csrc/gemm_tcgen05.cu):
     all_gather_rows(t)                 multimem.st broadcast of each rank's block
     gemm_allreduce(a, w, b_mn_major)   ONE kernel: tcgen05 GEMM whose tiles are reduced across ranks through the
                                        switch as they complete (RowParallelLinear fwd, ColumnParallelLinear dgrad)
+    gemm_reduce_scatter(a, w, ...)     ONE kernel: the sequence-parallel form -- every rank keeps only its rows of the
+                                       sum (opt-in with DPFS_FUSE_RS=1 until it has been timed against the split path)
 
 Synchronisation uses binary semaphores in a peer-mapped flag buffer (no epochs -> safe under CUDA-graph replay).
 All ranks must issue the same sequence of collectives (SPMD), on one stream.
@@ -161,6 +163,34 @@ class SymmComm:
         return out
 
     # ------------------------------------------------------------------------------------------ sequence parallel
+    def can_fuse_gemm_rs(self, a: torch.Tensor, w: torch.Tensor, b_mn_major: bool = False) -> bool:
+        """GEMM -> reduce-scatter in one kernel (both data paths: P2P pulls or NVLS multimem.ld_reduce)."""
+        if self.closed or a.dtype != BF16 or w.dtype != BF16 or self.n not in (2, 4, 8):
+            return False
+        M = a.shape[0]
+        N = w.shape[1] if b_mn_major else w.shape[0]
+        tiles = ((M + 127) // 128) * ((N + 127) // 128)
+        return (N % 8 == 0 and M % self.n == 0 and M // self.n >= 128 and M * N * 2 <= self.ag_off
+                and tiles <= 16384 and a.stride(0) % 8 == 0 and w.stride(0) % 8 == 0)
+
+    def gemm_reduce_scatter(self, a: torch.Tensor, w: torch.Tensor, b_mn_major: bool = False,
+                            bn: int = 0) -> torch.Tensor:
+        """This rank's rows of sum_r (a_r @ w_r^T) (or a_r @ w_r when ``b_mn_major``): bf16 [M / n, N], private memory.
+        ONE kernel: the partial tiles land in the symmetric buffer and the comm warps of the same CTAs reduce the rows
+        their rank owns while the tensor cores compute the next tiles."""
+        M, K = a.shape
+        N = w.shape[1] if b_mn_major else w.shape[0]
+        part = self.buffer((M, N), BF16)
+        out = torch.empty((M // self.n, N), dtype=BF16, device=a.device)
+        off = part.data_ptr() - self.base
+        mc = self.mc_base + off if self.mode == "nvls" else 0
+        rc = _lib.lib().dpfs_gemm_reduce_scatter_bf16(a.data_ptr(), a.stride(0), w.data_ptr(), w.stride(0),
+                                                      int(b_mn_major), part.data_ptr(), mc, self.data_ptrs, off,
+                                                      out.data_ptr(), M, N, K, self.flag_ptrs, self.rank, self.n, bn,
+                                                      _lib.stream())
+        _lib.check(rc, "dpfs_gemm_reduce_scatter_bf16")
+        return out
+
     def reduce_scatter_rows(self, partial: torch.Tensor) -> torch.Tensor:
         """partial: bf16 [M, N] living in the symmetric buffer (each rank's partial sums) -> this rank's reduced block
         of rows, bf16 [M / n, N] in private memory."""

@@ -50,6 +50,18 @@ int dpfs_gemm_allreduce_bf16(const void* A, long long lda, const void* B, long l
                              int N, int K, const unsigned long long* flag_ptrs, int rank, int n, int bn,
                              cudaStream_t stream);
 
+/* Fused GEMM -> reduce-scatter over rows (one kernel; the sequence-parallel form of the same call sites, SURVEY
+ * K-c1 "rowpar_gemm_reducescatter"): partial products go to the symmetric scratch `partial` ([M][N] bf16) and rank r
+ * receives rows [r*M/n, (r+1)*M/n) of the sum in its PRIVATE rs_out ([M/n][N] bf16).  Row-blocks are computed in
+ * owner-interleaved rounds so every owner's reduction overlaps the GEMM from the start.  mc_partial != NULL: the owner
+ * pulls switch-reduced rows with multimem.ld_reduce (NVLS); NULL: it sums the peers' copies in rank order (P2P).
+ * Requires M % n == 0 and M / n >= 128.  No counterpart in the reference (it has no sequence parallelism; its
+ * Reduce is always a full all-reduce, models/comm_ops.py:39). */
+int dpfs_gemm_reduce_scatter_bf16(const void* A, long long lda, const void* B, long long ldb, int b_mn_major,
+                                  void* partial, void* mc_partial, const unsigned long long* data_ptrs,
+                                  long long partial_offset, void* rs_out, int M, int N, int K,
+                                  const unsigned long long* flag_ptrs, int rank, int n, int bn, cudaStream_t stream);
+
 /* ---- Stand-alone NVLS collectives over symmetric memory ----------------------------------------------------------
  * In-place two-shot all-reduce of the `nbytes` at multicast address mc_ptr (every rank passes the same offset),
  * all-gather of nbytes_per_rank from local `src` into slot `rank` of mc_dst on every rank, and a rank-wide barrier.

@@ -1,4 +1,6 @@
 """Multi-GPU tensor-parallel tests (NCCL + our NVLink kernels).  Skipped unless the box has >= 2 GPUs."""
+import os
+
 import pytest
 import torch
 
@@ -56,6 +58,34 @@ def _comm_worker(rank, world):
         for _ in range(3):      # repeated calls reuse the same semaphores
             out = symm.gemm_allreduce(a, w, b_mn_major=bmn).clone()
         assert (out.float() - ref).abs().max().item() < 0.03 * ref.abs().max().item()
+
+
+def _fused_rs_worker(rank, world):
+    """GEMM -> reduce-scatter in one kernel vs fp32 GEMM + NCCL all-reduce + row slice; row ranges that straddle the
+    128-row tiles (1000 rows per rank) and aligned ones, K-major and MN-major B, both reduce data paths, repeated calls."""
+    import torch.distributed as dist
+    from distributed_pytorch_from_scratch_b200.ops.gemm import gemm_nt
+    from distributed_pytorch_from_scratch_b200.parallel.symm import try_enable_symm
+    symm = try_enable_symm(required=True)
+    torch.manual_seed(200 + rank)
+    for mode in (["p2p", "nvls"] if symm.mc_base else ["p2p"]):
+        symm.mode = mode
+        for (M, N, K, bmn) in [(1000 * world, 512, 256, False), (2048 * world, 768, 320, True),
+                               (128 * world, 256, 64, False)]:
+            a = torch.randn(M, K, device="cuda").to(torch.bfloat16)
+            w = (torch.randn(K, N, device="cuda") if bmn else torch.randn(N, K, device="cuda")).to(torch.bfloat16)
+            ref = gemm_nt(a, w, b_mn_major=bmn, out_dtype=torch.float32)
+            dist.all_reduce(ref)
+            rows = M // world
+            ref = ref[rank * rows:(rank + 1) * rows]
+            assert symm.can_fuse_gemm_rs(a, w, bmn)
+            for _ in range(3):      # repeated calls reuse the same semaphores
+                out = symm.gemm_reduce_scatter(a, w, b_mn_major=bmn)
+            torch.cuda.synchronize()
+            assert out.shape == (rows, N)
+            err = (out.float() - ref).abs().max().item()
+            assert err < 0.03 * ref.abs().max().item(), (mode, M, N, K, bmn, err)
+    symm.mode = "p2p"
 
 
 def _model_worker(rank, world, comm, sp=False):
@@ -116,6 +146,14 @@ def _model_worker(rank, world, comm, sp=False):
 @pytest.mark.skipif(_ngpu() < 2, reason="needs >= 2 GPUs")
 def test_symm_collectives_and_fused_gemm_allreduce():
     run_distributed(_comm_worker, 2, free_port(), backend="nccl")
+
+
+@pytest.mark.skipif(_ngpu() < 2, reason="needs >= 2 GPUs")
+@pytest.mark.skipif(os.environ.get("DPFS_TEST_EXPERIMENTAL", "0") != "1",
+                    reason="fused GEMM -> reduce-scatter is opt-in (DPFS_FUSE_RS=1) and has not been run on hardware "
+                           "yet: set DPFS_TEST_EXPERIMENTAL=1 to include it")
+def test_fused_gemm_reduce_scatter():
+    run_distributed(_fused_rs_worker, 2, free_port(), backend="nccl")
 
 
 @pytest.mark.skipif(_ngpu() < 2, reason="needs >= 2 GPUs")
