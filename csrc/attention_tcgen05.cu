@@ -600,6 +600,290 @@ attn_fwd_persistent_kernel(const __grid_constant__ CUtensorMap tm_qkv, __nv_bflo
   }
 }
 
+// ================================================================================================= forward, ping-pong
+// EXPERIMENTAL (DPFS_ATTN_FWD_PP=1, hd = 64 only).  The persistent kernel above is paced by the softmax warps' own
+// dependent chain (TMEM load -> row max -> exchange -> exp2 -> pack -> smem -> fence -> signal): the tensor pipe is 13 %
+// busy and the MUFU pipe would allow ~4x the rate.  Here one CTA works on TWO q tiles of the same (batch, head) -- tile
+// A = 2p, tile B = 2p + 1 -- with one softmax warp group each (one thread per row, no cross-thread exchange at all).
+// Every SM sub-partition then hosts one A warp and one B warp that are in different phases of the chain, and the MMA
+// thread alternates [PV_A(j), QK_A(j+1)], [PV_B(j), QK_B(j+1)], so a group's MMA latency hides behind the other
+// group's exponentials.  K / V tiles are loaded once for both q tiles (3-stage ring), Q is double buffered across
+// work items.  TMEM: S_A [0,128) S_B [128,256) O_A [256,320) O_B [320,384); S is single buffered per tile and is
+// released by the p_full signal (the group has read it twice -- max pass, exp pass -- before it signals).
+struct FwdPPCfg {
+  static constexpr int HD = 64;
+  static constexpr int kKvStages = 3;
+  static constexpr int kQBytes = kTile * HD * 2;      // one q tile
+  static constexpr int kKVBytes = kTile * HD * 2;     // one K or V tile
+  static constexpr int kPBytes = kTile * kTile * 2;   // one P tile
+  static constexpr int kSmem = 2 * 2 * kQBytes + kKvStages * 2 * kKVBytes + 2 * kPBytes + 256 + 1024;
+  static constexpr int kTmemCols = 512;
+  static_assert(kSmem <= 232448, "ping-pong forward does not fit in shared memory");
+};
+
+__global__ void __launch_bounds__(kAttnFwdThreads, 1)
+attn_fwd_pp_kernel(const __grid_constant__ CUtensorMap tm_qkv, __nv_bfloat16* __restrict__ out,
+                   float* __restrict__ lse, int B, int T, int H, int Dl, float scale_log2) {
+  using C = FwdPPCfg;
+  constexpr int HD = C::HD;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* sQ = smem;                                      // [q buffer][tile A | tile B]
+  uint8_t* sK = sQ + 2 * 2 * C::kQBytes;                   // [stage]
+  uint8_t* sV = sK + C::kKvStages * C::kKVBytes;           // [stage]
+  uint8_t* sP = sV + C::kKvStages * C::kKVBytes;           // [tile A | tile B]
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sP + 2 * C::kPBytes);
+  uint64_t* q_full = bars;         // [2]  per Q buffer
+  uint64_t* q_empty = bars + 2;    // [2]
+  uint64_t* k_full = bars + 4;     // [3]
+  uint64_t* v_full = bars + 7;     // [3]
+  uint64_t* kv_empty = bars + 10;  // [3]
+  uint64_t* s_full = bars + 13;    // [2]  per tile (A, B)
+  uint64_t* p_full = bars + 15;    // [2]
+  uint64_t* o_done = bars + 17;    // [2]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 19);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int nq = (T + kTile - 1) / kTile;
+  const int n_pairs = (nq + 1) / 2;
+  const int HB = H * B;
+  const int n_items = n_pairs * HB;
+
+  if (threadIdx.x == 0) {
+    prefetch_tmap(&tm_qkv);
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(&q_full[i], 1);
+      mbar_init(&q_empty[i], 1);
+      mbar_init(&s_full[i], 1);
+      mbar_init(&p_full[i], 4);   // the four warps of a group
+      mbar_init(&o_done[i], 1);
+    }
+    for (int i = 0; i < C::kKvStages; ++i) {
+      mbar_init(&k_full[i], 1);
+      mbar_init(&v_full[i], 1);
+      mbar_init(&kv_empty[i], 1);
+    }
+    fence_mbar_init();
+  }
+  if (warp == 1) {
+    tmem_alloc(tmem_slot, C::kTmemCols);
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  // work item w (heavy pairs first): pair = n_pairs-1 - w / HB; q tiles 2*pair (A) and 2*pair+1 (B, if it exists);
+  // kv tiles 0 .. n_kv-1 with n_kv = (B exists ? 2*pair+2 : 2*pair+1); A takes part in tiles j <= 2*pair.
+  if (warp == 0) {
+    if (lane == 0) {
+      int g = 0, it = 0;
+      for (int w = blockIdx.x; w < n_items; w += gridDim.x, ++it) {
+        const int pair = n_pairs - 1 - w / HB, rem = w % HB, h = rem % H, b = rem / H;
+        const bool has_b = 2 * pair + 1 < nq;
+        const int n_kv = has_b ? 2 * pair + 2 : 2 * pair + 1;
+        const int qb = it & 1;
+        mbar_wait(&q_empty[qb], ((it >> 1) & 1) ^ 1);
+        mbar_expect_tx(&q_full[qb], (has_b ? 2 : 1) * C::kQBytes);
+        tma_load_3d(sQ + (qb * 2 + 0) * C::kQBytes, &tm_qkv, &q_full[qb], h * HD, (2 * pair) * kTile, b);
+        if (has_b)
+          tma_load_3d(sQ + (qb * 2 + 1) * C::kQBytes, &tm_qkv, &q_full[qb], h * HD, (2 * pair + 1) * kTile, b);
+        for (int j = 0; j < n_kv; ++j, ++g) {
+          const int st = g % C::kKvStages;
+          mbar_wait(&kv_empty[st], ((g / C::kKvStages) & 1) ^ 1);
+          mbar_expect_tx(&k_full[st], C::kKVBytes);
+          tma_load_3d(sK + st * C::kKVBytes, &tm_qkv, &k_full[st], Dl + h * HD, j * kTile, b);
+          mbar_expect_tx(&v_full[st], C::kKVBytes);
+          tma_load_3d(sV + st * C::kKVBytes, &tm_qkv, &v_full[st], 2 * Dl + h * HD, j * kTile, b);
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      constexpr uint32_t idesc_s = make_idesc_bf16(kTile, kTile, false, false);
+      constexpr uint32_t idesc_o = make_idesc_bf16(kTile, HD, false, true);
+      int g = 0, it = 0;
+      int cnt_a = 0, cnt_b = 0;   // steps issued so far per tile slot (phase of s_full / p_full / o_done)
+      for (int w = blockIdx.x; w < n_items; w += gridDim.x, ++it) {
+        const int pair = n_pairs - 1 - w / HB;
+        const bool has_b = 2 * pair + 1 < nq;
+        const int n_kv = has_b ? 2 * pair + 2 : 2 * pair + 1;
+        const int n_of_a = 2 * pair + 1, n_of_b = has_b ? 2 * pair + 2 : 0;   // kv tiles each q tile takes part in
+        const int qb = it & 1;
+        const int g0 = g;   // ring position of kv tile 0 of this item
+        // S_x(j) = Q_x K(j)^T
+        auto issue_qk = [&](int x, int j) {
+          const int st = (g0 + j) % C::kKvStages;
+          mbar_wait(&k_full[st], ((g0 + j) / C::kKvStages) & 1);
+          tc_fence_after();
+          const uint32_t q_base = smem_u32(sQ + (qb * 2 + x) * C::kQBytes);
+          const uint32_t k_base = smem_u32(sK + st * C::kKVBytes);
+#pragma unroll
+          for (int kk = 0; kk < HD / 16; ++kk)
+            umma_bf16_ss(tmem_base + x * 128, desc_kmajor(q_base, kk, kTile * 128),
+                         desc_kmajor(k_base, kk, kTile * 128), idesc_s, kk > 0);
+          umma_commit(&s_full[x]);
+        };
+        mbar_wait(&q_full[qb], (it >> 1) & 1);
+        issue_qk(0, 0);
+        if (has_b) issue_qk(1, 0);
+        if (n_kv == 1) umma_commit(&q_empty[qb]);   // (single-tile item: no further QK)
+        for (int j = 0; j < n_kv; ++j) {
+          const int st = (g0 + j) % C::kKvStages;
+          bool v_ready = false;
+#pragma unroll
+          for (int x = 0; x < 2; ++x) {
+            const int n_of_x = x == 0 ? n_of_a : n_of_b;
+            int& cnt_x = x == 0 ? cnt_a : cnt_b;
+            if (j >= n_of_x) continue;
+            mbar_wait(&p_full[x], cnt_x & 1);       // P_x(j) is in smem, S_x has been read out
+            if (!v_ready) {
+              mbar_wait(&v_full[st], ((g0 + j) / C::kKvStages) & 1);
+              v_ready = true;
+            }
+            tc_fence_after();
+            const uint32_t p_base = smem_u32(sP + x * C::kPBytes);
+            const uint32_t v_base = smem_u32(sV + st * C::kKVBytes);
+#pragma unroll
+            for (int kk = 0; kk < kTile / 16; ++kk)
+              umma_bf16_ss(tmem_base + 256 + x * HD, desc_kmajor(p_base, kk, kTile * 128),
+                           desc_mnmajor(v_base, kk, kTile * 128), idesc_o, (j > 0 || kk > 0) ? 1u : 0u);
+            umma_commit(&o_done[x]);
+            ++cnt_x;
+            if (j + 1 < n_of_x) {
+              issue_qk(x, j + 1);
+              // the item's last QK is tile B's (or A's when there is no B) for kv tile n_kv - 1
+              if (j + 2 == n_kv && (x == 1 || !has_b)) umma_commit(&q_empty[qb]);
+            }
+          }
+          umma_commit(&kv_empty[st]);   // K(j) / V(j) have no reader left once the MMAs issued so far retire
+        }
+        g += n_kv;
+      }
+    }
+  } else {
+    // softmax groups: warps 2-5 -> tile A, warps 6-9 -> tile B; thread = one q row, all 128 kv columns
+    const int x = (warp - 2) >> 2;
+    const int q = warp & 3;
+    const int r = q * 32 + lane;
+    const uint32_t lane_off = static_cast<uint32_t>(q * 32) << 16;
+    const uint32_t tS = tmem_base + x * 128, tO = tmem_base + 256 + x * HD;
+    uint8_t* sPx = sP + x * C::kPBytes;
+    int cnt = 0;   // steps done by this group (phase of s_full / p_full / o_done of slot x)
+    for (int w = blockIdx.x; w < n_items; w += gridDim.x) {
+      const int pair = n_pairs - 1 - w / HB, rem = w % HB, h = rem % H, b = rem / H;
+      const int qt = 2 * pair + x;
+      if (qt >= nq) continue;   // odd number of q tiles: the last pair has no tile B
+      const int q0 = qt * kTile;
+      float m_run = -INFINITY, l_run = 0.f;
+      for (int j = 0; j <= qt; ++j, ++cnt) {
+        mbar_wait(&s_full[x], cnt & 1);
+        tc_fence_after();
+        // pass 1: row max over the 128 columns (two TMEM loads in flight)
+        float mloc = -INFINITY;
+#pragma unroll 1
+        for (int c2 = 0; c2 < 2; ++c2) {
+          uint32_t t0[32], t1[32];
+          tmem_ld32(tS + lane_off + (2 * c2) * 32, t0);
+          tmem_ld32(tS + lane_off + (2 * c2 + 1) * 32, t1);
+          tmem_ld_wait();
+          float m4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
+#pragma unroll
+          for (int i = 0; i < 32; ++i) {
+            float a = __uint_as_float(t0[i]), bb = __uint_as_float(t1[i]);
+            if (j == qt) {   // diagonal tile: causal mask (also hides kv columns past T)
+              if ((2 * c2) * 32 + i > r) a = -INFINITY;
+              if ((2 * c2 + 1) * 32 + i > r) bb = -INFINITY;
+            }
+            m4[i & 3] = fmaxf(m4[i & 3], fmaxf(a, bb));
+          }
+          mloc = fmaxf(mloc, fmaxf(fmaxf(m4[0], m4[1]), fmaxf(m4[2], m4[3])));
+        }
+        mloc *= scale_log2;   // scale > 0: max commutes with the scaling
+        const float mx = (mloc > m_run + 8.f) ? mloc : m_run;   // lazy rescaling (see attn_fwd_kernel)
+        const float alpha = fast_exp2(m_run - mx);
+        m_run = mx;
+        if (j > 0) {
+          mbar_wait(&o_done[x], (cnt - 1) & 1);   // PV_x(j-1): O may be rescaled, P may be overwritten
+          tc_fence_after();
+          if (__any_sync(0xffffffffu, alpha != 1.f)) {
+#pragma unroll
+            for (int c = 0; c < HD / 32; ++c) {
+              uint32_t o[32];
+              tmem_ld32(tO + lane_off + c * 32, o);
+              tmem_ld_wait();
+#pragma unroll
+              for (int i = 0; i < 32; ++i) o[i] = __float_as_uint(__uint_as_float(o[i]) * alpha);
+              tmem_st32(tO + lane_off + c * 32, o);
+            }
+            tmem_st_wait();
+          }
+        }
+        // pass 2: p = exp2(s * scale - m) -> bf16 P tile in smem, row sum
+        float s4[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+          uint32_t tv[32];
+          tmem_ld32(tS + lane_off + c * 32, tv);
+          tmem_ld_wait();
+          uint32_t packed[16];
+#pragma unroll
+          for (int i = 0; i < 32; i += 2) {
+            float p0 = fast_exp2(__uint_as_float(tv[i]) * scale_log2 - mx);
+            float p1 = fast_exp2(__uint_as_float(tv[i + 1]) * scale_log2 - mx);
+            if (j == qt) {
+              if (c * 32 + i > r) p0 = 0.f;
+              if (c * 32 + i + 1 > r) p1 = 0.f;
+            }
+            s4[i & 3] += p0;
+            s4[(i + 1) & 3] += p1;
+            packed[i >> 1] = pack_bf16(p0, p1);
+          }
+          st_tile_row32(sPx, r, c * 32, packed);
+        }
+        l_run = l_run * alpha + ((s4[0] + s4[1]) + (s4[2] + s4[3]));
+        fence_proxy_async_smem();
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&p_full[x]);
+      }
+      // item epilogue for this group's tile
+      mbar_wait(&o_done[x], (cnt - 1) & 1);
+      tc_fence_after();
+      const float inv_l = 1.f / l_run;
+      const bool valid = (q0 + r) < T;
+      __nv_bfloat16* orow = out + (static_cast<long long>(b) * T + q0 + r) * Dl + h * HD;
+#pragma unroll
+      for (int c = 0; c < HD / 32; ++c) {
+        uint32_t o[32];
+        tmem_ld32(tO + lane_off + c * 32, o);
+        tmem_ld_wait();
+        if (valid) {
+#pragma unroll
+          for (int v8 = 0; v8 < 4; ++v8) {
+            uint4 wv;
+            wv.x = pack_bf16(__uint_as_float(o[8 * v8 + 0]) * inv_l, __uint_as_float(o[8 * v8 + 1]) * inv_l);
+            wv.y = pack_bf16(__uint_as_float(o[8 * v8 + 2]) * inv_l, __uint_as_float(o[8 * v8 + 3]) * inv_l);
+            wv.z = pack_bf16(__uint_as_float(o[8 * v8 + 4]) * inv_l, __uint_as_float(o[8 * v8 + 5]) * inv_l);
+            wv.w = pack_bf16(__uint_as_float(o[8 * v8 + 6]) * inv_l, __uint_as_float(o[8 * v8 + 7]) * inv_l);
+            *reinterpret_cast<uint4*>(orow + c * 32 + v8 * 8) = wv;
+          }
+        }
+      }
+      if (valid && lse) lse[(static_cast<long long>(b) * H + h) * T + q0 + r] = (m_run + log2f(l_run)) * kLn2;
+      tc_fence_before();   // the O reads above are ordered before the next item's first PV_x (via p_full)
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, C::kTmemCols);
+  }
+}
+
 // ================================================================================================= backward
 // delta[b][h][i] = sum_c dO[i][c] * O[i][c]   (one warp per (row, head))
 __global__ void attn_delta_kernel(const __nv_bfloat16* __restrict__ o, const __nv_bfloat16* __restrict__ d_o,
@@ -1250,6 +1534,24 @@ static int launch_fwd_persistent(const CUtensorMap& tm, void* out, float* lse, i
   return static_cast<int>(cudaGetLastError());
 }
 
+static int launch_fwd_pp(const CUtensorMap& tm, void* out, float* lse, int B, int T, int H, float scale,
+                         cudaStream_t stream) {
+  using C = FwdPPCfg;
+  auto kfn = attn_fwd_pp_kernel;
+  static bool configured = false;
+  if (!configured) {
+    cudaError_t e = cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmem);
+    if (e != cudaSuccess) return static_cast<int>(e);
+    configured = true;
+  }
+  const int nq = (T + kTile - 1) / kTile;
+  const int items = ((nq + 1) / 2) * H * B;
+  const int grid = items < num_sms() ? items : num_sms();
+  kfn<<<(DPFS_COUNT(), grid), kAttnFwdThreads, C::kSmem, stream>>>(tm, reinterpret_cast<__nv_bfloat16*>(out), lse, B, T,
+                                                                  H, H * C::HD, scale * kLog2e);
+  return static_cast<int>(cudaGetLastError());
+}
+
 template <int HD>
 static int launch_bwd(const CUtensorMap& tm_qkv, const CUtensorMap& tm_do, const float* lse, const float* delta,
                       float* dq_acc, void* dqkv, int B, int T, int H, float scale, cudaStream_t stream) {
@@ -1304,6 +1606,12 @@ extern "C" int dpfs_attn_fwd(const void* qkv, void* out, float* lse, int B, int 
     const char* e = getenv("DPFS_ATTN_PERSISTENT");
     persistent = e ? atoi(e) : 1;
   }
+  static int pingpong = -1;   // experimental two-q-tile kernel (hd = 64), see attn_fwd_pp_kernel
+  if (pingpong < 0) {
+    const char* e = getenv("DPFS_ATTN_FWD_PP");
+    pingpong = e ? atoi(e) : 0;
+  }
+  if (pingpong && HD == 64) return launch_fwd_pp(tm, out, lse, B, T, H, scale, stream);
   if (persistent)
     return HD == 64 ? launch_fwd_persistent<64>(tm, out, lse, B, T, H, scale, stream)
                     : launch_fwd_persistent<128>(tm, out, lse, B, T, H, scale, stream);
