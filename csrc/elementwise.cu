@@ -48,6 +48,20 @@ __device__ __forceinline__ void store4<__nv_bfloat16>(__nv_bfloat16* p, const fl
   *reinterpret_cast<uint2*>(p) = t;
 }
 
+// A bf16 element addressed through an NVLS MULTICAST mapping: one store lands in every rank's copy of the symmetric
+// buffer (the NVSwitch replicates it).  Kernels instantiated with this output type all-gather what they produce as
+// they produce it ("push" all-gather: the separate all-gather kernel and its read of the local block disappear).
+struct McBf16 {
+  __nv_bfloat16 v;
+};
+static_assert(sizeof(McBf16) == 2, "McBf16 must index like bf16");
+template <>
+__device__ __forceinline__ void store4<McBf16>(McBf16* p, const float (&v)[4]) {
+  asm volatile("multimem.st.relaxed.sys.global.v2.bf16x2 [%0], {%1, %2};" ::"l"(p), "r"(pack_bf16(v[0], v[1])),
+               "r"(pack_bf16(v[2], v[3]))
+               : "memory");
+}
+
 constexpr int kNormThreads = 256;  // 8 warps, one row per warp at a time
 constexpr int kMaxNV = 16;         // float4 per lane -> D <= 2048 per warp-row
 
@@ -100,10 +114,10 @@ __global__ void __launch_bounds__(kNormThreads) rmsnorm_fwd_kernel(const XT* __r
 // x_out = x + y + bias (fp32 residual stream), h = rmsnorm(x_out) * scale (bf16).  `y` is the all-reduced bf16 output
 // of a row-parallel GEMM (reference models/layers.py:51-54 followed by models/model.py:119-120): the residual add,
 // the replicated bias and the next layer's norm become one pass.  h / scale may be null (residual add only).
-template <int NV>
+template <int NV, typename HT = __nv_bfloat16>
 __global__ void __launch_bounds__(kNormThreads) add_rmsnorm_fwd_kernel(
     const float* __restrict__ x, const __nv_bfloat16* __restrict__ y, const float* __restrict__ bias,
-    const float* __restrict__ scale, float* __restrict__ x_out, __nv_bfloat16* __restrict__ h,
+    const float* __restrict__ scale, float* __restrict__ x_out, HT* __restrict__ h,
     float* __restrict__ rstd_out, int M, int D, float eps) {
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int wpb = kNormThreads / 32;
@@ -148,7 +162,7 @@ __global__ void __launch_bounds__(kNormThreads) add_rmsnorm_fwd_kernel(
           float o[4];
 #pragma unroll
           for (int j = 0; j < 4; ++j) o[j] = v[i][j] * rstd * sc[i][j];
-          store4<__nv_bfloat16>(h + off + c, o);
+          store4<HT>(h + off + c, o);
         }
       }
     }
@@ -161,11 +175,11 @@ __global__ void __launch_bounds__(kNormThreads) add_rmsnorm_fwd_kernel(
 // in a fixed order (deterministic).
 // CS: also emit per-block column sums of the produced dx (the bias gradient of the row-parallel linear whose output
 // this residual-stream gradient is) as a second row of partials: scratch is then [gridDim.x][2 * D].
-template <typename XT, typename GT, int NV, bool CS = false>
+template <typename XT, typename GT, int NV, bool CS = false, typename BT = __nv_bfloat16>
 __global__ void __launch_bounds__(kNormThreads) rmsnorm_bwd_kernel(
     const GT* __restrict__ dy, const XT* __restrict__ x, const float* __restrict__ rstd_in,
     const float* __restrict__ scale, const float* __restrict__ dres, float* __restrict__ dx,
-    __nv_bfloat16* __restrict__ dx_bf16, float* __restrict__ scratch, int M, int D) {
+    BT* __restrict__ dx_bf16, float* __restrict__ scratch, int M, int D) {
   __shared__ float red[kNormThreads / 32][32 * 4];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int wpb = kNormThreads / 32;
@@ -222,7 +236,7 @@ __global__ void __launch_bounds__(kNormThreads) rmsnorm_bwd_kernel(
 #pragma unroll
         for (int j = 0; j < 4; ++j) o[j] = rstd * (g[i][j] - xh[i][j] * dot) + rs[i][j];
         if (dx) store4<float>(dx + off + c, o);
-        if (dx_bf16) store4<__nv_bfloat16>(dx_bf16 + off + c, o);
+        if (dx_bf16) store4<BT>(dx_bf16 + off + c, o);
         if (CS) {
 #pragma unroll
           for (int j = 0; j < 4; ++j) cs[i][j] += o[j];
@@ -701,6 +715,16 @@ __global__ void cast_f32_to_bf16_kernel(const float* __restrict__ x, __nv_bfloat
   }
 }
 
+// cast + push all-gather: y_mc is the multicast address of this rank's block in the landing zone
+__global__ void cast_f32_to_bf16_mc_kernel(const float* __restrict__ x, McBf16* __restrict__ y_mc, long long n4) {
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < n4;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const float4 v = *reinterpret_cast<const float4*>(x + i * 4);
+    const float o[4] = {v.x, v.y, v.z, v.w};
+    store4<McBf16>(y_mc + i * 4, o);
+  }
+}
+
 int num_sms();
 
 static inline int ew_grid(long long work_items, int threads) {
@@ -987,6 +1011,65 @@ extern "C" int dpfs_cast_f32_to_bf16(const float* x, void* y, long long n, cudaS
   if (n % 4 != 0) return -24;
   if (n <= 0) return 0;
   cast_f32_to_bf16_kernel<<<(DPFS_COUNT(), ew_grid(n / 4, 256)), 256, 0, stream>>>(x, (__nv_bfloat16*)y, n / 4);
+  return static_cast<int>(cudaGetLastError());
+}
+
+// ------------------------------------------------------------------------------------- push all-gather variants
+// Sequence parallelism needs the bf16 activations these kernels produce (h = norm(x), the bf16 copy of a
+// residual-stream gradient) on EVERY rank.  Instead of writing the local block and running an all-gather kernel over
+// it, the *_mc entry points write through the NVLS multicast mapping of the all-gather landing zone: `*_mc` arguments
+// are multicast addresses of THIS rank's block (mc_base + zone offset + rank * block bytes).  The caller runs
+// dpfs_comm_barrier afterwards; every rank then holds all n blocks.  fp32 outputs (x_out, dx, rstd, dscale) stay local.
+extern "C" int dpfs_rmsnorm_fwd_mc(const float* x, const float* scale, void* y_mc, float* rstd, int M, int D, float eps,
+                                   cudaStream_t stream) {
+  if (D % 4 != 0 || D > 128 * kMaxNV) return -20;
+  if (M <= 0) return 0;
+  const int grid = norm_grid(M);
+  DISPATCH_NV(D, {
+    rmsnorm_fwd_kernel<float, McBf16, NV><<<(DPFS_COUNT(), grid), kNormThreads, 0, stream>>>(
+        x, scale, reinterpret_cast<McBf16*>(y_mc), rstd, M, D, eps);
+  });
+  return static_cast<int>(cudaGetLastError());
+}
+
+extern "C" int dpfs_add_rmsnorm_fwd_mc(const float* x, const void* y_bf16, const float* bias, const float* scale,
+                                       float* x_out, void* h_mc, float* rstd, int M, int D, float eps,
+                                       cudaStream_t stream) {
+  if (D % 4 != 0 || D > 128 * kMaxNV) return -20;
+  if (!h_mc || !scale) return -21;
+  if (M <= 0) return 0;
+  const int grid = norm_grid(M);
+  DISPATCH_NV(D, {
+    add_rmsnorm_fwd_kernel<NV, McBf16><<<(DPFS_COUNT(), grid), kNormThreads, 0, stream>>>(
+        x, (const __nv_bfloat16*)y_bf16, bias, scale, x_out, reinterpret_cast<McBf16*>(h_mc), rstd, M, D, eps);
+  });
+  return static_cast<int>(cudaGetLastError());
+}
+
+// dy bf16, x fp32 (the sequence-parallel layer's combination); dx (fp32, local, nullable) and dx_mc (pushed bf16 copy)
+extern "C" int dpfs_rmsnorm_bwd_mc(const void* dy_bf16, const float* x, const float* rstd, const float* scale,
+                                   const float* dres, float* dx, void* dx_mc, float* dscale, int dscale_accumulate,
+                                   float* scratch, int M, int D, cudaStream_t stream) {
+  if (D % 4 != 0 || D > 128 * kMaxNV) return -20;
+  if (!dx_mc) return -21;
+  if (M <= 0) return 0;
+  const int grid = norm_grid(M);
+  DISPATCH_NV(D, {
+    rmsnorm_bwd_kernel<float, __nv_bfloat16, NV, false, McBf16><<<(DPFS_COUNT(), grid), kNormThreads, 0, stream>>>(
+        (const __nv_bfloat16*)dy_bf16, x, rstd, scale, dres, dx, reinterpret_cast<McBf16*>(dx_mc), scratch, M, D);
+  });
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return static_cast<int>(e);
+  reduce_partials_kernel<<<(DPFS_COUNT(), (D + 31) / 32), kReduceGroups * 32, 0, stream>>>(scratch, dscale, grid, D,
+                                                                                       dscale_accumulate);
+  return static_cast<int>(cudaGetLastError());
+}
+
+extern "C" int dpfs_cast_f32_to_bf16_mc(const float* x, void* y_mc, long long n, cudaStream_t stream) {
+  if (n % 4 != 0) return -24;
+  if (n <= 0) return 0;
+  cast_f32_to_bf16_mc_kernel<<<(DPFS_COUNT(), ew_grid(n / 4, 256)), 256, 0, stream>>>(
+      x, reinterpret_cast<McBf16*>(y_mc), n / 4);
   return static_cast<int>(cudaGetLastError());
 }
 

@@ -459,6 +459,15 @@ def _all_gather_rows(local, keep: bool = False):
     return out
 
 
+def _push_comm(x_l):
+    """The symmetric communicator when pushed all-gathers are enabled (DPFS_FUSE_AG=1 + NVLS multicast) and a block of
+    x_l's shape fits a push zone; None -> the split path (local block + all-gather kernel)."""
+    symm = pm.pgm.symm
+    if symm is not None and x_l.dim() == 2 and symm.can_push(x_l.shape[0], x_l.shape[1] * 2):
+        return symm
+    return None
+
+
 def _partial_out(M, N):
     """Where a row-parallel GEMM writes its partial sums: straight into the symmetric buffer when there is one."""
     symm = pm.pgm.symm
@@ -488,14 +497,23 @@ class FusedLayerSPFn(torch.autograd.Function):
     @staticmethod
     def forward(ctx, x_l, pos, rt, pack: LayerPack, meta: Meta, *params):
         m = meta
-        h1_l, rstd1 = fused.rmsnorm_fwd(x_l, pack.s1, rt.eps)
-        h1 = _all_gather_rows(h1_l, keep=True)
+        push = _push_comm(x_l)
+        if push is not None:   # the norm kernel all-gathers h as it writes it (multicast stores)
+            h1, rstd1 = fused.rmsnorm_fwd_push(x_l, pack.s1, rt.eps, push)
+            h1 = h1.clone()    # saved for the backward wgrad; the landing zone is recycled two pushes later
+        else:
+            h1_l, rstd1 = fused.rmsnorm_fwd(x_l, pack.s1, rt.eps)
+            h1 = _all_gather_rows(h1_l, keep=True)
         qkv = gemm_nt(h1, pack.wqkv, bias=pack.bqkv, out_dtype=BF16)
         fused.rope_inplace(qkv, pos, rt.cos_half, rt.sin_half, 2, m.Dl, m.Hl, m.hd, inverse=False)
         attn, lse = attn_fwd(qkv, m.B, m.T, m.Hl, m.hd, m.scale)
         y_l = _rowpar_rs(attn, pack.wo)
-        x2_l, h2_l, rstd2 = fused.add_rmsnorm_fwd(x_l, y_l, pack.bo, pack.s2, rt.eps)
-        h2 = _all_gather_rows(h2_l, keep=True)
+        if push is not None:
+            x2_l, h2, rstd2 = fused.add_rmsnorm_fwd_push(x_l, y_l, pack.bo, pack.s2, rt.eps, push)
+            h2 = h2.clone()
+        else:
+            x2_l, h2_l, rstd2 = fused.add_rmsnorm_fwd(x_l, y_l, pack.bo, pack.s2, rt.eps)
+            h2 = _all_gather_rows(h2_l, keep=True)
         gu = gemm_nt(h2, pack.wgu, bias=pack.bgu, out_dtype=BF16)
         act = fused.swiglu_fwd(gu)
         y_l = _rowpar_rs(act, pack.wd)
@@ -509,7 +527,11 @@ class FusedLayerSPFn(torch.autograd.Function):
         x_l, pos, h1, rstd1, qkv, attn, lse, x2_l, h2, rstd2, gu, act = ctx.saved_tensors
         pack, m, rt = ctx.pack, ctx.meta, ctx.rt
         dx3_l = dx3_l.contiguous()
-        dx3 = _all_gather_rows(fused.cast_to_bf16(dx3_l))                              # [M, d] bf16
+        push = _push_comm(dx3_l)
+        if push is not None:
+            dx3 = fused.cast_to_bf16_push(dx3_l, push)                                   # [M, d] bf16 (landing zone)
+        else:
+            dx3 = _all_gather_rows(fused.cast_to_bf16(dx3_l))                            # [M, d] bf16
         dact = gemm_nt(dx3, pack.wd, b_mn_major=True, out_dtype=BF16)
         _wgrad(dx3, act, pack.g_wd)
         fused.colsum(dx3, out=pack.g_bd)
@@ -518,9 +540,12 @@ class FusedLayerSPFn(torch.autograd.Function):
         dh2_l = _rowpar_rs(dgu, pack.wgu, b_mn_major=True)                               # [Ml, d]
         _wgrad(dgu, h2, pack.g_wgu)
         del dgu
-        dx2_l, dx2_lb, _ = fused.rmsnorm_bwd(dh2_l, x2_l, rstd2, pack.s2, dres=dx3_l, want_fp32=True, want_bf16=True,
-                                             dscale_out=pack.g_s2)
-        dx2 = _all_gather_rows(dx2_lb)
+        if push is not None:
+            dx2_l, dx2 = fused.rmsnorm_bwd_push(dh2_l, x2_l, rstd2, pack.s2, dx3_l, push, dscale_out=pack.g_s2)
+        else:
+            dx2_l, dx2_lb, _ = fused.rmsnorm_bwd(dh2_l, x2_l, rstd2, pack.s2, dres=dx3_l, want_fp32=True,
+                                                 want_bf16=True, dscale_out=pack.g_s2)
+            dx2 = _all_gather_rows(dx2_lb)
         dattn = gemm_nt(dx2, pack.wo, b_mn_major=True, out_dtype=BF16)
         _wgrad(dx2, attn, pack.g_wo)
         fused.colsum(dx2, out=pack.g_bo)

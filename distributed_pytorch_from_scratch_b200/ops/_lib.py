@@ -47,6 +47,10 @@ SIGS = {
     "dpfs_rmsnorm_bwd": (c_p, c_int, c_p, c_int, c_p, c_p, c_p, c_p, c_p, c_p, c_int, c_p, c_int, c_int, c_p),
     "dpfs_rmsnorm_bwd_bias": (c_p, c_int, c_p, c_int, c_p, c_p, c_p, c_p, c_p, c_p, c_int, c_p, c_p, c_int, c_int,
                               c_p),
+    "dpfs_rmsnorm_fwd_mc": (c_p, c_p, c_p, c_p, c_int, c_int, c_f, c_p),
+    "dpfs_add_rmsnorm_fwd_mc": (c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_int, c_int, c_f, c_p),
+    "dpfs_rmsnorm_bwd_mc": (c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_int, c_p, c_int, c_int, c_p),
+    "dpfs_cast_f32_to_bf16_mc": (c_p, c_p, c_ll, c_p),
     "dpfs_layernorm_fwd": (c_p, c_int, c_p, c_p, c_p, c_int, c_p, c_p, c_int, c_int, c_f, c_p),
     "dpfs_layernorm_bwd": (c_p, c_int, c_p, c_int, c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_int, c_int, c_p),
     "dpfs_swiglu_fwd": (c_p, c_p, c_int, c_int, c_p),

@@ -98,6 +98,67 @@ def rmsnorm_bwd(dy: torch.Tensor, x: torch.Tensor, rstd: torch.Tensor, scale: to
     return dx, dxb, dscale
 
 
+# ------------------------------------------------------------------------------------------------ push all-gather
+# Sequence-parallel producers that all-gather their bf16 output while writing it (NVLS multicast stores into every
+# rank's landing zone, parallel/symm_comm.py:push_block) instead of "write the local block, then all-gather kernel".
+# Each returns the gathered [n * Ml, D] bf16 view (valid until the second-next push) after the rank barrier.
+def rmsnorm_fwd_push(x_l: torch.Tensor, scale: torch.Tensor, eps: float, symm):
+    Ml, D = x_l.shape
+    assert x_l.dtype == F32 and x_l.is_contiguous()
+    mc, full = symm.push_block(Ml, D)
+    rstd = torch.empty(Ml, dtype=F32, device=x_l.device)
+    rc = _lib.lib().dpfs_rmsnorm_fwd_mc(x_l.data_ptr(), scale.data_ptr(), mc, rstd.data_ptr(), Ml, D, eps,
+                                        _lib.stream())
+    _lib.check(rc, "dpfs_rmsnorm_fwd_mc")
+    symm.push_done()
+    return full, rstd
+
+
+def add_rmsnorm_fwd_push(x_l: torch.Tensor, y_l: torch.Tensor, bias, scale: torch.Tensor, eps: float, symm):
+    """x_out = x + y + bias (fp32, local rows); h = rmsnorm(x_out) * scale pushed to every rank.
+    Returns (x_out [Ml, D], h_full [n * Ml, D] bf16, rstd [Ml])."""
+    Ml, D = x_l.shape
+    assert x_l.dtype == F32 and y_l.dtype == BF16 and x_l.is_contiguous() and y_l.is_contiguous()
+    mc, full = symm.push_block(Ml, D)
+    x_out = torch.empty_like(x_l)
+    rstd = torch.empty(Ml, dtype=F32, device=x_l.device)
+    rc = _lib.lib().dpfs_add_rmsnorm_fwd_mc(x_l.data_ptr(), y_l.data_ptr(), _lib.ptr(bias), scale.data_ptr(),
+                                            x_out.data_ptr(), mc, rstd.data_ptr(), Ml, D, eps, _lib.stream())
+    _lib.check(rc, "dpfs_add_rmsnorm_fwd_mc")
+    symm.push_done()
+    return x_out, full, rstd
+
+
+def rmsnorm_bwd_push(dy_l: torch.Tensor, x_l: torch.Tensor, rstd: torch.Tensor, scale: torch.Tensor, dres, symm,
+                     dscale_out: torch.Tensor, want_fp32: bool = True):
+    """dx = dres + rmsnorm'(dy) on the local rows; its bf16 copy is pushed to every rank.
+    Returns (dx fp32 [Ml, D] | None, dx_full bf16 [n * Ml, D])."""
+    Ml, D = x_l.shape
+    assert dy_l.dtype == BF16 and x_l.dtype == F32 and dy_l.is_contiguous() and x_l.is_contiguous()
+    mc, full = symm.push_block(Ml, D)
+    dx = torch.empty((Ml, D), dtype=F32, device=x_l.device) if want_fp32 else None
+    lib = _lib.lib()
+    scratch = _scratch(x_l.device, "norm", lib.dpfs_norm_bwd_blocks(Ml) * D)
+    if dres is not None:
+        assert dres.dtype == F32 and dres.is_contiguous()
+    rc = lib.dpfs_rmsnorm_bwd_mc(dy_l.data_ptr(), x_l.data_ptr(), rstd.data_ptr(), scale.data_ptr(), _lib.ptr(dres),
+                                 _lib.ptr(dx), mc, dscale_out.data_ptr(), 0, scratch.data_ptr(), Ml, D, _lib.stream())
+    _lib.check(rc, "dpfs_rmsnorm_bwd_mc")
+    symm.push_done()
+    return dx, full
+
+
+def cast_to_bf16_push(x_l: torch.Tensor, symm) -> torch.Tensor:
+    """bf16(x_l) pushed to every rank: [Ml, D] fp32 -> gathered [n * Ml, D] bf16."""
+    Ml, D = x_l.shape
+    assert x_l.dtype == F32 and x_l.is_contiguous() and x_l.numel() % 4 == 0
+    mc, full = symm.push_block(Ml, D)
+    _lib.check(_lib.lib().dpfs_cast_f32_to_bf16_mc(x_l.data_ptr(), mc, x_l.numel(), _lib.stream()),
+               "dpfs_cast_f32_to_bf16_mc")
+    symm.push_done()
+    return full
+
+
 # ------------------------------------------------------------------------------------------------ LayerNorm
 def layernorm_fwd(x, gamma, beta, eps: float, out_dtype=BF16):
     D = x.shape[-1]

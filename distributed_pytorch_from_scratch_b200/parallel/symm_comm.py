@@ -45,6 +45,16 @@ class SymmComm:
         self.gather_off = self.capacity - self.capacity // 16
         self.ag_off = (self.capacity // 2) // 256 * 256
         self.ag_bytes = self.gather_off - self.ag_off
+        # "push" all-gather (opt-in, DPFS_FUSE_AG=1, needs the multicast mapping): producers write their bf16 block
+        # straight into every rank's landing zone.  The landing area is then split: first half for the stand-alone
+        # all-gather kernels, second half = two alternating push zones (see push_block).
+        self.push_enabled = bool(self.mc_base) and os.environ.get("DPFS_FUSE_AG", "0") == "1"
+        if self.push_enabled:
+            half = (self.ag_bytes // 2) // 256 * 256
+            self.push_off = self.ag_off + half
+            self.push_zone_bytes = ((self.ag_bytes - half) // 2) // 256 * 256
+            self.ag_bytes = half
+            self._push_zone = 0
         self.closed = False
         # data path of the reduce: "p2p" (plain NVLink loads/stores, rank-ordered fp32 sums) or "nvls" (multimem.*)
         # Measured (profiles/comm_paths_r1.md): P2P wins at TP=2 (100 vs 116 us for 32.8 MB), NVLS wins at TP=8 (123 vs
@@ -224,6 +234,32 @@ class SymmComm:
         _lib.check(rc, "dpfs_allgather")
         shape = (self.n * local.shape[0],) + tuple(local.shape[1:])
         return self.data[self.ag_off:self.ag_off + nbytes * self.n].view(local.dtype).view(shape)
+
+    # ------------------------------------------------------------------------------------------ push all-gather
+    def can_push(self, block_rows: int, row_bytes: int) -> bool:
+        nbytes = block_rows * row_bytes
+        return (self.push_enabled and not self.closed and nbytes % 16 == 0
+                and nbytes * self.n <= self.push_zone_bytes)
+
+    def push_block(self, block_rows: int, cols: int, dtype=BF16):
+        """Next landing zone for a pushed all-gather of [block_rows, cols] blocks: returns (multicast address of THIS
+        rank's block, view [n * block_rows, cols] of the whole zone in this rank's copy).  The producer kernel writes
+        through the multicast address; call ``push_done()`` before reading the view.
+
+        Two zones alternate.  A rank can only be writing gather k+2 into a zone after it has passed the barrier of
+        gather k+1, which every rank enters only after it has finished (in stream order) reading gather k from that
+        zone -- so one barrier per gather is enough and no rank overwrites data a peer still reads."""
+        esz = torch.empty((), dtype=dtype).element_size()
+        nbytes = block_rows * cols * esz
+        assert self.can_push(block_rows, cols * esz), "push all-gather zone too small (or DPFS_FUSE_AG off)"
+        self._push_zone ^= 1
+        off = self.push_off + self._push_zone * self.push_zone_bytes
+        view = self.data[off:off + nbytes * self.n].view(dtype).view(self.n * block_rows, cols)
+        return self.mc_base + off + self.rank * nbytes, view
+
+    def push_done(self):
+        """Rank-wide barrier after a pushed all-gather: every rank's block is complete and visible."""
+        self.barrier()
 
     def barrier(self):
         _lib.check(_lib.lib().dpfs_comm_barrier(self.flag_ptrs, self.rank, self.n, _lib.stream()), "dpfs_comm_barrier")

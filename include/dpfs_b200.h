@@ -127,6 +127,20 @@ int dpfs_rmsnorm_bwd(const void* dy, int dy_bf16, const void* x, int x_bf16, con
 int dpfs_rmsnorm_bwd_bias(const void* dy, int dy_bf16, const void* x, int x_bf16, const float* rstd,
                           const float* scale, const float* dres /*nullable*/, float* dx, void* dx_bf16, float* dscale,
                           int dscale_accumulate, float* dbias, float* scratch, int M, int D, cudaStream_t stream);
+/* ---- "push" all-gather variants (sequence parallelism; no counterpart in the reference, which has no SP) --------
+ * The bf16 activation a kernel produces is written through the NVLS MULTICAST mapping of the all-gather landing zone
+ * (`*_mc` = multicast address of THIS rank's block), so it lands in every rank's copy as it is produced; the caller
+ * follows with dpfs_comm_barrier.  Replaces "write local block + all-gather kernel".  fp32 outputs stay local. */
+int dpfs_rmsnorm_fwd_mc(const float* x, const float* scale, void* y_mc, float* rstd /*nullable*/, int M, int D,
+                        float eps, cudaStream_t stream);
+int dpfs_add_rmsnorm_fwd_mc(const float* x, const void* y_bf16, const float* bias /*nullable*/, const float* scale,
+                            float* x_out, void* h_mc, float* rstd /*nullable*/, int M, int D, float eps,
+                            cudaStream_t stream);
+/* dy bf16, x fp32.  scratch: dpfs_norm_bwd_blocks(M) * D floats. */
+int dpfs_rmsnorm_bwd_mc(const void* dy_bf16, const float* x, const float* rstd, const float* scale,
+                        const float* dres /*nullable*/, float* dx /*nullable*/, void* dx_mc, float* dscale,
+                        int dscale_accumulate, float* scratch, int M, int D, cudaStream_t stream);
+int dpfs_cast_f32_to_bf16_mc(const float* x, void* y_mc, long long n, cudaStream_t stream);
 int dpfs_layernorm_fwd(const void* x, int x_bf16, const float* gamma, const float* beta /*nullable*/, void* y,
                        int y_bf16, float* mean, float* rstd, int M, int D, float eps, cudaStream_t stream);
 /* scratch: (dpfs_norm_bwd_blocks(M) + 1) * 2 * D floats. */

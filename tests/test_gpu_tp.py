@@ -88,6 +88,45 @@ def _fused_rs_worker(rank, world):
     symm.mode = "p2p"
 
 
+def _push_worker(rank, world):
+    """Producers that all-gather their bf16 output through the multicast mapping vs the same producers followed by the
+    stand-alone all-gather; several rounds so both landing zones are recycled."""
+    import os
+    os.environ["DPFS_FUSE_AG"] = "1"
+    import torch.distributed as dist
+    from distributed_pytorch_from_scratch_b200.ops import fused
+    from distributed_pytorch_from_scratch_b200.parallel.symm import try_enable_symm
+    symm = try_enable_symm(required=True)
+    if not symm.push_enabled:
+        return      # no NVLS multicast on this box: nothing to test
+    torch.manual_seed(300 + rank)
+    Ml, D = 1000, 512
+
+    def gather(t):
+        out = torch.empty((world * t.shape[0],) + tuple(t.shape[1:]), dtype=t.dtype, device=t.device)
+        dist.all_gather_into_tensor(out, t.contiguous())
+        return out
+
+    for rnd in range(5):
+        x = torch.randn(Ml, D, device="cuda")
+        y = torch.randn(Ml, D, device="cuda").to(torch.bfloat16)
+        bias, scale = torch.randn(D, device="cuda"), torch.rand(D, device="cuda") + 0.5
+        h_ref, rstd_ref = fused.rmsnorm_fwd(x, scale, 1e-5)
+        h, rstd = fused.rmsnorm_fwd_push(x, scale, 1e-5, symm)
+        assert torch.equal(h, gather(h_ref)) and torch.equal(rstd, rstd_ref), rnd
+        xo_ref, h2_ref, r2_ref = fused.add_rmsnorm_fwd(x, y, bias, scale, 1e-5)
+        xo, h2, r2 = fused.add_rmsnorm_fwd_push(x, y, bias, scale, 1e-5, symm)
+        assert torch.equal(xo, xo_ref) and torch.equal(h2, gather(h2_ref)) and torch.equal(r2, r2_ref), rnd
+        assert torch.equal(fused.cast_to_bf16_push(x, symm), gather(fused.cast_to_bf16(x))), rnd
+        dy, dres = torch.randn(Ml, D, device="cuda").to(torch.bfloat16), torch.randn(Ml, D, device="cuda")
+        ds_ref, ds = torch.empty(D, device="cuda"), torch.empty(D, device="cuda")
+        dx_ref, dxb_ref, _ = fused.rmsnorm_bwd(dy, x, rstd_ref, scale, dres=dres, want_fp32=True, want_bf16=True,
+                                               dscale_out=ds_ref)
+        dx, dxb = fused.rmsnorm_bwd_push(dy, x, rstd_ref, scale, dres, symm, dscale_out=ds)
+        assert torch.equal(dx, dx_ref) and torch.equal(dxb, gather(dxb_ref)) and torch.equal(ds, ds_ref), rnd
+    torch.cuda.synchronize()
+
+
 def _model_worker(rank, world, comm, sp=False):
     import process_manager as pm
     from distributed_pytorch_from_scratch_b200.engine import TrainStep
@@ -154,6 +193,14 @@ def test_symm_collectives_and_fused_gemm_allreduce():
                            "yet: set DPFS_TEST_EXPERIMENTAL=1 to include it")
 def test_fused_gemm_reduce_scatter():
     run_distributed(_fused_rs_worker, 2, free_port(), backend="nccl")
+
+
+@pytest.mark.skipif(_ngpu() < 2, reason="needs >= 2 GPUs")
+@pytest.mark.skipif(os.environ.get("DPFS_TEST_EXPERIMENTAL", "0") != "1",
+                    reason="pushed all-gathers are opt-in (DPFS_FUSE_AG=1) and have not been run on hardware yet: "
+                           "set DPFS_TEST_EXPERIMENTAL=1 to include them")
+def test_push_allgather_producers():
+    run_distributed(_push_worker, 2, free_port(), backend="nccl")
 
 
 @pytest.mark.skipif(_ngpu() < 2, reason="needs >= 2 GPUs")
