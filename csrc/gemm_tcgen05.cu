@@ -112,7 +112,9 @@ __device__ __forceinline__ void store_chunk32<__nv_bfloat16>(__nv_bfloat16* dst,
 // m_blk % n).  When its GEMM tiles are done, the CTA turns to the tiles its rank owns: as soon as all n partials of a
 // tile are flagged, it pulls their sum through the NVSwitch (multimem.ld_reduce) and broadcasts the result into every
 // rank's buffer (multimem.st).  A closing rank-wide barrier makes the full result visible before the kernel exits.
-template <int BN, bool A_MN, bool B_MN, typename OutT, bool FUSE_AR = false>
+// FUSE_RS (implies FUSE_AR): the reduce-scatter form -- rank r keeps only its rows of the sum (args.rs_out).  A separate
+// instantiation so that the all-reduce kernels stay exactly the binaries that were validated on hardware.
+template <int BN, bool A_MN, bool B_MN, typename OutT, bool FUSE_AR = false, bool FUSE_RS = false>
 __global__ void __launch_bounds__(FUSE_AR ? kGemmThreads + kCommThreads : kGemmThreads, 1)
 gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                  const GemmArgs args) {
@@ -137,9 +139,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   const int kb_total = (args.K + BK - 1) / BK;
   // work index -> tile id: identity, except for the fused reduce-scatter (see rs_block_of)
   auto tile_of = [&](int wt) -> int {
-    if constexpr (FUSE_AR) {
-      if (args.rs_out) return rs_block_of(wt / tiles_n, args.comm.n, args.rs_rows) * tiles_n + wt % tiles_n;
-    }
+    if constexpr (FUSE_RS) return rs_block_of(wt / tiles_n, args.comm.n, args.rs_rows) * tiles_n + wt % tiles_n;
     return wt;
   };
 
@@ -315,7 +315,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         if (threadIdx.x == 64 && !(args.debug & 1)) {
           const int m_blk = t / tiles_n;
           __threadfence_system();
-          if (args.rs_out) {
+          if constexpr (FUSE_RS) {
             const int o_lo = m0 / args.rs_rows;
             const int o_hi = (min(m0 + BM, args.M) - 1) / args.rs_rows;
             put_signal(args.comm.flags[o_lo] + (kMaxBlocks + t) * kMaxRanks + args.comm.rank);
@@ -335,7 +335,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       // every rank's buffer — while warps 0-5 of this CTA are still computing other tiles.
       const int ct = threadIdx.x - kGemmThreads;
       const int n = args.comm.n, rank = args.comm.rank;
-      if (args.rs_out) {
+      if constexpr (FUSE_RS) {
         // ---- reduce-scatter: the blocks that intersect this rank's rows, primary blocks in compute order first, the
         // leading straddler (primary owner rank - 1, computed in that owner's last round) last
         const int rpr = args.rs_rows;
@@ -505,10 +505,10 @@ static int launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const Gem
   return static_cast<int>(cudaGetLastError());
 }
 
-template <int BN, bool B_MN>
+template <int BN, bool B_MN, bool RS = false>
 static int launch_gemm_ar(const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmArgs& args, cudaStream_t stream) {
   using S = GemmSmem<BN>;
-  auto kfn = gemm_bf16_kernel<BN, false, B_MN, __nv_bfloat16, true>;
+  auto kfn = gemm_bf16_kernel<BN, false, B_MN, __nv_bfloat16, true, RS>;
   static bool configured = false;
   if (!configured) {
     cudaError_t e = cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, S::kTotal);
@@ -663,6 +663,13 @@ static int gemm_fused_collective(const void* A, long long lda, const void* B, lo
   for (int i = 0; i < kMaxRanks; ++i) args.comm.flags[i] = i < n ? reinterpret_cast<uint32_t*>(flag_ptrs[i]) : nullptr;
   args.comm.rank = rank;
   args.comm.n = n;
+  if (rs_out) {
+    if (bn == 256)
+      return b_mn_major ? launch_gemm_ar<256, true, true>(tmA, tmB, args, stream)
+                        : launch_gemm_ar<256, false, true>(tmA, tmB, args, stream);
+    return b_mn_major ? launch_gemm_ar<128, true, true>(tmA, tmB, args, stream)
+                      : launch_gemm_ar<128, false, true>(tmA, tmB, args, stream);
+  }
   if (bn == 256)
     return b_mn_major ? launch_gemm_ar<256, true>(tmA, tmB, args, stream)
                       : launch_gemm_ar<256, false>(tmA, tmB, args, stream);
