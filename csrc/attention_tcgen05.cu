@@ -26,7 +26,6 @@ namespace dpfs {
 
 int num_sms();
 
-constexpr int kAttnThreads = 192;
 constexpr int kAttnFwdThreads = 320;  // warp 0 TMA, warp 1 MMA, warps 2-9: two softmax warps per SM sub-partition
 constexpr int kAttnBwdThreads = 320;  // warp 0 TMA, warp 1 MMA, warps 2-9: two groups of 4 gradient-math warps
 constexpr int kTile = 128;  // q rows and kv rows per tile

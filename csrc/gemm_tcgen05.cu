@@ -53,10 +53,13 @@ struct GemmArgs {
 // owner's comm warps get finished tiles at an even rate from the start (with the natural order owner 0 would be served
 // first and owner n-1 would reduce its whole share after the GEMM).  A block that straddles two row ranges is flagged
 // to both owners.
-__device__ __forceinline__ int rs_first_blk(int o, int rs_rows) { return (o * rs_rows + BM - 1) / BM; }
-__device__ __forceinline__ int rs_block_of(int wb, int n, int rs_rows) {  // wb-th block in compute order -> m_blk
+__host__ __device__ __forceinline__ int rs_first_blk(int o, int rs_rows) { return (o * rs_rows + BM - 1) / BM; }
+__host__ __device__ __forceinline__ int rs_block_of(int wb, int n, int rs_rows) {  // wb-th block in compute order
   int cmin = 0x7fffffff;
-  for (int o = 0; o < n; ++o) cmin = min(cmin, rs_first_blk(o + 1, rs_rows) - rs_first_blk(o, rs_rows));
+  for (int o = 0; o < n; ++o) {
+    const int cnt = rs_first_blk(o + 1, rs_rows) - rs_first_blk(o, rs_rows);
+    cmin = cnt < cmin ? cnt : cmin;
+  }
   if (wb < cmin * n) return rs_first_blk(wb % n, rs_rows) + wb / n;
   int idx = wb - cmin * n;  // the owners that have one more block than the others, in rank order
   for (int o = 0; o < n; ++o) {
@@ -700,4 +703,18 @@ extern "C" int dpfs_gemm_reduce_scatter_bf16(const void* A, long long lda, const
   if (!rs_out) return -54;
   return gemm_fused_collective(A, lda, B, ldb, b_mn_major, partial, mc_partial, data_ptrs, partial_offset, rs_out, M,
                                N, K, flag_ptrs, rank, n, bn, stream);
+}
+
+// Host-side view of the fused reduce-scatter's schedule, for the CPU tests: order[i] = row-block computed i-th by every
+// rank (i < ceil(M / 128)); owner_lo / owner_hi[b] = the rank(s) whose comm warps are signalled when block b is done.
+extern "C" int dpfs_debug_rs_schedule(int M, int n, int* order, int* owner_lo, int* owner_hi) {
+  if (n < 1 || M <= 0 || M % n != 0 || M / n < BM) return -53;
+  const int rpr = M / n, tiles_m = (M + BM - 1) / BM;
+  for (int i = 0; i < tiles_m; ++i) order[i] = rs_block_of(i, n, rpr);
+  for (int b = 0; b < tiles_m; ++b) {
+    const int m0 = b * BM, m1 = (m0 + BM < M ? m0 + BM : M) - 1;
+    owner_lo[b] = m0 / rpr;
+    owner_hi[b] = m1 / rpr;
+  }
+  return 0;
 }
