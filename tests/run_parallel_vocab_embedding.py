@@ -1,4 +1,4 @@
-"""Script-style entry point with the reference's CLI (its tests/test_parallel_vocab_embedding.py is run as
+"""Script-style entry point with the reference's CLI (its tests/test_parallel_vocab_embedding.py:1-178 is run as
 `python tests/test_parallel_vocab_embedding.py --tp_size N`): spawns N ranks (gloo on CPU; the multi-GPU NCCL variants live in tests/test_gpu_tp.py) and runs the same
 assertions as the pytest suite.  Unlike the reference, a failing assertion makes the process exit non-zero."""
 import argparse

@@ -1,4 +1,4 @@
-"""Script-style entry point with the reference's CLI (its tests/test_transformers.py is run as
+"""Script-style entry point with the reference's CLI (its tests/test_transformers.py:1-145 is run as
 `python tests/test_transformers.py --tp_size N`): spawns N ranks (gloo on CPU; the multi-GPU NCCL variants live in tests/test_gpu_tp.py) and runs the same
 assertions as the pytest suite.  Unlike the reference, a failing assertion makes the process exit non-zero."""
 import argparse
