@@ -35,6 +35,29 @@ __global__ void embedding_fwd_kernel(const long long* __restrict__ ids, const fl
   }
 }
 
+// Vocab-parallel lookup fused with its collective (SURVEY K-c3 "vocab_embed_allreduce"): exactly one rank owns each
+// token's row, so the all-reduce of the masked lookups degenerates into a scatter.  The owner writes the bf16 row
+// through the NVLS multicast mapping of the output (it lands in every rank's copy); the other ranks write nothing and
+// nothing is summed.  The caller follows with a rank barrier.  out_mc: multicast address of the [M][D] bf16 output.
+__global__ void embedding_fwd_mc_kernel(const long long* __restrict__ ids, const float* __restrict__ weight,
+                                        __nv_bfloat16* __restrict__ out_mc, int M, int D, long long vocab_start,
+                                        long long vocab_end) {
+  const int vec = D / 4;
+  const long long total = static_cast<long long>(M) * vec;
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const int row = static_cast<int>(i / vec);
+    const int c = static_cast<int>(i % vec) * 4;
+    const long long id = ids[row];
+    if (id < vocab_start || id >= vocab_end) continue;   // another rank owns this token
+    const float4 v = *reinterpret_cast<const float4*>(weight + (id - vocab_start) * D + c);
+    asm volatile("multimem.st.relaxed.sys.global.v2.bf16x2 [%0], {%1, %2};" ::"l"(out_mc +
+                                                                                  static_cast<long long>(row) * D + c),
+                 "r"(pack_bf16(v.x, v.y)), "r"(pack_bf16(v.z, v.w))
+                 : "memory");
+  }
+}
+
 // dweight[ids[m] - vocab_start][:] += dout[m][:] for owned ids (dweight must be zeroed by the caller).
 __global__ void embedding_bwd_kernel(const long long* __restrict__ ids, const float* __restrict__ dout,
                                      float* __restrict__ dweight, int M, int D, long long vocab_start,
@@ -261,6 +284,16 @@ extern "C" int dpfs_embedding_fwd(const long long* ids, const float* weight, voi
   else
     embedding_fwd_kernel<float><<<(DPFS_COUNT(), ew_grid2(total, 256)), 256, 0, stream>>>(ids, weight, (float*)out, M, D, vocab_start,
                                                                          vocab_end);
+  return static_cast<int>(cudaGetLastError());
+}
+
+extern "C" int dpfs_embedding_fwd_mc(const long long* ids, const float* weight, void* out_mc, int M, int D,
+                                     long long vocab_start, long long vocab_end, cudaStream_t stream) {
+  if (D % 4 != 0) return -30;
+  if (M <= 0) return 0;
+  const long long total = static_cast<long long>(M) * (D / 4);
+  embedding_fwd_mc_kernel<<<(DPFS_COUNT(), ew_grid2(total, 256)), 256, 0, stream>>>(
+      ids, weight, reinterpret_cast<__nv_bfloat16*>(out_mc), M, D, vocab_start, vocab_end);
   return static_cast<int>(cudaGetLastError());
 }
 

@@ -276,7 +276,12 @@ class FusedEmbedFn(torch.autograd.Function):
             # output to bf16 before the first layer (models/model.py:153-154)
             symm = pm.pgm.symm
             D = weight.shape[1]
-            if symm is not None and ids_flat.numel() * D * 2 <= symm.ag_off:
+            if symm is not None and symm.push_enabled and ids_flat.numel() * D * 2 <= symm.push_zone_bytes \
+                    and (ids_flat.numel() * D * 2) % 16 == 0:
+                # opt-in (DPFS_FUSE_AG=1): owner-scatter through the multicast mapping, no reduction at all
+                out = fused.embedding_fwd_scatter(ids_flat, weight.detach(), emb.vocab_st_idx, emb.vocab_ed_idx,
+                                                  symm).float()
+            elif symm is not None and ids_flat.numel() * D * 2 <= symm.ag_off:
                 part = symm.buffer((ids_flat.numel(), D), BF16)
                 fused.embedding_fwd(ids_flat, weight.detach(), emb.vocab_st_idx, emb.vocab_ed_idx, out=part)
                 out = symm.all_reduce(part, out=part).float()

@@ -66,6 +66,7 @@ SIGS = {
     "dpfs_cast_f32_to_bf16": (c_p, c_p, c_ll, c_p),
     "dpfs_colsum_bf16_static": (c_p, c_ll, c_p, c_int, c_int, c_int, c_p),
     "dpfs_embedding_fwd": (c_p, c_p, c_p, c_int, c_int, c_int, c_ll, c_ll, c_p),
+    "dpfs_embedding_fwd_mc": (c_p, c_p, c_p, c_int, c_int, c_ll, c_ll, c_p),
     "dpfs_embedding_bwd": (c_p, c_p, c_p, c_int, c_ll, c_int, c_int, c_ll, c_ll, c_p),
     "dpfs_ce_stats": (c_p, c_int, c_ll, c_p, c_p, c_p, c_int, c_int, c_ll, c_ll, c_p),
     "dpfs_ce_loss": (c_p, c_p, c_int, c_p, c_p, c_int, c_ll, c_p),

@@ -148,6 +148,19 @@ def rmsnorm_bwd_push(dy_l: torch.Tensor, x_l: torch.Tensor, rstd: torch.Tensor, 
     return dx, full
 
 
+def embedding_fwd_scatter(ids_flat: torch.Tensor, weight: torch.Tensor, vocab_start: int, vocab_end: int, symm):
+    """Vocab-parallel embedding + its collective in one kernel: the owner of each token writes the bf16 row into every
+    rank's copy of the output (multicast store), nobody sums anything.  Returns the [M, D] bf16 view (landing zone)."""
+    M, D = ids_flat.numel(), weight.shape[1]
+    assert ids_flat.dtype == torch.int64 and ids_flat.is_contiguous() and weight.dtype == F32
+    mc, out = symm.push_zone(M, D)
+    rc = _lib.lib().dpfs_embedding_fwd_mc(ids_flat.data_ptr(), weight.data_ptr(), mc, M, D, vocab_start, vocab_end,
+                                          _lib.stream())
+    _lib.check(rc, "dpfs_embedding_fwd_mc")
+    symm.push_done()
+    return out
+
+
 def cast_to_bf16_push(x_l: torch.Tensor, symm) -> torch.Tensor:
     """bf16(x_l) pushed to every rank: [Ml, D] fp32 -> gathered [n * Ml, D] bf16."""
     Ml, D = x_l.shape

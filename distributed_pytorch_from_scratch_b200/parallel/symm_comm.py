@@ -257,6 +257,16 @@ class SymmComm:
         view = self.data[off:off + nbytes * self.n].view(dtype).view(self.n * block_rows, cols)
         return self.mc_base + off + self.rank * nbytes, view
 
+    def push_zone(self, rows: int, cols: int, dtype=BF16):
+        """Like push_block but for producers that address the whole [rows, cols] zone themselves (the vocab-parallel
+        embedding scatters token rows): returns (multicast address of the zone, view of this rank's copy)."""
+        esz = torch.empty((), dtype=dtype).element_size()
+        nbytes = rows * cols * esz
+        assert self.push_enabled and nbytes % 16 == 0 and nbytes <= self.push_zone_bytes
+        self._push_zone ^= 1
+        off = self.push_off + self._push_zone * self.push_zone_bytes
+        return self.mc_base + off, self.data[off:off + nbytes].view(dtype).view(rows, cols)
+
     def push_done(self):
         """Rank-wide barrier after a pushed all-gather: every rank's block is complete and visible."""
         self.barrier()

@@ -203,6 +203,11 @@ int dpfs_colsum_bf16_static(const void* x, long long ld, float* out, int accumul
  * ref: ParallelVocabularyEmbedding.forward, models/layers.py:134-141. */
 int dpfs_embedding_fwd(const long long* ids, const float* weight, void* out, int out_bf16, int M, int D,
                        long long vocab_start, long long vocab_end, cudaStream_t stream);
+/* Vocab-parallel lookup + its collective in one kernel (SURVEY K-c3): the rank that owns a token's row writes it (bf16)
+ * through the multicast address out_mc of the [M][D] output, the others write nothing; follow with dpfs_comm_barrier.
+ * ref: ParallelVocabularyEmbedding.forward + Reduce (models/layers.py:134-141). */
+int dpfs_embedding_fwd_mc(const long long* ids, const float* weight, void* out_mc, int M, int D, long long vocab_start,
+                          long long vocab_end, cudaStream_t stream);
 int dpfs_embedding_bwd(const long long* ids, const float* dout, float* dweight, int zero_first,
                        long long local_vocab, int M, int D, long long vocab_start, long long vocab_end,
                        cudaStream_t stream);

@@ -124,6 +124,14 @@ def _push_worker(rank, world):
                                                dscale_out=ds_ref)
         dx, dxb = fused.rmsnorm_bwd_push(dy, x, rstd_ref, scale, dres, symm, dscale_out=ds)
         assert torch.equal(dx, dx_ref) and torch.equal(dxb, gather(dxb_ref)) and torch.equal(ds, ds_ref), rnd
+        # vocab-parallel embedding: owner-scatter == masked lookup + all-reduce (exact: one owner per token)
+        V, Vl = 1024, 1024 // world
+        w = torch.randn(Vl, D, device="cuda")
+        ids = torch.randint(0, V, (Ml * 2,), device="cuda")
+        dist.broadcast(ids, 0)
+        part = fused.embedding_fwd(ids, w, rank * Vl, (rank + 1) * Vl, out_dtype=torch.bfloat16)
+        dist.all_reduce(part)
+        assert torch.equal(fused.embedding_fwd_scatter(ids, w, rank * Vl, (rank + 1) * Vl, symm), part), rnd
     torch.cuda.synchronize()
 
 
