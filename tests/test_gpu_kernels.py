@@ -13,7 +13,9 @@ def _bf(x):
 
 
 @pytest.mark.parametrize("a_mn,b_mn", [(False, False), (False, True), (True, True), (True, False)])
-@pytest.mark.parametrize("shape", [(128, 128, 64), (1000, 512, 512), (520, 264, 200), (4096, 1536, 512)])
+# K <= 1024 runs the 8-epilogue-warp shape of the 2-SM kernel, K = 2048 the 4-warp / 6-stage one
+@pytest.mark.parametrize("shape", [(128, 128, 64), (1000, 512, 512), (520, 264, 200), (4096, 1536, 512),
+                                   (640, 512, 2048)])
 def test_gemm_tcgen05(a_mn, b_mn, shape):
     from distributed_pytorch_from_scratch_b200.ops.gemm import gemm_nt
     M, N, K = shape
