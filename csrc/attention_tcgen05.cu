@@ -22,6 +22,8 @@
 #include <cudaTypedefs.h>
 #include <stdlib.h>
 
+#include <type_traits>
+
 namespace dpfs {
 
 int num_sms();
@@ -776,7 +778,10 @@ attn_fwd_pp_kernel(const __grid_constant__ CUtensorMap tm_qkv, __nv_bfloat16* __
       if (qt >= nq) continue;   // odd number of q tiles: the last pair has no tile B
       const int q0 = qt * kTile;
       float m_run = -INFINITY, l_run = 0.f;
-      for (int j = 0; j <= qt; ++j, ++cnt) {
+      // One kv tile.  DIAG (the causal diagonal tile, the last one of the item) is a compile-time flag so that the
+      // 127 other tiles of a long row do not pay per-element mask predicates.
+      auto kv_step = [&](int j, auto diag_tag) {
+        constexpr bool DIAG = decltype(diag_tag)::value;
         mbar_wait(&s_full[x], cnt & 1);
         tc_fence_after();
         // pass 1: row max over the 128 columns (two TMEM loads in flight)
@@ -787,16 +792,17 @@ attn_fwd_pp_kernel(const __grid_constant__ CUtensorMap tm_qkv, __nv_bfloat16* __
           tmem_ld32(tS + lane_off + (2 * c2) * 32, t0);
           tmem_ld32(tS + lane_off + (2 * c2 + 1) * 32, t1);
           tmem_ld_wait();
+          if constexpr (DIAG) {   // causal mask, also hides kv columns past T
+#pragma unroll
+            for (int i = 0; i < 32; ++i) {
+              if ((2 * c2) * 32 + i > r) t0[i] = 0xff800000u;       // -inf
+              if ((2 * c2 + 1) * 32 + i > r) t1[i] = 0xff800000u;
+            }
+          }
           float m4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
 #pragma unroll
-          for (int i = 0; i < 32; ++i) {
-            float a = __uint_as_float(t0[i]), bb = __uint_as_float(t1[i]);
-            if (j == qt) {   // diagonal tile: causal mask (also hides kv columns past T)
-              if ((2 * c2) * 32 + i > r) a = -INFINITY;
-              if ((2 * c2 + 1) * 32 + i > r) bb = -INFINITY;
-            }
-            m4[i & 3] = fmaxf(m4[i & 3], fmaxf(a, bb));
-          }
+          for (int i = 0; i < 32; ++i)
+            m4[i & 3] = fmaxf(m4[i & 3], fmaxf(__uint_as_float(t0[i]), __uint_as_float(t1[i])));
           mloc = fmaxf(mloc, fmaxf(fmaxf(m4[0], m4[1]), fmaxf(m4[2], m4[3])));
         }
         mloc *= scale_log2;   // scale > 0: max commutes with the scaling
@@ -821,32 +827,41 @@ attn_fwd_pp_kernel(const __grid_constant__ CUtensorMap tm_qkv, __nv_bfloat16* __
         }
         // pass 2: p = exp2(s * scale - m) -> bf16 P tile in smem, row sum
         float s4[4] = {0.f, 0.f, 0.f, 0.f};
+        auto emit_chunk = [&](int c, uint32_t (&tv)[32]) {
+          if constexpr (DIAG) {   // masked scores become -inf: exp2 gives an exact 0
 #pragma unroll
-        for (int c = 0; c < 4; ++c) {
-          uint32_t tv[32];
-          tmem_ld32(tS + lane_off + c * 32, tv);
-          tmem_ld_wait();
+            for (int i = 0; i < 32; ++i)
+              if (c * 32 + i > r) tv[i] = 0xff800000u;
+          }
           uint32_t packed[16];
 #pragma unroll
           for (int i = 0; i < 32; i += 2) {
-            float p0 = fast_exp2(__uint_as_float(tv[i]) * scale_log2 - mx);
-            float p1 = fast_exp2(__uint_as_float(tv[i + 1]) * scale_log2 - mx);
-            if (j == qt) {
-              if (c * 32 + i > r) p0 = 0.f;
-              if (c * 32 + i + 1 > r) p1 = 0.f;
-            }
+            const float p0 = fast_exp2(__uint_as_float(tv[i]) * scale_log2 - mx);
+            const float p1 = fast_exp2(__uint_as_float(tv[i + 1]) * scale_log2 - mx);
             s4[i & 3] += p0;
             s4[(i + 1) & 3] += p1;
             packed[i >> 1] = pack_bf16(p0, p1);
           }
           st_tile_row32(sPx, r, c * 32, packed);
+        };
+#pragma unroll 1
+        for (int c2 = 0; c2 < 2; ++c2) {   // two TMEM loads in flight, like pass 1
+          uint32_t ta[32], tb[32];
+          tmem_ld32(tS + lane_off + (2 * c2) * 32, ta);
+          tmem_ld32(tS + lane_off + (2 * c2 + 1) * 32, tb);
+          tmem_ld_wait();
+          emit_chunk(2 * c2, ta);
+          emit_chunk(2 * c2 + 1, tb);
         }
         l_run = l_run * alpha + ((s4[0] + s4[1]) + (s4[2] + s4[3]));
         fence_proxy_async_smem();
         tc_fence_before();
         __syncwarp();
         if (lane == 0) mbar_arrive(&p_full[x]);
-      }
+      };
+      for (int j = 0; j < qt; ++j, ++cnt) kv_step(j, std::false_type{});
+      kv_step(qt, std::true_type{});
+      ++cnt;
       // item epilogue for this group's tile
       mbar_wait(&o_done[x], (cnt - 1) & 1);
       tc_fence_after();
