@@ -1188,7 +1188,10 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
   }
 }
 
-template <int HD>
+// V2 (opt-in, DPFS_ATTN_BWD_V2=1): the per-element causal / row-validity predicates of the P, dS computation are paid
+// only on the diagonal tile (compile-time flag per step) and rows past T get lse = +inf (p = exp2(-inf) = 0) instead
+// of a select per element -- about a quarter fewer instructions per element for the math warps.
+template <int HD, bool V2 = false>
 __global__ void __launch_bounds__(kAttnBwdThreads, 1)
 attn_bwd_persistent_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constant__ CUtensorMap tm_do,
                 const __grid_constant__ CUtensorMap tm_dq, const __grid_constant__ CUtensorMap tm_dkv,
@@ -1338,7 +1341,7 @@ attn_bwd_persistent_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __g
     auto load_stats = [&](int w, int it, float& l2, float& dl) {
       const int jt_ = w / HB, rem_ = w % HB;
       const int row = (jt_ + it) * kTile + r;
-      l2 = 0.f;
+      l2 = V2 ? INFINITY : 0.f;
       dl = 0.f;
       if (w < n_items && row < T) {
         const long long idx = (static_cast<long long>(rem_ / H) * H + rem_ % H) * T + row;
@@ -1358,6 +1361,36 @@ attn_bwd_persistent_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __g
       const float lse2 = lse2_nx, dlt = dlt_nx;
       mbar_wait(sdp_full, gs & 1);
       tc_fence_after();
+      if constexpr (V2) {
+        auto chunks = [&](auto diag_tag) {
+          constexpr bool DIAG = decltype(diag_tag)::value;
+#pragma unroll 1
+          for (int c = 2 * half; c < 2 * half + 2; ++c) {
+            uint32_t sv[32], dv[32];
+            tmem_ld32(tS + lane_off + c * 32, sv);
+            tmem_ld32(tDP + lane_off + c * 32, dv);
+            tmem_ld_wait();
+            if constexpr (DIAG) {   // causal mask: a masked score becomes -inf, so p and dS come out as exact zeros
+#pragma unroll
+              for (int i = 0; i < 32; ++i)
+                if (c * 32 + i > r) sv[i] = 0xff800000u;
+            }
+            uint32_t pp[16], dd[16];
+#pragma unroll
+            for (int i = 0; i < 32; i += 2) {
+              const float p0 = fast_exp2(__uint_as_float(sv[i]) * scale_log2 - lse2);
+              const float p1 = fast_exp2(__uint_as_float(sv[i + 1]) * scale_log2 - lse2);
+              const float d0 = p0 * (__uint_as_float(dv[i]) - dlt) * scale;
+              const float d1 = p1 * (__uint_as_float(dv[i + 1]) - dlt) * scale;
+              pp[i >> 1] = pack_bf16(p0, p1);
+              dd[i >> 1] = pack_bf16(d0, d1);
+            }
+            st_tile_row32(sP, r, c * 32, pp);
+            st_tile_row32(sDS, r, c * 32, dd);
+          }
+        };
+        if (it == 0) chunks(std::true_type{}); else chunks(std::false_type{});
+      } else {
 #pragma unroll 1
       for (int c = 2 * half; c < 2 * half + 2; ++c) {
         uint32_t sv[32], dv[32];
@@ -1379,6 +1412,7 @@ attn_bwd_persistent_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __g
         }
         st_tile_row32(sP, r, c * 32, pp);
         st_tile_row32(sDS, r, c * 32, dd);
+      }
       }
       fence_proxy_async_smem();
       tc_fence_before();
@@ -1584,12 +1618,12 @@ static int launch_bwd(const CUtensorMap& tm_qkv, const CUtensorMap& tm_do, const
   return static_cast<int>(cudaGetLastError());
 }
 
-template <int HD>
+template <int HD, bool V2 = false>
 static int launch_bwd_persistent(const CUtensorMap& tm_qkv, const CUtensorMap& tm_do, const CUtensorMap& tm_dq,
                                  const CUtensorMap& tm_dkv,                                 const float* lse, const float* delta, void* dqkv, int B, int T, int H, float scale,
                                  cudaStream_t stream) {
   using C = BwdCfg<HD>;
-  auto kfn = attn_bwd_persistent_kernel<HD>;
+  auto kfn = attn_bwd_persistent_kernel<HD, V2>;
   static bool configured = false;
   if (!configured) {
     cudaError_t e = cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmemPersistent);
@@ -1667,9 +1701,20 @@ extern "C" int dpfs_attn_bwd(const void* qkv, const void* out, const void* d_out
     CUtensorMap tm_dkv;
     rc = make_tmap_dkv(&tm_dkv, dqkv, 3 * Dl, T, B);
     if (rc) return rc;
-    rc = HD == 64
-             ? launch_bwd_persistent<64>(tm_qkv, tm_do, tm_dq, tm_dkv, lse, delta, dqkv, B, T, H, scale, stream)
-             : launch_bwd_persistent<128>(tm_qkv, tm_do, tm_dq, tm_dkv, lse, delta, dqkv, B, T, H, scale, stream);
+    static int v2 = -1;
+    if (v2 < 0) {
+      const char* e = getenv("DPFS_ATTN_BWD_V2");
+      v2 = e ? atoi(e) : 0;
+    }
+    if (v2)
+      rc = HD == 64 ? launch_bwd_persistent<64, true>(tm_qkv, tm_do, tm_dq, tm_dkv, lse, delta, dqkv, B, T, H, scale,
+                                                      stream)
+                    : launch_bwd_persistent<128, true>(tm_qkv, tm_do, tm_dq, tm_dkv, lse, delta, dqkv, B, T, H, scale,
+                                                       stream);
+    else
+      rc = HD == 64
+               ? launch_bwd_persistent<64>(tm_qkv, tm_do, tm_dq, tm_dkv, lse, delta, dqkv, B, T, H, scale, stream)
+               : launch_bwd_persistent<128>(tm_qkv, tm_do, tm_dq, tm_dkv, lse, delta, dqkv, B, T, H, scale, stream);
   } else
     rc = HD == 64 ? launch_bwd<64>(tm_qkv, tm_do, lse, delta, dq_acc, dqkv, B, T, H, scale, stream)
                   : launch_bwd<128>(tm_qkv, tm_do, lse, delta, dq_acc, dqkv, B, T, H, scale, stream);
