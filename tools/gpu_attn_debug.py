@@ -1,4 +1,11 @@
-"""GPU bring-up for the tcgen05 flash attention (fwd + bwd) against an fp32 PyTorch oracle."""
+"""GPU bring-up for the tcgen05 flash attention (fwd + bwd) against an fp32 PyTorch oracle.
+
+The kernel variant is picked by the library from the environment (read once per process), so the opt-in kernels are
+checked and timed with the same script:
+    DPFS_ATTN_PERSISTENT=0 python tools/gpu_attn_debug.py        # one-CTA-per-tile kernels
+    DPFS_ATTN_FWD_PP=1     python tools/gpu_attn_debug.py fwd    # ping-pong forward (hd = 64)
+    DPFS_ATTN_BWD_V2=1     python tools/gpu_attn_debug.py bwd    # backward with the lighter math path
+"""
 import os
 import subprocess
 import sys
