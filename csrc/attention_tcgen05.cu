@@ -40,6 +40,41 @@ __device__ __forceinline__ float fast_exp2(float x) {
   return y;
 }
 
+// ---- work-item order of the persistent kernels ------------------------------------------------------------------------
+// Items are sorted heavy-first.  Round-robin (CTA b takes items b, b + G, b + 2G, ...) always hands CTA 0 the heaviest
+// item of every round; with few rounds (TP = 8: 256 items on 148 CTAs) the makespan is 12 tile-steps where 8 would do.
+// The "snake" order reverses every other round -- CTA b takes position G-1-b of the odd rounds -- so the CTAs that got
+// the heaviest items of one round get the lightest of the next (LPT-like).  Only the last round can be partial, and a
+// CTA whose position there is past the end has no later item either, so "w >= n_items" still ends the loop.
+__host__ __device__ __forceinline__ int snake_item(int k, int bid, int G) {
+  return k * G + ((k & 1) ? (G - 1 - bid) : bid);
+}
+// k-th item of this CTA given the previous one (SNAKE = false: the plain round-robin of the validated kernels)
+template <bool SNAKE>
+__device__ __forceinline__ int item_w(int k, int w_prev) {
+  if constexpr (SNAKE) return snake_item(k, static_cast<int>(blockIdx.x), static_cast<int>(gridDim.x));
+  else return w_prev + static_cast<int>(gridDim.x);
+}
+
+// the item sequence of one CTA as a loop variable: SNAKE = false is literally "w = blockIdx.x; w += gridDim.x"
+template <bool SNAKE>
+struct ItemWalk {
+  int w, k;
+  __device__ __forceinline__ ItemWalk() : w(static_cast<int>(blockIdx.x)), k(0) {}
+  __device__ __forceinline__ void next() {
+    if constexpr (SNAKE) {
+      ++k;
+      w = snake_item(k, static_cast<int>(blockIdx.x), static_cast<int>(gridDim.x));
+    } else {
+      w += gridDim.x;
+    }
+  }
+  __device__ __forceinline__ int peek() const {   // the item after the current one (may be >= n_items)
+    if constexpr (SNAKE) return snake_item(k + 1, static_cast<int>(blockIdx.x), static_cast<int>(gridDim.x));
+    else return w + gridDim.x;
+  }
+};
+
 // K-major SW128 operand [rows][cols] made of 64-column atoms (each atom = rows x 128 B, atoms `atom_bytes` apart):
 // descriptor for the 16-wide K slice kk.
 __device__ __forceinline__ uint64_t desc_kmajor(uint32_t base, int kk, uint32_t atom_bytes) {
@@ -680,7 +715,7 @@ attn_fwd_pp_kernel(const __grid_constant__ CUtensorMap tm_qkv, __nv_bfloat16* __
   if (warp == 0) {
     if (lane == 0) {
       int g = 0, it = 0;
-      for (int w = blockIdx.x; w < n_items; w += gridDim.x, ++it) {
+      for (int k_ = 0, w = blockIdx.x; w < n_items; ++k_, w = item_w<true>(k_, w), ++it) {
         const int pair = n_pairs - 1 - w / HB, rem = w % HB, h = rem % H, b = rem / H;
         const bool has_b = 2 * pair + 1 < nq;
         const int n_kv = has_b ? 2 * pair + 2 : 2 * pair + 1;
@@ -706,7 +741,7 @@ attn_fwd_pp_kernel(const __grid_constant__ CUtensorMap tm_qkv, __nv_bfloat16* __
       constexpr uint32_t idesc_o = make_idesc_bf16(kTile, HD, false, true);
       int g = 0, it = 0;
       int cnt_a = 0, cnt_b = 0;   // steps issued so far per tile slot (phase of s_full / p_full / o_done)
-      for (int w = blockIdx.x; w < n_items; w += gridDim.x, ++it) {
+      for (int k_ = 0, w = blockIdx.x; w < n_items; ++k_, w = item_w<true>(k_, w), ++it) {
         const int pair = n_pairs - 1 - w / HB;
         const bool has_b = 2 * pair + 1 < nq;
         const int n_kv = has_b ? 2 * pair + 2 : 2 * pair + 1;
@@ -772,7 +807,7 @@ attn_fwd_pp_kernel(const __grid_constant__ CUtensorMap tm_qkv, __nv_bfloat16* __
     const uint32_t tS = tmem_base + x * 128, tO = tmem_base + 256 + x * HD;
     uint8_t* sPx = sP + x * C::kPBytes;
     int cnt = 0;   // steps done by this group (phase of s_full / p_full / o_done of slot x)
-    for (int w = blockIdx.x; w < n_items; w += gridDim.x) {
+    for (int k_ = 0, w = blockIdx.x; w < n_items; ++k_, w = item_w<true>(k_, w)) {
       const int pair = n_pairs - 1 - w / HB, rem = w % HB, h = rem % H, b = rem / H;
       const int qt = 2 * pair + x;
       if (qt >= nq) continue;   // odd number of q tiles: the last pair has no tile B
@@ -1253,7 +1288,8 @@ attn_bwd_persistent_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __g
   if (warp == 0) {
     if (lane == 0) {
       int gs = 0, item = 0;
-      for (int w = blockIdx.x; w < n_items; w += gridDim.x, ++item) {
+      for (ItemWalk<V2> iw_; iw_.w < n_items; iw_.next(), ++item) {
+      const int w = iw_.w;
         const int jt = w / HB, rem = w % HB, h = rem % H, b = rem / H;
         const int kv0 = jt * kTile, n_it = nq - jt;
         const int kb = item % C::kKvBufs;
@@ -1287,7 +1323,8 @@ attn_bwd_persistent_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __g
       const uint32_t p_base = smem_u32(sP), ds_base = smem_u32(sDS);
       constexpr uint32_t kAtom = kTile * 128;
       int gs = 0, item = 0;
-      for (int w = blockIdx.x; w < n_items; w += gridDim.x, ++item) {
+      for (ItemWalk<V2> iw_; iw_.w < n_items; iw_.next(), ++item) {
+      const int w = iw_.w;
         const int n_it = nq - w / HB;
         const int kb = item % C::kKvBufs;
         const uint32_t k_base = smem_u32(sKV + kb * 2 * C::kTileBytes), v_base = k_base + C::kTileBytes;
@@ -1352,7 +1389,8 @@ attn_bwd_persistent_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __g
     int gs = 0, item = 0;
     float lse2_nx, dlt_nx;
     load_stats(blockIdx.x, 0, lse2_nx, dlt_nx);
-    for (int w = blockIdx.x; w < n_items; w += gridDim.x, ++item) {
+    for (ItemWalk<V2> iw_; iw_.w < n_items; iw_.next(), ++item) {
+      const int w = iw_.w;
     const int jt = w / HB, rem = w % HB, h = rem % H, b = rem / H;
     const int kv0 = jt * kTile, n_it = nq - jt;
     for (int it = 0; it < n_it; ++it, ++gs) {
@@ -1419,7 +1457,7 @@ attn_bwd_persistent_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __g
       __syncwarp();
       if (lane == 0) mbar_arrive(pds_full);
       if (it + 1 < n_it) load_stats(w, it + 1, lse2_nx, dlt_nx);
-      else load_stats(w + gridDim.x, 0, lse2_nx, dlt_nx);
+      else load_stats(iw_.peek(), 0, lse2_nx, dlt_nx);
       // dQ tile -> this warp's smem slab -> one TMA reduce-add per 32x32 fp32 block (rows past T are clipped by the
       // tensor map); the L2 does the accumulation in 128-byte lines while the warp goes on with the next tile
       mbar_wait(dq_full, gs & 1);
@@ -1727,4 +1765,15 @@ extern "C" int dpfs_attn_bwd(const void* qkv, const void* out, const void* d_out
         dq_acc, reinterpret_cast<__nv_bfloat16*>(dqkv), M, Dl);
   }
   return static_cast<int>(cudaGetLastError());
+}
+
+// Host-side view of the persistent kernels' work distribution, for the CPU tests: the items CTA `bid` of `grid`
+// processes, in order (snake != 0: the reversed-odd-rounds order of the opt-in kernels).  Returns the count.
+extern "C" int dpfs_debug_attn_items(int n_items, int grid, int bid, int snake, int* out, int cap) {
+  int n = 0;
+  for (int k = 0, w = bid; w < n_items; ++k, w = snake ? dpfs::snake_item(k, bid, grid) : w + grid) {
+    if (n < cap) out[n] = w;
+    ++n;
+  }
+  return n;
 }

@@ -32,6 +32,7 @@ SIGS = {
     "dpfs_gemm_reduce_scatter_bf16": (c_p, c_ll, c_p, c_ll, c_int, c_p, c_p, c_p, c_ll, c_p, c_int, c_int, c_int, c_p,
                                       c_int, c_int, c_int, c_p),
     "dpfs_debug_rs_schedule": (c_int, c_int, c_p, c_p, c_p),
+    "dpfs_debug_attn_items": (c_int, c_int, c_int, c_int, c_p, c_int),
     "dpfs_allreduce_p2p": (c_p, c_ll, c_ll, c_int, c_p, c_int, c_int, c_p),
     "dpfs_comm_flag_words": (),
     "dpfs_allreduce_nvls": (c_p, c_ll, c_int, c_p, c_int, c_int, c_p),

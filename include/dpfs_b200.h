@@ -62,6 +62,10 @@ int dpfs_gemm_reduce_scatter_bf16(const void* A, long long lda, const void* B, l
                                   long long partial_offset, void* rs_out, int M, int N, int K,
                                   const unsigned long long* flag_ptrs, int rank, int n, int bn, cudaStream_t stream);
 
+/* Host-only (no GPU): the work items (heavy-first list positions) CTA `bid` of `grid` persistent attention CTAs
+ * processes, in order; snake != 0 = the reversed-odd-rounds order of the opt-in kernels.  Returns the count. */
+int dpfs_debug_attn_items(int n_items, int grid, int bid, int snake, int* out, int cap);
+
 /* Host-only (no GPU): the fused reduce-scatter's schedule for M rows over n ranks -- order[i] = row-block computed
  * i-th, owner_lo/hi[b] = ranks signalled when block b completes (arrays of ceil(M/128) ints).  For the CPU tests. */
 int dpfs_debug_rs_schedule(int M, int n, int* order, int* owner_lo, int* owner_hi);
