@@ -1251,6 +1251,13 @@ attn_bwd_persistent_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __g
   uint64_t* s_free = bars + 9;
   uint64_t* kv_empty = bars + 10;  // [2]
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 12);
+  uint64_t* sdp_read = bars + 13;  // kLook only: the math warps have read S / dP of the current step out of TMEM
+  // V2, hd = 64 (private dQ columns, two K/V buffers): S / dP of step g+1 are issued as soon as the math warps have
+  // READ S / dP of step g, i.e. while they are still computing P / dS(g) -- instead of queueing behind dQ / dV / dK(g).
+  // The math warps then find S / dP(g+1) complete when they come back from the dQ drain.  Because S / dP(g+1) no longer
+  // orders dV / dK(g) before the next step's math, the math warps wait for the Q/dO stage release of step g (committed
+  // after dV / dK(g)) before they overwrite P / dS.
+  constexpr bool kLook = V2 && !C::kDqAliasesS && C::kKvBufs == 2;
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int nq = (T + kTile - 1) / kTile;
@@ -1272,6 +1279,7 @@ attn_bwd_persistent_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __g
     mbar_init(pds_full, 8);
     mbar_init(dq_full, 1);
     mbar_init(s_free, 8);
+    if constexpr (kLook) mbar_init(sdp_read, 8);
     fence_mbar_init();
   }
   if (warp == 1) {
@@ -1322,6 +1330,74 @@ attn_bwd_persistent_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __g
       constexpr uint32_t idesc_q = make_idesc_bf16(kTile, HD, false, true);       // dQ
       const uint32_t p_base = smem_u32(sP), ds_base = smem_u32(sDS);
       constexpr uint32_t kAtom = kTile * 128;
+      if constexpr (kLook) {
+        int gs = 0, item = 0;
+        auto kbase = [&](int it_) { return smem_u32(sKV + (it_ % C::kKvBufs) * 2 * C::kTileBytes); };
+        // S(g) = Q K^T and dP(g) = dO V^T for global step g, K / V of the item it belongs to
+        auto issue_sdp = [&](int g, uint32_t k_base, uint32_t v_base) {
+          const int st = g % C::kStages;
+          const uint32_t q_base = smem_u32(sQ + st * C::kTileBytes), do_base = smem_u32(sDO + st * C::kTileBytes);
+          mbar_wait(&qdo_full[st], (g / C::kStages) & 1);
+          tc_fence_after();
+#pragma unroll
+          for (int kk = 0; kk < HD / 16; ++kk)
+            umma_bf16_ss(tS, desc_kmajor(q_base, kk, kAtom), desc_kmajor(k_base, kk, kAtom), idesc_s, kk > 0);
+#pragma unroll
+          for (int kk = 0; kk < HD / 16; ++kk)
+            umma_bf16_ss(tDP, desc_kmajor(do_base, kk, kAtom), desc_kmajor(v_base, kk, kAtom), idesc_s, kk > 0);
+          umma_commit(sdp_full);
+        };
+        ItemWalk<V2> iw_;
+        if (iw_.w < n_items) {
+          mbar_wait(&kv_full[0], 0);
+          issue_sdp(0, kbase(0), kbase(0) + C::kTileBytes);
+        }
+        for (; iw_.w < n_items; iw_.next(), ++item) {
+          const int w = iw_.w;
+          const int n_it = nq - w / HB;
+          const int kb = item % C::kKvBufs;
+          const uint32_t k_base = kbase(item), v_base = k_base + C::kTileBytes;
+          for (int it = 0; it < n_it; ++it, ++gs) {
+            const int st = gs % C::kStages;
+            const uint32_t q_base = smem_u32(sQ + st * C::kTileBytes), do_base = smem_u32(sDO + st * C::kTileBytes);
+            // look ahead: S / dP of the next step (of this item, or the first step of this CTA's next item)
+            bool has_next = true;
+            uint32_t nk = k_base;
+            if (it + 1 == n_it) {
+              has_next = iw_.peek() < n_items;
+              if (has_next) {
+                mbar_wait(&kv_full[(item + 1) % C::kKvBufs], ((item + 1) / C::kKvBufs) & 1);
+                nk = kbase(item + 1);
+              }
+            }
+            if (has_next) {
+              mbar_wait(sdp_read, gs & 1);   // S / dP(gs) are in the math warps' registers
+              tc_fence_after();
+              issue_sdp(gs + 1, nk, nk + C::kTileBytes);
+            }
+            mbar_wait(pds_full, gs & 1);
+            tc_fence_after();
+            if (gs > 0) {
+              mbar_wait(s_free, (gs - 1) & 1);   // previous dQ tile drained out of its own columns
+              tc_fence_after();
+            }
+#pragma unroll
+            for (int kk = 0; kk < kTile / 16; ++kk)  // dQ = dS K   (reduction over the 128 kv rows)
+              umma_bf16_ss(tDQ, desc_kmajor(ds_base, kk, kAtom), desc_mnmajor(k_base, kk, kAtom), idesc_q, kk > 0);
+            umma_commit(dq_full);
+#pragma unroll
+            for (int kk = 0; kk < kTile / 16; ++kk)  // dV += P^T dO   (reduction over the 128 q rows)
+              umma_bf16_ss(tDV, desc_mnmajor(p_base, kk, kAtom), desc_mnmajor(do_base, kk, kAtom), idesc_kv,
+                           (it > 0 || kk > 0) ? 1u : 0u);
+#pragma unroll
+            for (int kk = 0; kk < kTile / 16; ++kk)  // dK += dS^T Q
+              umma_bf16_ss(tDK, desc_mnmajor(ds_base, kk, kAtom), desc_mnmajor(q_base, kk, kAtom), idesc_kv,
+                           (it > 0 || kk > 0) ? 1u : 0u);
+            umma_commit(&qdo_empty[st]);   // also tells the math warps that P / dS(gs) have been consumed
+          }
+          umma_commit(&kv_empty[kb]);   // K / V of this item are no longer read
+        }
+      } else {
       int gs = 0, item = 0;
       for (ItemWalk<V2> iw_; iw_.w < n_items; iw_.next(), ++item) {
       const int w = iw_.w;
@@ -1364,6 +1440,7 @@ attn_bwd_persistent_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __g
           umma_commit(&qdo_empty[st]);
         }
         umma_commit(&kv_empty[kb]);   // K / V of this item are no longer read
+      }
       }
     }
   } else {
@@ -1408,6 +1485,15 @@ attn_bwd_persistent_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __g
             tmem_ld32(tS + lane_off + c * 32, sv);
             tmem_ld32(tDP + lane_off + c * 32, dv);
             tmem_ld_wait();
+            if constexpr (kLook) {
+              if (c == 2 * half + 1) {   // last TMEM read of this step: S / dP(gs+1) may overwrite the columns
+                tc_fence_before();
+                __syncwarp();
+                if (lane == 0) mbar_arrive(sdp_read);
+              } else if (gs > 0) {       // before the first P / dS store: dV / dK(gs-1) have consumed the tiles
+                mbar_wait(&qdo_empty[(gs - 1) % C::kStages], ((gs - 1) / C::kStages) & 1);
+              }
+            }
             if constexpr (DIAG) {   // causal mask: a masked score becomes -inf, so p and dS come out as exact zeros
 #pragma unroll
               for (int i = 0; i < 32; ++i)
