@@ -241,6 +241,30 @@ def run_ours(args):
         last["loss_host"] = loss.item()
 
     ms_e2e, _, _ = timed(e2e_step, args.steps, 1, world, None)
+    # ---- parity of the in-kernel NVLink collectives against NCCL on this very box (after the timed regions):
+    # loss and this rank's gradient arena of one forward/backward, fused path vs the same model with NCCL collectives
+    parity = None
+    if world > 1 and pm.pgm.symm is not None and not args.no_check:
+        try:
+            ids_d, pos_d, tgt_d = ids_h.cuda(), pos_h.cuda(), tgt_h.cuda()
+            model.zero_grad(set_to_none=False)
+            loss_f = model.loss(ids_d, pos_d, tgt_d, IGNORE_INDEX)
+            loss_f.backward()
+            g_f = opt.arena.grads.clone()
+            symm_saved, pm.pgm.symm = pm.pgm.symm, None          # same kernels, collectives through NCCL
+            loss_n = model.loss(ids_d, pos_d, tgt_d, IGNORE_INDEX)
+            loss_n.backward()
+            g_n = opt.arena.grads.clone()
+            pm.pgm.symm = symm_saved
+            t = torch.stack([(g_f - g_n).norm() / g_n.norm().clamp_min(1e-30), (loss_f - loss_n).abs().float()])
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            parity = {"loss_abs_diff": float(t[1]), "gradnorm_rel_diff": float(t[0]),
+                      "what": "fused NVLink collectives vs NCCL collectives, same weights and batch, max over ranks"}
+            del g_f, g_n
+        except Exception as e:  # noqa: BLE001  (the check must never take the benchmark down)
+            parity = {"error": f"{type(e).__name__}: {e}"}
+            pm.pgm.symm = pm.pgm.symm or locals().get("symm_saved")
+
     tokens = BATCH * SEQ
     payload = {
         "metric": METRIC, "value": tokens / ms_step * 1e3, "unit": "tokens/s", "n_gpus": world,
@@ -260,6 +284,7 @@ def run_ours(args):
         "gpu_launches": int(step.kernels_per_step) * args.steps,
         "kernels_per_step": int(step.kernels_per_step),
         "final_loss": loss_dev,
+        "parity": parity,
         "lib": os.path.relpath(_lib.LIB_PATH, REPO),
     }
     emit(rank, payload)
@@ -355,6 +380,7 @@ def run_reference(args):
                 "h2d_bytes_per_step": int(3 * BATCH * SEQ * 8), "d2h_bytes_per_step": 4},
         "gpu_launches": 0,
         "final_loss": loss_dev,
+        "parity": parity,
         "max_mem_gib": torch.cuda.max_memory_allocated() / 2 ** 30,
     }
     emit(rank, payload)
@@ -372,6 +398,8 @@ def main():
                     help="default = the reference's train.py model (the headline); gpt2m / 1p3b = BASELINE.json configs 3 / 4")
     ap.add_argument("--comm", choices=["auto", "fused", "nccl"], default="auto",
                     help="TP collectives: our NVLink kernels over symmetric memory (fused), NCCL, or auto")
+    ap.add_argument("--no-check", action="store_true",
+                    help="skip the one-step fused-vs-NCCL parity check that runs before the timed region at N > 1")
     ap.add_argument("--no-graph", action="store_true", help="run eagerly instead of replaying a CUDA graph")
     ap.add_argument("--sp", choices=["on", "off", "auto"], default="auto",
                     help="Megatron sequence parallelism on top of TP (reduce-scatter / all-gather forms)")

@@ -1676,12 +1676,7 @@ static int launch_fwd(const CUtensorMap& tm, void* out, float* lse, int B, int T
                       cudaStream_t stream) {
   using C = FwdCfg<HD>;
   auto kfn = attn_fwd_kernel<HD>;
-  static bool configured = false;
-  if (!configured) {
-    cudaError_t e = cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmem);
-    if (e != cudaSuccess) return static_cast<int>(e);
-    configured = true;
-  }
+  DPFS_ENSURE_DYN_SMEM(kfn, C::kSmem);
   dim3 grid((T + kTile - 1) / kTile, H, B);
   kfn<<<(DPFS_COUNT(), grid), kAttnFwdThreads, C::kSmem, stream>>>(tm, reinterpret_cast<__nv_bfloat16*>(out), lse, T, H, H * HD,
                                                scale * kLog2e);
@@ -1693,12 +1688,7 @@ static int launch_fwd_persistent(const CUtensorMap& tm, void* out, float* lse, i
                                  cudaStream_t stream) {
   using C = FwdPCfg<HD>;
   auto kfn = attn_fwd_persistent_kernel<HD>;
-  static bool configured = false;
-  if (!configured) {
-    cudaError_t e = cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmem);
-    if (e != cudaSuccess) return static_cast<int>(e);
-    configured = true;
-  }
+  DPFS_ENSURE_DYN_SMEM(kfn, C::kSmem);
   const int items = ((T + kTile - 1) / kTile) * H * B;
   const int grid = items < num_sms() ? items : num_sms();
   kfn<<<(DPFS_COUNT(), grid), kAttnFwdThreads, C::kSmem, stream>>>(tm, reinterpret_cast<__nv_bfloat16*>(out), lse, B, T,
@@ -1710,12 +1700,7 @@ static int launch_fwd_pp(const CUtensorMap& tm, void* out, float* lse, int B, in
                          cudaStream_t stream) {
   using C = FwdPPCfg;
   auto kfn = attn_fwd_pp_kernel;
-  static bool configured = false;
-  if (!configured) {
-    cudaError_t e = cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmem);
-    if (e != cudaSuccess) return static_cast<int>(e);
-    configured = true;
-  }
+  DPFS_ENSURE_DYN_SMEM(kfn, C::kSmem);
   const int nq = (T + kTile - 1) / kTile;
   const int items = ((nq + 1) / 2) * H * B;
   const int grid = items < num_sms() ? items : num_sms();
@@ -1729,12 +1714,7 @@ static int launch_bwd(const CUtensorMap& tm_qkv, const CUtensorMap& tm_do, const
                       float* dq_acc, void* dqkv, int B, int T, int H, float scale, cudaStream_t stream) {
   using C = BwdCfg<HD>;
   auto kfn = attn_bwd_kernel<HD>;
-  static bool configured = false;
-  if (!configured) {
-    cudaError_t e = cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmem);
-    if (e != cudaSuccess) return static_cast<int>(e);
-    configured = true;
-  }
+  DPFS_ENSURE_DYN_SMEM(kfn, C::kSmem);
   dim3 grid((T + kTile - 1) / kTile, H, B);
   kfn<<<(DPFS_COUNT(), grid), kAttnBwdThreads, C::kSmem, stream>>>(tm_qkv, tm_do, lse, delta, dq_acc,
                                                reinterpret_cast<__nv_bfloat16*>(dqkv), T, H, H * HD, scale,
@@ -1748,12 +1728,7 @@ static int launch_bwd_persistent(const CUtensorMap& tm_qkv, const CUtensorMap& t
                                  cudaStream_t stream) {
   using C = BwdCfg<HD>;
   auto kfn = attn_bwd_persistent_kernel<HD, V2>;
-  static bool configured = false;
-  if (!configured) {
-    cudaError_t e = cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmemPersistent);
-    if (e != cudaSuccess) return static_cast<int>(e);
-    configured = true;
-  }
+  DPFS_ENSURE_DYN_SMEM(kfn, C::kSmemPersistent);
   const int items = ((T + kTile - 1) / kTile) * H * B;
   const int grid = items < num_sms() ? items : num_sms();
   kfn<<<(DPFS_COUNT(), grid), kAttnBwdThreads, C::kSmemPersistent, stream>>>(tm_qkv, tm_do, tm_dq, tm_dkv, lse, delta,

@@ -222,6 +222,28 @@ __device__ __forceinline__ void reduce_region_to_local_nvls(const uint8_t* mc_ba
   }
 }
 
+// All-reduce flavour through the switch, in place: pull the switch-reduced chunk and broadcast it back into every
+// rank's copy.  Every chunk is read by exactly one thread of one rank (its owner) before that thread overwrites it.
+template <int INFLIGHT = 4>
+__device__ __forceinline__ void reduce_region_nvls(uint8_t* mc_base, long long off0, long long ld_bytes, int rows,
+                                                   int cpr, int tid, int nthreads) {
+  const int total = rows * cpr;
+  for (int base = tid; base < total; base += nthreads * INFLIGHT) {
+    uint4 v[INFLIGHT];
+    long long off[INFLIGHT];
+#pragma unroll
+    for (int k = 0; k < INFLIGHT; ++k) {
+      const int idx = base + k * nthreads;
+      const int r_ = idx / cpr, cc = idx - r_ * cpr;
+      off[k] = off0 + r_ * ld_bytes + cc * 16;
+      if (idx < total) v[k] = multimem_ld_reduce_bf16x8(mc_base + off[k]);
+    }
+#pragma unroll
+    for (int k = 0; k < INFLIGHT; ++k)
+      if (base + k * nthreads < total) multimem_st_16B(mc_base + off[k], v[k]);
+  }
+}
+
 // fp32 variant (4 floats per 16-byte unit)
 template <int NR>
 __device__ __forceinline__ void reduce_region_p2p_f32(const PeerPtrs& peers, long long off0, long long units, int tid,

@@ -16,6 +16,21 @@ namespace dpfs {
 extern unsigned long long g_launches;
 #define DPFS_COUNT() (++::dpfs::g_launches)
 
+// Opt a kernel into more than 48 KB of dynamic shared memory.  The attribute is per DEVICE, so the "already done" state
+// is a bit per device ordinal (a process that drives several GPUs configures each of them); the static lives at the
+// expansion site, i.e. one per kernel instantiation.  Setting it twice is harmless, so no lock is needed.
+#define DPFS_ENSURE_DYN_SMEM(kfn, bytes)                                                                       \
+  do {                                                                                                         \
+    static unsigned long long done_mask_ = 0;                                                                  \
+    int dev_ = 0;                                                                                              \
+    cudaGetDevice(&dev_);                                                                                      \
+    if (!((done_mask_ >> (dev_ & 63)) & 1ull)) {                                                               \
+      cudaError_t e_ = cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (bytes));        \
+      if (e_ != cudaSuccess) return static_cast<int>(e_);                                                      \
+      done_mask_ |= 1ull << (dev_ & 63);                                                                       \
+    }                                                                                                          \
+  } while (0)
+
 // ---------------------------------------------------------------------------------------------
 // misc
 // ---------------------------------------------------------------------------------------------

@@ -964,8 +964,10 @@ extern "C" int dpfs_colsum_scratch_floats(int M, int N) {
 extern "C" int dpfs_colsum_bf16(const void* x, long long ld, float* out, int accumulate, float* scratch, int M, int N,
                                 cudaStream_t stream) {
   if (N % 8 != 0 || ld % 8 != 0) return -23;
+  if (reinterpret_cast<uintptr_t>(x) & 15) return -26;
   if (M <= 0) return 0;
   const int strips = (M + kColsumRowsPerBlock - 1) / kColsumRowsPerBlock;
+  if (strips > 65535) return -27;
   dim3 grid((N / 8 + 127) / 128, strips);
   colsum_partial_kernel<<<(DPFS_COUNT(), grid), 128, 0, stream>>>((const __nv_bfloat16*)x, ld, scratch, M, N);
   cudaError_t e = cudaGetLastError();
@@ -1119,8 +1121,10 @@ int static_scratch_for_current_device(float** out) {
 extern "C" int dpfs_colsum_bf16_static(const void* x, long long ld, float* out, int accumulate, int M, int N,
                                        cudaStream_t stream) {
   if (N % 8 != 0 || ld % 8 != 0) return -23;
+  if (reinterpret_cast<uintptr_t>(x) & 15) return -26;   // the kernel reads 16-byte vectors
   if (M <= 0) return 0;
   const long long strips = (static_cast<long long>(M) + kColsumRowsPerBlock - 1) / kColsumRowsPerBlock;
+  if (strips > 65535) return -27;                        // strips ride in gridDim.y
   if (strips * N > static_cast<long long>(DPFS_COLSUM_STATIC_MAX_FLOATS)) {
     fprintf(stderr,
             "dpfs_colsum_bf16_static: M=%d N=%d needs %lld scratch floats but the built-in scratch holds %d; "

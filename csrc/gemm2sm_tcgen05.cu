@@ -463,21 +463,11 @@ static int launch(const CUtensorMap& tmA, const CUtensorMap& tmB, const Args& ar
   const bool epi8 = force >= 0 ? force != 0 : k_per_tile <= 1024;
   if (epi8) {
     auto kfn = gemm2sm_kernel<A_MN, B_MN, OutT, 8>;
-    static bool configured = false;
-    if (!configured) {
-      cudaError_t e = cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg<8>::kSmem);
-      if (e != cudaSuccess) return static_cast<int>(e);
-      configured = true;
-    }
+    DPFS_ENSURE_DYN_SMEM(kfn, Cfg<8>::kSmem);
     kfn<<<(DPFS_COUNT(), 2 * clusters), Cfg<8>::kThreads, Cfg<8>::kSmem, stream>>>(tmA, tmB, tmOut, args);
   } else {
     auto kfn = gemm2sm_kernel<A_MN, B_MN, OutT, 4>;
-    static bool configured = false;
-    if (!configured) {
-      cudaError_t e = cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg<4>::kSmem);
-      if (e != cudaSuccess) return static_cast<int>(e);
-      configured = true;
-    }
+    DPFS_ENSURE_DYN_SMEM(kfn, Cfg<4>::kSmem);
     kfn<<<(DPFS_COUNT(), 2 * clusters), Cfg<4>::kThreads, Cfg<4>::kSmem, stream>>>(tmA, tmB, tmOut, args);
   }
   return static_cast<int>(cudaGetLastError());

@@ -389,7 +389,9 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
           const int cpr = min(BN, args.N - n0) / 8;  // 16-byte chunks per row
           const long long off0 = (static_cast<long long>(m0) * args.ldo + n0) * 2;
           const long long ldb = args.ldo * 2;
-          if (n == 2) {
+          if (args.mc_out) {   // NVLS data path: the switch sums, the owner re-broadcasts
+            reduce_region_nvls<4>(args.mc_out, off0, ldb, rows, cpr, ct, kCommThreads);
+          } else if (n == 2) {
             reduce_region_p2p<2, 8>(args.peers, off0, ldb, rows, cpr, ct, kCommThreads);
           } else if (n == 4) {
             reduce_region_p2p<4, 8>(args.peers, off0, ldb, rows, cpr, ct, kCommThreads);
@@ -496,12 +498,7 @@ template <int BN, bool A_MN, bool B_MN, typename OutT>
 static int launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmArgs& args, cudaStream_t stream) {
   using S = GemmSmem<BN>;
   auto kfn = gemm_bf16_kernel<BN, A_MN, B_MN, OutT>;
-  static bool configured = false;
-  if (!configured) {
-    cudaError_t e = cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, S::kTotal);
-    if (e != cudaSuccess) return static_cast<int>(e);
-    configured = true;
-  }
+  DPFS_ENSURE_DYN_SMEM(kfn, S::kTotal);
   const int tiles = ((args.M + BM - 1) / BM) * ((args.N + BN - 1) / BN) * args.splits;
   const int grid = tiles < num_sms() ? tiles : num_sms();
   kfn<<<(DPFS_COUNT(), grid), kGemmThreads, S::kTotal, stream>>>(tmA, tmB, args);
@@ -512,12 +509,7 @@ template <int BN, bool B_MN, bool RS = false>
 static int launch_gemm_ar(const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmArgs& args, cudaStream_t stream) {
   using S = GemmSmem<BN>;
   auto kfn = gemm_bf16_kernel<BN, false, B_MN, __nv_bfloat16, true, RS>;
-  static bool configured = false;
-  if (!configured) {
-    cudaError_t e = cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, S::kTotal);
-    if (e != cudaSuccess) return static_cast<int>(e);
-    configured = true;
-  }
+  DPFS_ENSURE_DYN_SMEM(kfn, S::kTotal);
   const int tiles = ((args.M + BM - 1) / BM) * ((args.N + BN - 1) / BN);
   if (tiles > kMaxTiles) return -52;
   int grid = tiles < num_sms() ? tiles : num_sms();
@@ -658,8 +650,11 @@ static int gemm_fused_collective(const void* A, long long lda, const void* B, lo
   args.rs_out = static_cast<__nv_bfloat16*>(rs_out);
   args.rs_rows = rs_out ? M / n : 0;
   {
-    const char* e = getenv("DPFS_FUSE_DEBUG");
-    args.debug = e ? atoi(e) : 0;
+    static const int fuse_debug = [] {   // read once per process, not once per launch
+      const char* e = getenv("DPFS_FUSE_DEBUG");
+      return e ? atoi(e) : 0;
+    }();
+    args.debug = fuse_debug;
   }
   for (int i = 0; i < kMaxRanks; ++i)
     args.peers.p[i] = (i < n && data_ptrs) ? reinterpret_cast<uint8_t*>(data_ptrs[i]) + out_offset : nullptr;

@@ -1,0 +1,355 @@
+// Sequence-parallel "reduce -> row op -> broadcast" kernels: ONE kernel per residual-stream hand-off.
+//
+// With Megatron sequence parallelism every row-parallel GEMM (wo, down_proj, the dgrads of q|k|v and gate|up) is
+// followed by   reduce-scatter -> (residual add + RMSNorm | RMSNorm backward) on this rank's rows -> all-gather
+// before the next column-parallel GEMM can start.  As three kernels that is two collectives with four rank barriers,
+// the reduce-scatter saturating only the GPU's NVLink egress and the all-gather only its ingress.  Here the rank's rows
+// are processed by one kernel, a warp per row:
+//     multimem.ld_reduce  (the NVSwitch returns the fp32-accumulated sum of the n partial rows)
+//  -> the row op in registers
+//  -> multimem.st         (the NVSwitch writes the bf16 result row into every rank's landing zone)
+// so the pull of row i+1 and the push of row i use both link directions at once, the intermediate [M/n, D] tensors
+// never touch HBM, and there are two barriers (partials complete / results landed) instead of four.
+//
+// The reference has no sequence parallelism; the call sites these serve are its Reduce after the row-parallel GEMM
+// (models/comm_ops.py:39 <- models/layers.py:51) + residual add + next RMSNorm (models/model.py:119-120), and the
+// Copy.backward all-reduce (models/comm_ops.py:59 <- models/layers.py:91) + RMSNorm backward.
+#include "comm.cuh"
+#include "dpfs_b200.h"
+
+namespace dpfs {
+
+int num_sms();
+
+// Block shape: T threads = T / 32 warps, each owns whole rows (512 threads for D <= 512, 256 for the wider rows, whose
+// per-lane accumulators need more than 128 registers).
+
+__device__ __forceinline__ void unpack8(const uint4& u, float (&f)[8]) {
+  const uint32_t w[4] = {u.x, u.y, u.z, u.w};
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const float2 t = unpack_bf16(w[i]);
+    f[2 * i] = t.x;
+    f[2 * i + 1] = t.y;
+  }
+}
+__device__ __forceinline__ uint4 pack8(const float (&f)[8]) {
+  return make_uint4(pack_bf16(f[0], f[1]), pack_bf16(f[2], f[3]), pack_bf16(f[4], f[5]), pack_bf16(f[6], f[7]));
+}
+__device__ __forceinline__ void ld8f(const float* p, float (&f)[8]) {
+  const float4 a = *reinterpret_cast<const float4*>(p), b = *reinterpret_cast<const float4*>(p + 4);
+  f[0] = a.x, f[1] = a.y, f[2] = a.z, f[3] = a.w, f[4] = b.x, f[5] = b.y, f[6] = b.z, f[7] = b.w;
+}
+__device__ __forceinline__ void st8f(float* p, const float (&f)[8]) {
+  *reinterpret_cast<float4*>(p) = make_float4(f[0], f[1], f[2], f[3]);
+  *reinterpret_cast<float4*>(p + 4) = make_float4(f[4], f[5], f[6], f[7]);
+}
+
+// A lane owns the 16-byte chunks (8 bf16 columns) j * 32 + lane, j < NC, of a row: D <= NC * 256.
+// R rows per warp are in flight together (the loads of all R rows are issued before the first use).
+
+// ------------------------------------------------------------------------------------------------ forward
+// x_out = x + sum_r partial_r + bias   (fp32, this rank's rows);   h = rmsnorm(x_out) * scale -> every rank (bf16).
+//   mc_part : multicast alias of the partial matrix [n * rpr][D] bf16 (row r0 + i of it is this rank's row i)
+//   x_l     : fp32 [rpr][D] residual or nullptr (treated as zero: the embedding hand-off)
+//   mc_h    : multicast alias of the landing zone [n * rpr][D] bf16, or nullptr (no norm wanted)
+//   h_local : optional private bf16 [rpr][D] copy of this rank's h rows (nullptr = none)
+template <int NC, int R, int T>
+__global__ void __launch_bounds__(T) rs_add_rmsnorm_ag_kernel(
+    CommCtx c, const uint8_t* __restrict__ mc_part, const float* __restrict__ x_l, const float* __restrict__ bias,
+    const float* __restrict__ scale, float* __restrict__ xout_l, float* __restrict__ rstd_l, uint8_t* mc_h, int rpr,
+    int D, float eps) {
+  sync_ranks(c, blockIdx.x);  // every rank's partial matrix is complete; every rank is done with the landing zone
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  constexpr int wpb = T / 32;
+  const int nchunk = D >> 3;
+  float sc[NC][8], bs[NC][8];
+#pragma unroll
+  for (int j = 0; j < NC; ++j) {
+    const int ch = j * 32 + lane;
+#pragma unroll
+    for (int e = 0; e < 8; ++e) sc[j][e] = bs[j][e] = 0.f;
+    if (ch < nchunk) {
+      if (scale) ld8f(scale + ch * 8, sc[j]);
+      if (bias) ld8f(bias + ch * 8, bs[j]);
+    }
+  }
+  const long long r0 = static_cast<long long>(c.rank) * rpr;
+  const long long rowb = static_cast<long long>(D) * 2;
+  for (int row = (blockIdx.x * wpb + warp) * R; row < rpr; row += gridDim.x * wpb * R) {
+    uint4 p[R][NC];
+    float v[R][NC][8];
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+      if (row + r < rpr) {
+#pragma unroll
+        for (int j = 0; j < NC; ++j) {
+          const int ch = j * 32 + lane;
+          if (ch < nchunk) p[r][j] = multimem_ld_reduce_bf16x8(mc_part + (r0 + row + r) * rowb + ch * 16);
+        }
+      }
+    }
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+      if (row + r < rpr) {
+#pragma unroll
+        for (int j = 0; j < NC; ++j) {
+          const int ch = j * 32 + lane;
+#pragma unroll
+          for (int e = 0; e < 8; ++e) v[r][j][e] = 0.f;
+          if (ch < nchunk && x_l) ld8f(x_l + static_cast<long long>(row + r) * D + ch * 8, v[r][j]);
+        }
+      }
+    }
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+      if (row + r >= rpr) continue;
+      float ss = 0.f;
+#pragma unroll
+      for (int j = 0; j < NC; ++j) {
+        const int ch = j * 32 + lane;
+        if (ch < nchunk) {
+          float y[8];
+          unpack8(p[r][j], y);
+#pragma unroll
+          for (int e = 0; e < 8; ++e) {
+            v[r][j][e] += y[e] + bs[j][e];
+            ss += v[r][j][e] * v[r][j][e];
+          }
+          st8f(xout_l + static_cast<long long>(row + r) * D + ch * 8, v[r][j]);
+        }
+      }
+      if (mc_h) {
+        ss = warp_sum(ss);
+        const float rstd = rsqrtf(ss / D + eps);
+        if (lane == 0) rstd_l[row + r] = rstd;
+#pragma unroll
+        for (int j = 0; j < NC; ++j) {
+          const int ch = j * 32 + lane;
+          if (ch < nchunk) {
+            float o[8];
+#pragma unroll
+            for (int e = 0; e < 8; ++e) o[e] = v[r][j][e] * rstd * sc[j][e];
+            multimem_st_16B(mc_h + (r0 + row + r) * rowb + ch * 16, pack8(o));
+          }
+        }
+      }
+    }
+  }
+  sync_ranks(c, blockIdx.x);  // every rank's h rows have landed everywhere; nobody still reads the partials
+}
+
+// ------------------------------------------------------------------------------------------------ backward
+// dh = sum_r partial_r (this rank's rows);  dx = dres + rstd * (g - xhat * mean(g * xhat)),  g = dh * scale,
+// xhat = x * rstd;  dx -> fp32 private rows (optional) and bf16 to every rank (optional).
+// Per-block partial sums over this rank's rows go to scratch[blockIdx.x][2 * D]: [0, D) = dscale = sum dh * xhat,
+// [D, 2D) = column sums of dx (the bias gradient of the row-parallel linear whose output gradient dx is).
+template <int NC, int R, int T>
+__global__ void __launch_bounds__(T) rs_rmsnorm_bwd_ag_kernel(
+    CommCtx c, const uint8_t* __restrict__ mc_part, const float* __restrict__ x_l, const float* __restrict__ rstd_l,
+    const float* __restrict__ scale, const float* __restrict__ dres_l, float* __restrict__ dx_l, uint8_t* mc_dx,
+    float* __restrict__ scratch, int rpr, int D) {
+  __shared__ float red[T / 32][32 * 8];
+  sync_ranks(c, blockIdx.x);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  constexpr int wpb = T / 32;
+  const int nchunk = D >> 3;
+  float sc[NC][8], ds[NC][8], cs[NC][8];
+#pragma unroll
+  for (int j = 0; j < NC; ++j) {
+    const int ch = j * 32 + lane;
+#pragma unroll
+    for (int e = 0; e < 8; ++e) sc[j][e] = ds[j][e] = cs[j][e] = 0.f;
+    if (ch < nchunk) ld8f(scale + ch * 8, sc[j]);
+  }
+  const long long r0 = static_cast<long long>(c.rank) * rpr;
+  const long long rowb = static_cast<long long>(D) * 2;
+  for (int row = (blockIdx.x * wpb + warp) * R; row < rpr; row += gridDim.x * wpb * R) {
+    uint4 p[R][NC];
+    float xh[R][NC][8], rs[R][NC][8];
+    float rstd[R];
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+      rstd[r] = 0.f;
+      if (row + r < rpr) {
+#pragma unroll
+        for (int j = 0; j < NC; ++j) {
+          const int ch = j * 32 + lane;
+          if (ch < nchunk) p[r][j] = multimem_ld_reduce_bf16x8(mc_part + (r0 + row + r) * rowb + ch * 16);
+        }
+      }
+    }
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+      if (row + r < rpr) {
+        rstd[r] = rstd_l[row + r];
+#pragma unroll
+        for (int j = 0; j < NC; ++j) {
+          const int ch = j * 32 + lane;
+#pragma unroll
+          for (int e = 0; e < 8; ++e) xh[r][j][e] = rs[r][j][e] = 0.f;
+          if (ch < nchunk) {
+            const long long off = static_cast<long long>(row + r) * D + ch * 8;
+            ld8f(x_l + off, xh[r][j]);
+            if (dres_l) ld8f(dres_l + off, rs[r][j]);
+          }
+        }
+      }
+    }
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+      if (row + r >= rpr) continue;
+      float g[NC][8];
+      float dot = 0.f;
+#pragma unroll
+      for (int j = 0; j < NC; ++j) {
+        const int ch = j * 32 + lane;
+        if (ch < nchunk) {
+          float dh[8];
+          unpack8(p[r][j], dh);
+#pragma unroll
+          for (int e = 0; e < 8; ++e) {
+            const float xv = xh[r][j][e] * rstd[r];
+            xh[r][j][e] = xv;
+            g[j][e] = dh[e] * sc[j][e];
+            ds[j][e] += dh[e] * xv;
+            dot += g[j][e] * xv;
+          }
+        }
+      }
+      dot = warp_sum(dot) / D;
+#pragma unroll
+      for (int j = 0; j < NC; ++j) {
+        const int ch = j * 32 + lane;
+        if (ch < nchunk) {
+          float o[8];
+#pragma unroll
+          for (int e = 0; e < 8; ++e) {
+            o[e] = rstd[r] * (g[j][e] - xh[r][j][e] * dot) + rs[r][j][e];
+            cs[j][e] += o[e];
+          }
+          if (dx_l) st8f(dx_l + static_cast<long long>(row + r) * D + ch * 8, o);
+          if (mc_dx) multimem_st_16B(mc_dx + (r0 + row + r) * rowb + ch * 16, pack8(o));
+        }
+      }
+    }
+  }
+  // block-level reduction of the two partial-sum rows: warps -> smem -> warp 0 sums in a fixed order
+  float* srow = scratch + static_cast<long long>(blockIdx.x) * 2 * D;
+#pragma unroll
+  for (int which = 0; which < 2; ++which) {
+#pragma unroll
+    for (int j = 0; j < NC; ++j) {
+      __syncthreads();
+#pragma unroll
+      for (int e = 0; e < 8; ++e) red[warp][lane * 8 + e] = which ? cs[j][e] : ds[j][e];
+      __syncthreads();
+      if (warp == 0) {
+        const int ch = j * 32 + lane;
+        if (ch < nchunk) {
+          float o[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+          for (int w = 0; w < wpb; ++w)
+#pragma unroll
+            for (int e = 0; e < 8; ++e) o[e] += red[w][lane * 8 + e];
+          st8f(srow + which * D + ch * 8, o);
+        }
+      }
+    }
+  }
+  sync_ranks(c, blockIdx.x);
+}
+
+// out0[c] (+)= sum_b scratch[b][c], out1[c] (+)= sum_b scratch[b][D + c]: fixed order, deterministic.
+__global__ void __launch_bounds__(256) sp_reduce_partials_kernel(const float* __restrict__ scratch, int nblocks, int D,
+                                                                 float* __restrict__ out0, float* __restrict__ out1,
+                                                                 int accumulate) {
+  __shared__ float sm[8][33];
+  const int lane = threadIdx.x & 31, grp = threadIdx.x >> 5;
+  const int c = blockIdx.x * 32 + lane;  // column of the [2 * D] partial row
+  float s = 0.f;
+  if (c < 2 * D)
+    for (int b = grp; b < nblocks; b += 8) s += scratch[static_cast<long long>(b) * 2 * D + c];
+  sm[grp][lane] = s;
+  __syncthreads();
+  if (grp == 0 && c < 2 * D) {
+    float t = 0.f;
+#pragma unroll
+    for (int g = 0; g < 8; ++g) t += sm[g][lane];
+    float* o = c < D ? (out0 ? out0 + c : nullptr) : (out1 ? out1 + (c - D) : nullptr);
+    if (o) *o = accumulate ? *o + t : t;
+  }
+}
+
+static CommCtx sp_ctx(const unsigned long long* flag_ptrs, int rank, int n) {
+  CommCtx c;
+  for (int i = 0; i < kMaxRanks; ++i) c.flags[i] = i < n ? reinterpret_cast<uint32_t*>(flag_ptrs[i]) : nullptr;
+  c.rank = rank;
+  c.n = n;
+  return c;
+}
+
+// One row per warp-slot: enough blocks that (for the model's shapes) every row of the rank is in flight at once, capped
+// at two resident 512-thread blocks per SM.
+static int sp_grid(int rpr, int R, int T) {
+  const int rows_per_block = (T / 32) * R;
+  int b = (rpr + rows_per_block - 1) / rows_per_block;
+  const int cap = 2 * num_sms() < kMaxBlocks ? 2 * num_sms() : kMaxBlocks;
+  if (b > cap) b = cap;
+  return b < 1 ? 1 : b;
+}
+
+}  // namespace dpfs
+
+using namespace dpfs;
+
+// upper bound of the backward kernel's grid (sizes its [blocks][2 * D] partial-sum scratch)
+extern "C" int dpfs_sp_blocks(int rows_per_rank, int D) {
+  return D <= 512 ? sp_grid(rows_per_rank, 2, 512) : sp_grid(rows_per_rank, 1, 256);
+}
+
+extern "C" int dpfs_rs_add_rmsnorm_ag(const void* mc_partial, const float* x_l, const float* bias, const float* scale,
+                                      float* xout_l, float* rstd_l, void* mc_h, int rows_per_rank, int D, float eps,
+                                      const unsigned long long* flag_ptrs, int rank, int n, cudaStream_t stream) {
+  if (n < 2 || n > kMaxRanks) return -50;
+  if (D % 8 != 0 || D > 1024 || rows_per_rank <= 0) return -60;
+  if (!mc_partial || !xout_l || (mc_h && (!scale || !rstd_l))) return -61;
+  if ((reinterpret_cast<uintptr_t>(mc_partial) & 15) || (reinterpret_cast<uintptr_t>(mc_h) & 15)) return -51;
+  CommCtx c = sp_ctx(flag_ptrs, rank, n);
+  const uint8_t* part = static_cast<const uint8_t*>(mc_partial);
+  uint8_t* h = static_cast<uint8_t*>(mc_h);
+#define DPFS_SP_FWD(NC, R, T)                                                                          \
+  rs_add_rmsnorm_ag_kernel<NC, R, T><<<(DPFS_COUNT(), sp_grid(rows_per_rank, R, T)), T, 0, stream>>>(  \
+      c, part, x_l, bias, scale, xout_l, rstd_l, h, rows_per_rank, D, eps)
+  if (D <= 256) DPFS_SP_FWD(1, 2, 512);
+  else if (D <= 512) DPFS_SP_FWD(2, 2, 512);
+  else DPFS_SP_FWD(4, 1, 256);
+#undef DPFS_SP_FWD
+  return static_cast<int>(cudaGetLastError());
+}
+
+extern "C" int dpfs_rs_rmsnorm_bwd_ag(const void* mc_partial, const float* x_l, const float* rstd_l, const float* scale,
+                                      const float* dres_l, float* dx_l, void* mc_dx, float* dscale_out,
+                                      float* dbias_out, int accumulate, float* scratch, int rows_per_rank, int D,
+                                      const unsigned long long* flag_ptrs, int rank, int n, cudaStream_t stream) {
+  if (n < 2 || n > kMaxRanks) return -50;
+  if (D % 8 != 0 || D > 1024 || rows_per_rank <= 0) return -60;
+  if (!mc_partial || !x_l || !rstd_l || !scale || !scratch) return -61;
+  if ((reinterpret_cast<uintptr_t>(mc_partial) & 15) || (reinterpret_cast<uintptr_t>(mc_dx) & 15)) return -51;
+  CommCtx c = sp_ctx(flag_ptrs, rank, n);
+  const uint8_t* part = static_cast<const uint8_t*>(mc_partial);
+  uint8_t* dx = static_cast<uint8_t*>(mc_dx);
+  int grid = 0;
+#define DPFS_SP_BWD(NC, R, T)                                                         \
+  grid = sp_grid(rows_per_rank, R, T);                                                \
+  rs_rmsnorm_bwd_ag_kernel<NC, R, T><<<(DPFS_COUNT(), grid), T, 0, stream>>>(         \
+      c, part, x_l, rstd_l, scale, dres_l, dx_l, dx, scratch, rows_per_rank, D)
+  if (D <= 256) { DPFS_SP_BWD(1, 2, 512); }
+  else if (D <= 512) { DPFS_SP_BWD(2, 2, 512); }
+  else { DPFS_SP_BWD(4, 1, 256); }
+#undef DPFS_SP_BWD
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return static_cast<int>(e);
+  sp_reduce_partials_kernel<<<(DPFS_COUNT(), (2 * D + 31) / 32), 256, 0, stream>>>(scratch, grid, D, dscale_out,
+                                                                                    dbias_out, accumulate);
+  return static_cast<int>(cudaGetLastError());
+}

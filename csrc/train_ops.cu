@@ -59,7 +59,8 @@ __global__ void embedding_fwd_mc_kernel(const long long* __restrict__ ids, const
 }
 
 // dweight[ids[m] - vocab_start][:] += dout[m][:] for owned ids (dweight must be zeroed by the caller).
-__global__ void embedding_bwd_kernel(const long long* __restrict__ ids, const float* __restrict__ dout,
+template <typename GT>
+__global__ void embedding_bwd_kernel(const long long* __restrict__ ids, const GT* __restrict__ dout,
                                      float* __restrict__ dweight, int M, int D, long long vocab_start,
                                      long long vocab_end) {
   const int vec = D / 4;
@@ -70,7 +71,14 @@ __global__ void embedding_bwd_kernel(const long long* __restrict__ ids, const fl
     const int c = static_cast<int>(i % vec) * 4;
     const long long id = ids[row];
     if (id < vocab_start || id >= vocab_end) continue;
-    const float4 g = *reinterpret_cast<const float4*>(dout + static_cast<long long>(row) * D + c);
+    float4 g;
+    if constexpr (sizeof(GT) == 4) {
+      g = *reinterpret_cast<const float4*>(dout + static_cast<long long>(row) * D + c);
+    } else {
+      const uint2 u = *reinterpret_cast<const uint2*>(dout + static_cast<long long>(row) * D + c);
+      const float2 a = unpack_bf16(u.x), b = unpack_bf16(u.y);
+      g = make_float4(a.x, a.y, b.x, b.y);
+    }
     float* w = dweight + (id - vocab_start) * D + c;
     atomicAdd(w + 0, g.x);
     atomicAdd(w + 1, g.y);
@@ -304,7 +312,21 @@ extern "C" int dpfs_embedding_bwd(const long long* ids, const float* dout, float
   if (zero_first) cudaMemsetAsync(dweight, 0, sizeof(float) * local_vocab * D, stream);
   if (M <= 0) return 0;
   const long long total = static_cast<long long>(M) * (D / 4);
-  embedding_bwd_kernel<<<(DPFS_COUNT(), ew_grid2(total, 256)), 256, 0, stream>>>(ids, dout, dweight, M, D, vocab_start, vocab_end);
+  embedding_bwd_kernel<float><<<(DPFS_COUNT(), ew_grid2(total, 256)), 256, 0, stream>>>(ids, dout, dweight, M, D,
+                                                                                        vocab_start, vocab_end);
+  return static_cast<int>(cudaGetLastError());
+}
+
+// same with a bf16 output gradient (the sequence-parallel path all-gathers the residual-stream gradient in bf16)
+extern "C" int dpfs_embedding_bwd_bf16(const long long* ids, const void* dout_bf16, float* dweight, int zero_first,
+                                       long long local_vocab, int M, int D, long long vocab_start,
+                                       long long vocab_end, cudaStream_t stream) {
+  if (D % 4 != 0) return -30;
+  if (zero_first) cudaMemsetAsync(dweight, 0, sizeof(float) * local_vocab * D, stream);
+  if (M <= 0) return 0;
+  const long long total = static_cast<long long>(M) * (D / 4);
+  embedding_bwd_kernel<__nv_bfloat16><<<(DPFS_COUNT(), ew_grid2(total, 256)), 256, 0, stream>>>(
+      ids, static_cast<const __nv_bfloat16*>(dout_bf16), dweight, M, D, vocab_start, vocab_end);
   return static_cast<int>(cudaGetLastError());
 }
 

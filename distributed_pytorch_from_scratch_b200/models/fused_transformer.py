@@ -38,19 +38,37 @@ BF16, F32 = torch.bfloat16, torch.float32
 _ALIGN = 64  # elements; keeps every group 256 B (fp32) / 128 B (bf16) aligned for TMA and vector access
 
 
-def fused_supported(model) -> bool:
+def fused_unsupported_reason(model) -> Optional[str]:
+    """None when the hand-scheduled sm_100a path can run this model, else a sentence naming the limit it hits."""
     n = pm.pgm.tp_size
     hd = model.head_dim
     d, f, V = model.attn_dim, model.ffn_dim, model.vocab_size
     if hd not in (64, 128):
-        return False
-    if d % 8 or d > 2048 and d % 4:
-        return False
-    if d > 2048:   # fused norm kernels keep a row in registers (D <= 2048)
-        return False
-    if (d // n) % 8 or (f // n) % 8 or V % n or (V // n) % 8:
-        return False
-    return True
+        return f"head_dim {hd} is not 64 or 128 (the tcgen05 flash-attention kernels are built for those two)"
+    if d % 8:
+        return f"attn_dim {d} is not a multiple of 8 (16-byte vector access / TMA alignment)"
+    if d > 2048:
+        return f"attn_dim {d} > 2048 (the fused norm kernels keep one row of the residual stream in registers)"
+    if (d // n) % 8 or (f // n) % 8:
+        return f"attn_dim / tp ({d // n}) and ffn_dim / tp ({f // n}) must be multiples of 8"
+    if V % n or (V // n) % 8:
+        return f"vocab_size {V} must split into multiples of 8 over tp_size {n}"
+    return None
+
+
+_WARNED = set()
+
+
+def fused_supported(model) -> bool:
+    """Whether the fused path runs.  A model that misses a limit drops to the module path (PyTorch attention with a
+    materialised t x t mask, cuBLAS GEMMs: the reference's own path) -- never silently: the reason is printed once."""
+    why = fused_unsupported_reason(model)
+    if why is not None and why not in _WARNED and model.attn_dim > 0:
+        _WARNED.add(why)
+        if next(model.parameters()).is_cuda:
+            print(f"[dpfs] WARNING: the fused sm_100a Transformer path is OFF for this model: {why}. "
+                  f"Falling back to the PyTorch module path (much slower).", flush=True)
+    return why is None
 
 
 # ================================================================================================ parameter arena
@@ -62,13 +80,15 @@ class ParamArena:
         for layer in model.layers:
             a, f = layer.attn, layer.ffn
             groups += [[a.wq.weight, a.wk.weight, a.wv.weight], [a.wq.bias, a.wk.bias, a.wv.bias],
-                       [a.wo.weight], [a.wo.bias], [f.gate_proj.weight, f.up_proj.weight],
-                       [f.gate_proj.bias, f.up_proj.bias], [f.down_proj.weight], [f.down_proj.bias]]
+                       [a.wo.weight], [f.gate_proj.weight, f.up_proj.weight],
+                       [f.gate_proj.bias, f.up_proj.bias], [f.down_proj.weight]]
         groups += [[model.embedding.weight], [model.lm_head.weight], [model.lm_head.bias]]
-        # every RMSNorm scale in ONE contiguous block: under sequence parallelism their gradients are partial sums
-        # over the local rows and are all-reduced with a single small collective
+        # every REPLICATED parameter (RMSNorm scales, the biases of the row-parallel wo / down_proj) in ONE contiguous
+        # block: under sequence parallelism their gradients are partial sums over the local rows and are all-reduced
+        # with a single small collective at the end of the backward pass
         norm_group = [s_ for layer in model.layers for s_ in (layer.norm1.scale, layer.norm2.scale)]
         norm_group.append(model.norm.scale)
+        norm_group += [b_ for layer in model.layers for b_ in (layer.attn.wo.bias, layer.ffn.down_proj.bias)]
         groups.append(norm_group)
         seen = set()
         for g in groups:
@@ -360,7 +380,11 @@ class FusedRuntime:
         self.packs: List[LayerPack] = [LayerPack(A, layer, d, self.Dl, self.Fl) for layer in model.layers]
         for i, pack in enumerate(self.packs):
             pack.prev = self.packs[i - 1] if i > 0 else None
+            pack.index = i
         self._stash = None
+        self._fwd_handoff = None      # (x_l, gathered normalised input of the next block, its rstd)
+        self._zones = None            # symmetric activation zones of the hand-off path (allocated on first use)
+        self._zone_rows = 0
         head, emb = model.lm_head, model.embedding
         Vl = head.odim_partition
         self.wlm, self.g_wlm = A.view(A.shadow, head.weight, Vl, d), A.view(A.grads, head.weight, Vl, d)
@@ -399,6 +423,12 @@ class FusedRuntime:
         ids = input_ids.reshape(-1).contiguous()
         pos = position_ids.reshape(-1).contiguous()
         if self.sp_active(B * T):
+            if self.handoff_ready(B * T):
+                # ONE kernel per residual-stream hand-off (reduce-scatter -> norm -> all-gather through the switch)
+                x = HandoffEmbedFn.apply(ids, self, self.model.embedding.weight)
+                for pack in self.packs:
+                    x = HandoffLayerFn.apply(x, pos, self, pack, meta, *pack.params)
+                return x
             x = FusedEmbedSPFn.apply(ids, self, self.model.embedding.weight)
             for pack in self.packs:
                 x = FusedLayerSPFn.apply(x, pos, self, pack, meta, *pack.params)
@@ -407,6 +437,31 @@ class FusedRuntime:
         for pack in self.packs:
             x = FusedLayerFn.apply(x, pos, self, pack, meta, *pack.params)
         return x  # fp32 [M, d]
+
+    # ---------------------------------------------------------------------------------------------- SP hand-off path
+    def handoff_ready(self, M: int) -> bool:
+        """True when the one-kernel hand-offs (csrc/sp_fused.cu) can run this batch: NVLS multicast available, model
+        width within the kernels' register budget, partial matrix fits the symmetric buffer.  Allocates the symmetric
+        activation zones on first use (a collective: every rank takes this branch for the same batch shapes)."""
+        symm = pm.pgm.symm
+        if symm is None or not symm.mc_base or symm.closed or os.environ.get("DPFS_SP_HANDOFF", "1") != "1":
+            return False
+        if self.d % 8 or self.d > 1024 or M * self.d * 2 > symm.ag_off:
+            return False
+        if self._zones is None or M > self._zone_rows:
+            # h1 / h2 of every layer and the final norm's output stay resident for the backward pass (2L + 1 zones);
+            # one more zone carries the gathered bf16 residual-stream gradient during the backward pass
+            self._zones = symm.alloc_zones(2 * len(self.packs) + 2, M * self.d * 2)
+            self._zone_rows = M
+        return True
+
+    def put_handoff(self, x_l, h, rstd) -> None:
+        self._fwd_handoff = (x_l, h, rstd)
+
+    def take_handoff(self, x_l):
+        st, self._fwd_handoff = self._fwd_handoff, None
+        assert st is not None and st[0].data_ptr() == x_l.data_ptr(), "hand-off state does not belong to this input"
+        return st[1], st[2]
 
     def sp_active(self, M: int) -> bool:
         """Sequence parallelism is on when the model asks for it, TP > 1 and the rows split evenly (16 B units)."""
@@ -417,12 +472,15 @@ class FusedRuntime:
         x = self.forward_hidden(input_ids, position_ids)
         tg = target_ids.reshape(-1).contiguous()
         if self.sp_active(tg.numel()):
+            if self._fwd_handoff is not None:
+                return HandoffHeadLossFn.apply(x, tg, self, ignore_index, *self.head_params)
             return FusedHeadLossSPFn.apply(x, tg, self, ignore_index, *self.head_params)
         return FusedHeadLossFn.apply(x, tg, self, ignore_index, *self.head_params)
 
     def forward_logits(self, input_ids, position_ids) -> torch.Tensor:
         B, T = input_ids.shape
         x = self.forward_hidden(input_ids, position_ids)
+        self._fwd_handoff = None
         if self.sp_active(B * T):
             x = _all_gather_rows(x, keep=True)      # gather the rows back for the (replicated) logits path
         x = x.view(B, T, self.d)
@@ -539,7 +597,8 @@ class FusedLayerSPFn(torch.autograd.Function):
             dx3 = _all_gather_rows(fused.cast_to_bf16(dx3_l))                            # [M, d] bf16
         dact = gemm_nt(dx3, pack.wd, b_mn_major=True, out_dtype=BF16)
         _wgrad(dx3, act, pack.g_wd)
-        fused.colsum(dx3, out=pack.g_bd)
+        Ml, r = dx3_l.shape[0], pm.pgm.tp_rank
+        fused.colsum(dx3[r * Ml:(r + 1) * Ml], out=pack.g_bd)    # partial over this rank's rows (see norm_grads)
         dgu = fused.swiglu_bwd_bias(dact, gu, pack.g_bgu)
         del dact
         dh2_l = _rowpar_rs(dgu, pack.wgu, b_mn_major=True)                               # [Ml, d]
@@ -553,7 +612,7 @@ class FusedLayerSPFn(torch.autograd.Function):
             dx2 = _all_gather_rows(dx2_lb)
         dattn = gemm_nt(dx2, pack.wo, b_mn_major=True, out_dtype=BF16)
         _wgrad(dx2, attn, pack.g_wo)
-        fused.colsum(dx2, out=pack.g_bo)
+        fused.colsum(dx2[r * Ml:(r + 1) * Ml], out=pack.g_bo)
         dqkv = attn_bwd(qkv, attn, dattn, lse, m.B, m.T, m.Hl, m.hd, m.scale)
         fused.rope_inplace(dqkv, pos, rt.cos_half, rt.sin_half, 2, m.Dl, m.Hl, m.hd, inverse=True)
         dh1_l = _rowpar_rs(dqkv, pack.wqkv, b_mn_major=True)
@@ -620,4 +679,135 @@ class FusedHeadLossSPFn(torch.autograd.Function):
         _wgrad(dlogits, h, rt.g_wlm)
         fused.colsum(dlogits, out=rt.g_blm)
         dx_l, _, _ = fused.rmsnorm_bwd(dh_l, x_l, rstd, rt.sN, dres=None, want_fp32=True, dscale_out=rt.g_sN)
+        return (dx_l, None, None, None) + (None,) * 3
+
+
+# ================================================================================================ SP hand-off path
+# The same sequence-parallel schedule with every residual-stream hand-off as ONE kernel (csrc/sp_fused.cu):
+#     partial = row-parallel GEMM (symmetric buffer)   ->   rs_add_rmsnorm_ag / rs_rmsnorm_bwd_ag
+# i.e. reduce-scatter, residual + bias + RMSNorm (or RMSNorm backward) on this rank's rows and the all-gather of the
+# bf16 result run as one pass through the NVSwitch (multimem.ld_reduce in, multimem.st out, both link directions busy).
+# The norm that OPENS a block is therefore computed by the kernel that CLOSES the previous one: autograd carries only
+# the fp32 local rows x_l between the Functions; the gathered activations travel through the runtime (put_handoff /
+# take_handoff forward, put_stash / take_stash backward) and are checked against the tensor they belong to.
+class HandoffEmbedFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, ids_flat, rt, weight):
+        emb = rt.model.embedding
+        symm = pm.pgm.symm
+        M, D = ids_flat.numel(), weight.shape[1]
+        part = symm.buffer((M, D), BF16)
+        fused.embedding_fwd(ids_flat, weight.detach(), emb.vocab_st_idx, emb.vocab_ed_idx, out=part)
+        # exact: one owner per row, the others contribute zeros; the first layer's norm rides in the same kernel
+        x_l, h1, rstd1 = fused.rs_add_rmsnorm_ag(symm, part, None, None, rt.packs[0].s1, rt.eps, rt._zones[0])
+        rt.put_handoff(x_l, h1, rstd1)
+        ctx.save_for_backward(ids_flat)
+        ctx.rt = rt
+        return x_l
+
+    @staticmethod
+    def backward(ctx, dx_l):
+        (ids_flat,) = ctx.saved_tensors
+        rt = ctx.rt
+        emb = rt.model.embedding
+        dx = rt.take_stash(dx_l)          # gathered bf16 [M, d], produced by layer 0's closing hand-off
+        assert dx is not None
+        fused.embedding_bwd(ids_flat, dx, emb.weight.shape[0], emb.vocab_st_idx, emb.vocab_ed_idx, dweight=rt.g_emb,
+                            zero_first=True)
+        # last node of the backward pass: complete the gradients of the replicated parameters (partial sums over rows)
+        comm_ops.all_reduce_sum_(rt.arena.norm_grads)
+        return None, None, None
+
+
+class HandoffLayerFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x_l, pos, rt, pack: LayerPack, meta: Meta, *params):
+        m = meta
+        symm = pm.pgm.symm
+        li = pack.index
+        h1, rstd1 = rt.take_handoff(x_l)
+        qkv = gemm_nt(h1, pack.wqkv, bias=pack.bqkv, out_dtype=BF16)
+        fused.rope_inplace(qkv, pos, rt.cos_half, rt.sin_half, 2, m.Dl, m.Hl, m.hd, inverse=False)
+        attn, lse = attn_fwd(qkv, m.B, m.T, m.Hl, m.hd, m.scale)
+        part = symm.buffer((m.M, m.d), BF16)
+        gemm_nt(attn, pack.wo, out=part)
+        x2_l, h2, rstd2 = fused.rs_add_rmsnorm_ag(symm, part, x_l, pack.bo, pack.s2, rt.eps, rt._zones[2 * li + 1])
+        gu = gemm_nt(h2, pack.wgu, bias=pack.bgu, out_dtype=BF16)
+        act = fused.swiglu_fwd(gu)
+        gemm_nt(act, pack.wd, out=part)
+        nxt = rt.packs[li + 1].s1 if li + 1 < len(rt.packs) else rt.sN      # the norm that opens the next block
+        x3_l, hn, rstdn = fused.rs_add_rmsnorm_ag(symm, part, x2_l, pack.bd, nxt, rt.eps, rt._zones[2 * li + 2])
+        rt.put_handoff(x3_l, hn, rstdn)
+        ctx.save_for_backward(x_l, pos, h1, rstd1, qkv, attn, lse, x2_l, h2, rstd2, gu, act)
+        ctx.pack, ctx.meta, ctx.rt = pack, meta, rt
+        return x3_l
+
+    @staticmethod
+    def backward(ctx, dx3_l):
+        x_l, pos, h1, rstd1, qkv, attn, lse, x2_l, h2, rstd2, gu, act = ctx.saved_tensors
+        pack, m, rt = ctx.pack, ctx.meta, ctx.rt
+        symm = pm.pgm.symm
+        bzone = rt._zones[-1]
+        dx3_l = dx3_l.contiguous()
+        dx3 = rt.take_stash(dx3_l)        # gathered bf16 [M, d] from the hand-off that closed the block above
+        assert dx3 is not None
+        dact = gemm_nt(dx3, pack.wd, b_mn_major=True, out_dtype=BF16)
+        _wgrad(dx3, act, pack.g_wd)
+        dgu = fused.swiglu_bwd_bias(dact, gu, pack.g_bgu)
+        del dact
+        part = symm.buffer((m.M, m.d), BF16)
+        gemm_nt(dgu, pack.wgu, b_mn_major=True, out=part)
+        _wgrad(dgu, h2, pack.g_wgu)
+        del dgu
+        # dx2 is the output gradient of wo's residual add: its (local) column sums are the wo bias gradient
+        dx2_l, dx2 = fused.rs_rmsnorm_bwd_ag(symm, part, x2_l, rstd2, pack.s2, dx3_l, bzone, pack.g_s2, pack.g_bo)
+        dattn = gemm_nt(dx2, pack.wo, b_mn_major=True, out_dtype=BF16)
+        _wgrad(dx2, attn, pack.g_wo)
+        dqkv = attn_bwd(qkv, attn, dattn, lse, m.B, m.T, m.Hl, m.hd, m.scale)
+        fused.rope_inplace(dqkv, pos, rt.cos_half, rt.sin_half, 2, m.Dl, m.Hl, m.hd, inverse=True)
+        gemm_nt(dqkv, pack.wqkv, b_mn_major=True, out=part)
+        _wgrad(dqkv, h1, pack.g_wqkv)
+        fused.colsum(dqkv, out=pack.g_bqkv)
+        # dx is the output gradient of the block below (its down_proj bias gradient comes from the same pass)
+        prev_bd = pack.prev.g_bd if pack.prev is not None else None
+        dx_l, dx = fused.rs_rmsnorm_bwd_ag(symm, part, x_l, rstd1, pack.s1, dx2_l, bzone, pack.g_s1, prev_bd)
+        rt.put_stash(dx_l, dx)
+        return (dx_l, None, None, None, None) + (None,) * len(pack.params)
+
+
+class HandoffHeadLossFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x_l, targets_flat, rt, ignore_index, *params):
+        n = pm.pgm.tp_size
+        head = rt.model.lm_head
+        Vl = head.odim_partition
+        vocab_start = pm.pgm.tp_rank * Vl
+        h, rstd = rt.take_handoff(x_l)        # final RMSNorm, computed and gathered by the last layer's hand-off
+        logits = gemm_nt(h, rt.wlm, bias=rt.blm, out_dtype=F32)
+        stats, loss_acc = fused.ce_stats(logits, targets_flat, vocab_start, ignore_index)
+        symm = pm.pgm.symm
+        all_stats = symm.all_gather_rows(stats)
+        fused.ce_loss(targets_flat, all_stats, n, loss_acc, ignore_index)
+        loss = loss_acc[0] / loss_acc[1]
+        ctx.save_for_backward(x_l, targets_flat, h, rstd, logits, all_stats, loss_acc)
+        ctx.rt, ctx.ignore_index, ctx.vocab_start = rt, ignore_index, vocab_start
+        return loss
+
+    @staticmethod
+    def backward(ctx, gout):
+        x_l, targets_flat, h, rstd, logits, all_stats, loss_acc = ctx.saved_tensors
+        rt = ctx.rt
+        n = pm.pgm.tp_size
+        symm = pm.pgm.symm
+        up = gout.detach().reshape(1).float().contiguous()
+        dlogits = fused.ce_grad(logits, targets_flat, all_stats, n, loss_acc, ctx.vocab_start, ctx.ignore_index,
+                                upstream=up)
+        M, d = h.shape
+        part = symm.buffer((M, d), BF16)
+        gemm_nt(dlogits, rt.wlm, b_mn_major=True, out=part)
+        _wgrad(dlogits, h, rt.g_wlm)
+        fused.colsum(dlogits, out=rt.g_blm)
+        dx_l, dx = fused.rs_rmsnorm_bwd_ag(symm, part, x_l, rstd, rt.sN, None, rt._zones[-1], rt.g_sN,
+                                           rt.packs[-1].g_bd)
+        rt.put_stash(dx_l, dx)
         return (dx_l, None, None, None) + (None,) * 3

@@ -64,7 +64,14 @@ class RowParallelLinear(nn.Module):
     def forward(self, x: torch.Tensor) -> torch.Tensor:
         if self.split_input:
             x = Split.apply(x)
-        if dispatch.use_native(x) and self.idim_partition % 8 == 0 and self.odim % 8 == 0:
+        native = dispatch.use_native(x) and self.idim_partition % 8 == 0 and self.odim % 8 == 0
+        if native and pm.pgm.tp_size > 1:
+            from ..ops.linear import RowParallelLinearFn, can_fuse_row_parallel
+            if can_fuse_row_parallel(x, self.weight):
+                # ONE kernel: tcgen05 GEMM whose finished tiles are summed over NVLink while the next ones compute
+                y = RowParallelLinearFn.apply(x, self.weight)
+                return y + self.bias if self.add_bias else y
+        if native:
             from ..ops.linear import native_linear
             y = native_linear(x, self.weight, None)
         else:
@@ -103,8 +110,14 @@ class ColumnParallelLinear(nn.Module):
             nn.init.zeros_(self.bias)
 
     def forward(self, x: torch.Tensor) -> torch.Tensor:
+        native = dispatch.use_native(x) and self.idim % 8 == 0 and self.odim_partition % 8 == 0
+        if native and pm.pgm.tp_size > 1 and pm.pgm.symm is not None:
+            # backward = dgrad GEMM + all-reduce in ONE kernel (takes the place of Copy.backward)
+            from ..ops.linear import ColumnParallelLinearFn
+            y = ColumnParallelLinearFn.apply(x, self.weight, self.bias if self.add_bias else None)
+            return Gather.apply(y) if self.gather_output else y
         x = Copy.apply(x)
-        if dispatch.use_native(x) and self.idim % 8 == 0 and self.odim_partition % 8 == 0:
+        if native:
             from ..ops.linear import native_linear
             y = native_linear(x, self.weight, self.bias if self.add_bias else None)  # bias fused in the epilogue
         else:
@@ -157,6 +170,11 @@ class ParallelVocabularyEmbedding(nn.Module):
         assert x.ndim == 2, f"Input should be 2D tensor (B, L), but got {x.ndim}D tensor."
         if pm.pgm.tp_size == 1:
             return F.embedding(x, self.weight)
+        if (x.is_cuda and dispatch.use_native(self.weight) and self.weight.dtype == torch.float32
+                and self.hdim % 8 == 0 and self.vocab_size % pm.pgm.tp_size == 0):
+            # lookup kernel (+ owner scatter through the NVSwitch when multicast is available) and native backward
+            from ..ops.linear import VocabParallelEmbeddingFn
+            return VocabParallelEmbeddingFn.apply(x, self.weight, self.vocab_st_idx, self.vocab_ed_idx)
         mask = torch.logical_and(self.vocab_st_idx <= x, x < self.vocab_ed_idx)
         local = torch.where(mask, x - self.vocab_st_idx, torch.zeros_like(x))
         out = F.embedding(local, self.weight)

@@ -69,6 +69,11 @@ SIGS = {
     "dpfs_embedding_fwd": (c_p, c_p, c_p, c_int, c_int, c_int, c_ll, c_ll, c_p),
     "dpfs_embedding_fwd_mc": (c_p, c_p, c_p, c_int, c_int, c_ll, c_ll, c_p),
     "dpfs_embedding_bwd": (c_p, c_p, c_p, c_int, c_ll, c_int, c_int, c_ll, c_ll, c_p),
+    "dpfs_embedding_bwd_bf16": (c_p, c_p, c_p, c_int, c_ll, c_int, c_int, c_ll, c_ll, c_p),
+    "dpfs_rs_add_rmsnorm_ag": (c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_int, c_int, c_f, c_p, c_int, c_int, c_p),
+    "dpfs_rs_rmsnorm_bwd_ag": (c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_int, c_p, c_int, c_int, c_p, c_int,
+                               c_int, c_p),
+    "dpfs_sp_blocks": (c_int, c_int),
     "dpfs_ce_stats": (c_p, c_int, c_ll, c_p, c_p, c_p, c_int, c_int, c_ll, c_ll, c_p),
     "dpfs_ce_loss": (c_p, c_p, c_int, c_p, c_p, c_int, c_ll, c_p),
     "dpfs_ce_grad": (c_p, c_int, c_ll, c_p, c_p, c_int, c_p, c_ll, c_p, c_p, c_int, c_int, c_ll, c_ll, c_p),

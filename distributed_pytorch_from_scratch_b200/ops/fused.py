@@ -12,6 +12,7 @@ import torch
 from . import _lib
 
 _SCRATCH = {}
+_RETIRED = []   # outgrown scratch buffers stay allocated: a CUDA graph captured earlier has their addresses baked in
 BF16 = torch.bfloat16
 F32 = torch.float32
 
@@ -20,6 +21,11 @@ def _scratch(device, key: str, nfloats: int) -> torch.Tensor:
     k = (device, key)
     buf = _SCRATCH.get(k)
     if buf is None or buf.numel() < nfloats:
+        if buf is not None:
+            # Never hand an outgrown buffer back to the caching allocator: TrainStep keeps one captured graph per batch
+            # shape, and a graph captured for a smaller shape still writes its partial sums through the old pointer on
+            # every replay.  The buffers are a few hundred KB; keeping them costs nothing.
+            _RETIRED.append(buf)
         buf = torch.empty(max(nfloats, 1024), dtype=F32, device=device)
         _SCRATCH[k] = buf
     return buf
@@ -170,6 +176,56 @@ def cast_to_bf16_push(x_l: torch.Tensor, symm) -> torch.Tensor:
                "dpfs_cast_f32_to_bf16_mc")
     symm.push_done()
     return full
+
+
+# ------------------------------------------------------------------------------------------------ SP hand-offs
+# Sequence-parallel residual-stream hand-offs as ONE kernel each (csrc/sp_fused.cu): reduce-scatter of the row-parallel
+# GEMM's partial products -> row op on this rank's rows -> all-gather of the bf16 result, through the NVSwitch
+# (multimem.ld_reduce / multimem.st).  ``part`` is the [M, D] bf16 partial matrix in the symmetric buffer, ``zone`` a
+# parallel.symm_comm.SymmZone that receives the gathered [M, D] bf16 result on every rank.
+def rs_add_rmsnorm_ag(symm, part: torch.Tensor, x_l: Optional[torch.Tensor], bias: Optional[torch.Tensor],
+                      scale: torch.Tensor, eps: float, zone):
+    """x_out_l = x_l + reduce_scatter(part) + bias; h = all_gather(rmsnorm(x_out_l) * scale).
+    Returns (x_out_l fp32 [M/n, D], h bf16 [M, D] (view of ``zone``), rstd fp32 [M/n])."""
+    M, D = part.shape
+    n = symm.n
+    Ml = M // n
+    assert part.dtype == BF16 and part.is_contiguous() and symm._inside(part) and M % n == 0 and symm.mc_base
+    if x_l is not None:
+        assert x_l.dtype == F32 and x_l.shape == (Ml, D) and x_l.is_contiguous()
+    x_out = torch.empty((Ml, D), dtype=F32, device=part.device)
+    rstd = torch.empty(Ml, dtype=F32, device=part.device)
+    h = zone.view((M, D), BF16)
+    mc_part = symm.mc_base + (part.data_ptr() - symm.base)
+    rc = _lib.lib().dpfs_rs_add_rmsnorm_ag(mc_part, _lib.ptr(x_l), _lib.ptr(bias), scale.data_ptr(), x_out.data_ptr(),
+                                           rstd.data_ptr(), zone.mc, Ml, D, eps, symm.flag_ptrs, symm.rank, n,
+                                           _lib.stream())
+    _lib.check(rc, "dpfs_rs_add_rmsnorm_ag")
+    return x_out, h, rstd
+
+
+def rs_rmsnorm_bwd_ag(symm, part: torch.Tensor, x_l: torch.Tensor, rstd: torch.Tensor, scale: torch.Tensor,
+                      dres_l: Optional[torch.Tensor], zone, dscale_out: torch.Tensor,
+                      dbias_out: Optional[torch.Tensor] = None, want_fp32: bool = True):
+    """dx_l = dres_l + rmsnorm'(reduce_scatter(part)); its bf16 copy is all-gathered into ``zone``.
+    dscale_out / dbias_out receive partial sums over THIS rank's rows.  Returns (dx_l | None, dx bf16 [M, D] view)."""
+    M, D = part.shape
+    n = symm.n
+    Ml = M // n
+    assert part.dtype == BF16 and part.is_contiguous() and symm._inside(part) and M % n == 0 and symm.mc_base
+    assert x_l.dtype == F32 and x_l.shape == (Ml, D) and x_l.is_contiguous() and rstd.numel() == Ml
+    if dres_l is not None:
+        assert dres_l.dtype == F32 and dres_l.shape == (Ml, D) and dres_l.is_contiguous()
+    lib = _lib.lib()
+    dx_l = torch.empty((Ml, D), dtype=F32, device=part.device) if want_fp32 else None
+    scratch = _scratch(part.device, "sp_norm", lib.dpfs_sp_blocks(Ml, D) * 2 * D)
+    mc_part = symm.mc_base + (part.data_ptr() - symm.base)
+    rc = lib.dpfs_rs_rmsnorm_bwd_ag(mc_part, x_l.data_ptr(), rstd.data_ptr(), scale.data_ptr(), _lib.ptr(dres_l),
+                                    _lib.ptr(dx_l), zone.mc if zone is not None else 0, _lib.ptr(dscale_out),
+                                    _lib.ptr(dbias_out), 0, scratch.data_ptr(), Ml, D, symm.flag_ptrs, symm.rank, n,
+                                    _lib.stream())
+    _lib.check(rc, "dpfs_rs_rmsnorm_bwd_ag")
+    return dx_l, (zone.view((M, D), BF16) if zone is not None else None)
 
 
 # ------------------------------------------------------------------------------------------------ LayerNorm
@@ -326,10 +382,11 @@ def embedding_bwd(ids: torch.Tensor, dout: torch.Tensor, local_vocab: int, vocab
     ids_flat = ids.reshape(-1).contiguous()
     D = dout.shape[-1]
     dout2 = dout.reshape(-1, D)
-    assert dout2.dtype == F32 and dout2.is_contiguous()
+    assert dout2.dtype in (F32, BF16) and dout2.is_contiguous()
     if dweight is None:
         dweight = torch.empty((local_vocab, D), dtype=F32, device=dout.device)
-    rc = _lib.lib().dpfs_embedding_bwd(ids_flat.data_ptr(), dout2.data_ptr(), dweight.data_ptr(), int(zero_first),
+    fn = _lib.lib().dpfs_embedding_bwd if dout2.dtype == F32 else _lib.lib().dpfs_embedding_bwd_bf16
+    rc = fn(ids_flat.data_ptr(), dout2.data_ptr(), dweight.data_ptr(), int(zero_first),
                                        local_vocab, ids_flat.numel(), D, vocab_start, vocab_end, _lib.stream())
     _lib.check(rc, "dpfs_embedding_bwd")
     return dweight

@@ -16,6 +16,7 @@ from . import _lib
 import os
 
 _WS = {}
+_WS_RETIRED = []   # outgrown split-K workspaces stay allocated (captured CUDA graphs hold their addresses)
 _DEFAULT_BN = int(os.environ.get("DPFS_GEMM_BN", "256"))
 _USE_2SM = os.environ.get("DPFS_GEMM_2SM", "1") == "1"
 
@@ -23,6 +24,8 @@ _USE_2SM = os.environ.get("DPFS_GEMM_2SM", "1") == "1"
 def _workspace(device, nfloats: int) -> torch.Tensor:
     ws = _WS.get(device)
     if ws is None or ws.numel() < nfloats:
+        if ws is not None:
+            _WS_RETIRED.append(ws)
         ws = torch.empty(max(nfloats, 1 << 22), dtype=torch.float32, device=device)
         _WS[device] = ws
     return ws

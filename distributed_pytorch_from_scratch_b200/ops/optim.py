@@ -6,6 +6,10 @@ itself is ONE kernel launch over the model's flat parameter arena; ``lr``/``beta
 small device buffer (refreshed by an async H2D copy), which makes the launch CUDA-graph capturable.  The same launch
 rewrites the bf16 shadow weights the tcgen05 GEMMs consume.
 
+The H2D copy reads its pinned source when the copy EXECUTES on the stream, not when it is enqueued, and the host runs
+many steps ahead of the GPU under graph replay.  Every step therefore writes its hyper-parameters into its own pinned
+slot of a ring; a slot is only rewritten after the event recorded behind its previous copy has completed.
+
 Off the fused path (CPU / parameters not in an arena) it runs the identical math with torch ops, so CPU tests can
 compare it against ``torch.optim.Adam`` directly.
 """
@@ -20,6 +24,8 @@ from . import fused
 
 
 class FusedAdam(torch.optim.Optimizer):
+    _RING = 64      # pinned hyper-parameter slots (steps the host may run ahead before it has to wait)
+
     def __init__(self, params, lr=1e-3, betas=(0.9, 0.999), eps=1e-8, weight_decay=0.0, arena=None):
         """``arena``: a models.fused_transformer.ParamArena (or None for the generic per-tensor torch fallback).
         ``weight_decay`` is decoupled (AdamW); with the reference's wd = 0 Adam == AdamW exactly."""
@@ -27,13 +33,14 @@ class FusedAdam(torch.optim.Optimizer):
         super().__init__(params, defaults)
         self.arena = arena
         self.step_count = 0
-        self._hyper_host: Optional[torch.Tensor] = None
+        self._hyper_host: Optional[torch.Tensor] = None   # [_RING, 8] pinned: one slot per in-flight step
         self._hyper_dev: Optional[torch.Tensor] = None
+        self._hyper_events = [None] * self._RING
         self._m = self._v = None
         if arena is not None:
             self._m = torch.zeros_like(arena.params)
             self._v = torch.zeros_like(arena.params)
-            self._hyper_host = torch.zeros(8, dtype=torch.float32)
+            self._hyper_host = torch.zeros(self._RING, 8, dtype=torch.float32)
             if arena.params.is_cuda:
                 self._hyper_host = self._hyper_host.pin_memory()
             self._hyper_dev = torch.zeros(8, dtype=torch.float32, device=arena.params.device)
@@ -64,8 +71,18 @@ class FusedAdam(torch.optim.Optimizer):
         t = self.step_count
         vals = [g["lr"], b1, b2, g["eps"], 1.0 - b1 ** t, 1.0 - b2 ** t, g["weight_decay"], 0.0]
         if self._hyper_host is not None:
-            self._hyper_host.copy_(torch.tensor(vals, dtype=torch.float32))
-            self._hyper_dev.copy_(self._hyper_host, non_blocking=True)
+            i = t % self._RING
+            ev = self._hyper_events[i]
+            if ev is not None:
+                ev.synchronize()          # the copy that last read this slot has executed (a no-op unless the host
+                                          # is more than _RING steps ahead of the GPU)
+            slot = self._hyper_host[i]
+            slot.copy_(torch.tensor(vals, dtype=torch.float32))
+            self._hyper_dev.copy_(slot, non_blocking=True)
+            if self._hyper_dev.is_cuda:
+                ev = ev or torch.cuda.Event()
+                ev.record()
+                self._hyper_events[i] = ev
         return vals
 
     def launch(self):

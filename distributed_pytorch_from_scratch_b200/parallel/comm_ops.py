@@ -40,6 +40,9 @@ def all_reduce_sum(t: torch.Tensor) -> torch.Tensor:
 def _all_gather_stacked(t: torch.Tensor, n: int, group) -> torch.Tensor:
     """(...) -> (n, ...) in rank order; one flat buffer, no per-rank list (the reference builds a zeros list + cat)."""
     t = t.contiguous()
+    symm = pm.pgm.symm
+    if symm is not None and t.is_cuda and symm.can_gather(t):
+        return symm.all_gather_rows(t)          # our own NVLink all-gather kernel (multimem.st / peer stores)
     flat = t.reshape(-1)
     out = torch.empty(n * flat.numel(), dtype=t.dtype, device=t.device)
     dist.all_gather_into_tensor(out, flat, group=group)

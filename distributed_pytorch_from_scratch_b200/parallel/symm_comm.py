@@ -30,6 +30,23 @@ from . import process_manager as pm
 BF16, F32 = torch.bfloat16, torch.float32
 
 
+class SymmZone:
+    """One region of a symmetric allocation: this rank's bytes, their multicast alias (0 without NVLS) and every
+    rank's address of the same region."""
+
+    def __init__(self, local_u8: torch.Tensor, mc_ptr: int, peer_ptrs):
+        self.local, self.mc, self.peer_ptrs = local_u8, mc_ptr, peer_ptrs
+        self.nbytes = local_u8.numel()
+
+    def view(self, shape, dtype=BF16) -> torch.Tensor:
+        numel = 1
+        for d in shape:
+            numel *= d
+        nbytes = numel * torch.empty((), dtype=dtype).element_size()
+        assert nbytes <= self.nbytes, "symmetric zone too small"
+        return self.local[:nbytes].view(dtype).view(*shape)
+
+
 class SymmComm:
     def __init__(self, data, data_hdl, flags, flags_hdl, rank, n):
         self.data, self.hdl = data, data_hdl
@@ -45,10 +62,10 @@ class SymmComm:
         self.gather_off = self.capacity - self.capacity // 16
         self.ag_off = (self.capacity // 2) // 256 * 256
         self.ag_bytes = self.gather_off - self.ag_off
-        # "push" all-gather (opt-in, DPFS_FUSE_AG=1, needs the multicast mapping): producers write their bf16 block
+        # "push" all-gather (needs the multicast mapping; DPFS_FUSE_AG=0 turns it off): producers write their bf16 block
         # straight into every rank's landing zone.  The landing area is then split: first half for the stand-alone
         # all-gather kernels, second half = two alternating push zones (see push_block).
-        self.push_enabled = bool(self.mc_base) and os.environ.get("DPFS_FUSE_AG", "0") == "1"
+        self.push_enabled = bool(self.mc_base) and os.environ.get("DPFS_FUSE_AG", "1") == "1"
         if self.push_enabled:
             half = (self.ag_bytes // 2) // 256 * 256
             self.push_off = self.ag_off + half
@@ -56,6 +73,7 @@ class SymmComm:
             self.ag_bytes = half
             self._push_zone = 0
         self.closed = False
+        self._zone_allocs = []
         # data path of the reduce: "p2p" (plain NVLink loads/stores, rank-ordered fp32 sums) or "nvls" (multimem.*)
         # Measured (profiles/comm_paths_r1.md): P2P wins at TP=2 (100 vs 116 us for 32.8 MB), NVLS wins at TP=8 (123 vs
         # 143 us; NCCL 158 us) because the switch-side reduction moves S(1+1/n) bytes instead of 2S(n-1)/n.
@@ -92,6 +110,23 @@ class SymmComm:
 
     def close(self):
         self.closed = True
+
+    # ------------------------------------------------------------------------------------------ activation zones
+    def alloc_zones(self, count: int, zone_bytes: int):
+        """``count`` persistent symmetric regions of ``zone_bytes`` each (one extra symmetric allocation, rendezvoused
+        over the TP group: every rank must call this at the same point with the same arguments).  Returns a list of
+        ``SymmZone``.  The sequence-parallel runtime keeps one zone per gathered activation that the backward pass
+        needs again (h1 / h2 of every layer), so nothing is cloned out of a recycled landing buffer."""
+        import torch.distributed._symmetric_memory as symm_mem
+        zone_bytes = (zone_bytes + 255) // 256 * 256
+        dev = self.data.device
+        buf = symm_mem.empty(count * zone_bytes, dtype=torch.uint8, device=dev)
+        hdl = symm_mem.rendezvous(buf, pm.pgm.tp_group.group_name)
+        mc = int(getattr(hdl, "multicast_ptr", 0) or 0)
+        ptrs = [int(x) for x in hdl.buffer_ptrs]
+        self._zone_allocs.append((buf, hdl))     # keep the allocation (and its peer mappings) alive
+        return [SymmZone(buf[i * zone_bytes:(i + 1) * zone_bytes], mc + i * zone_bytes if mc else 0,
+                         [q + i * zone_bytes for q in ptrs]) for i in range(count)]
 
     # ------------------------------------------------------------------------------------------ buffers
     def buffer(self, shape, dtype, offset_bytes: int = 0) -> torch.Tensor:
@@ -134,6 +169,11 @@ class SymmComm:
             out.copy_(work)
         return out
 
+    def can_gather(self, t: torch.Tensor) -> bool:
+        nbytes = t.numel() * t.element_size()
+        return (not self.closed and nbytes > 0 and nbytes % 16 == 0
+                and nbytes * self.n <= self.capacity - self.gather_off)
+
     def all_gather_rows(self, t: torch.Tensor) -> torch.Tensor:
         """(...) -> (n, ...), rank order; the result is a private copy."""
         t = t.contiguous()
@@ -150,13 +190,17 @@ class SymmComm:
         view = self.data[self.gather_off:self.gather_off + nbytes * self.n].view(t.dtype).view((self.n,) + t.shape)
         return view.clone()
 
-    def can_fuse_gemm_ar(self, a: torch.Tensor, w: torch.Tensor, b_mn_major: bool = False) -> bool:
-        if self.closed or a.dtype != BF16 or w.dtype != BF16 or self.mode != "p2p":
-            return False     # the in-kernel reduce uses the P2P data path; with NVLS the GEMM and the reduce stay split
-        M = a.shape[0]
-        N = w.shape[1] if b_mn_major else w.shape[0]
+    def can_fuse_shape(self, M: int, N: int) -> bool:
+        """Whether an [M, N] bf16 output can go through the fused GEMM + all-reduce kernel."""
+        if self.closed or self.n not in (2, 4, 8) or (self.mode == "nvls" and not self.mc_base):
+            return False
         tiles = ((M + 127) // 128) * ((N + 127) // 128)
-        return N % 8 == 0 and M * N * 2 <= self.ag_off and tiles <= 16384
+        return M > 0 and N % 8 == 0 and M * N * 2 <= self.ag_off and tiles <= 16384
+
+    def can_fuse_gemm_ar(self, a: torch.Tensor, w: torch.Tensor, b_mn_major: bool = False) -> bool:
+        if a.dtype != BF16 or w.dtype != BF16 or a.stride(0) % 8 or w.stride(0) % 8:
+            return False
+        return self.can_fuse_shape(a.shape[0], w.shape[1] if b_mn_major else w.shape[0])
 
     def gemm_allreduce(self, a: torch.Tensor, w: torch.Tensor, b_mn_major: bool = False, bn: int = 0) -> torch.Tensor:
         """all_reduce(a @ w^T) (or a @ w when ``b_mn_major``) in ONE kernel; the result is a view of the symmetric

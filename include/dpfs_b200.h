@@ -62,6 +62,33 @@ int dpfs_gemm_reduce_scatter_bf16(const void* A, long long lda, const void* B, l
                                   long long partial_offset, void* rs_out, int M, int N, int K,
                                   const unsigned long long* flag_ptrs, int rank, int n, int bn, cudaStream_t stream);
 
+/* ---- Sequence-parallel hand-offs: reduce-scatter -> row op -> all-gather in ONE kernel (csrc/sp_fused.cu) ------------
+ * mc_partial: MULTICAST alias of the [n * rows_per_rank][D] bf16 partial products every rank wrote at the same
+ * symmetric offset (the output of its row-parallel GEMM).  Rank r owns rows [r * rows_per_rank, (r+1) * rows_per_rank).
+ * One warp per row: multimem.ld_reduce pulls the switch-reduced row, the row op runs in registers, multimem.st pushes
+ * the bf16 result row into every rank's copy of the landing zone (mc_h / mc_dx: MULTICAST alias of [n * rpr][D] bf16).
+ * Two rank barriers (partials complete / results landed) per call.  D % 8 == 0, D <= 1024.
+ *
+ * forward:  xout_l = x_l + sum_r partial_r + bias (fp32, [rpr][D]; x_l / bias nullable), rstd_l[rpr],
+ *           h = rmsnorm(xout_l) * scale -> every rank.   mc_h == NULL: residual add only (no norm, no broadcast).
+ * ref: Reduce after the row-parallel GEMM + bias + residual + the next RMSNorm (models/comm_ops.py:39,
+ * models/layers.py:51-54, models/model.py:119-120); the reference has no sequence parallelism. */
+int dpfs_rs_add_rmsnorm_ag(const void* mc_partial, const float* x_l, const float* bias, const float* scale,
+                           float* xout_l, float* rstd_l, void* mc_h, int rows_per_rank, int D, float eps,
+                           const unsigned long long* flag_ptrs, int rank, int n, cudaStream_t stream);
+/* backward: dh = sum_r partial_r (this rank's rows of a column-parallel dgrad); dx = dres_l + rmsnorm'(dh) with the
+ * saved x_l / rstd_l; dx -> dx_l (fp32 private, nullable) and bf16 -> every rank (mc_dx, nullable).
+ * dscale_out[D] (+)= sum over this rank's rows of dh * xhat, dbias_out[D] (+)= column sums of dx over this rank's rows
+ * (both nullable; partial sums over LOCAL rows: the caller all-reduces them once per step).  scratch: fp32
+ * [dpfs_sp_blocks(rows_per_rank, D)][2 * D].
+ * ref: Copy.backward all-reduce after the dgrad GEMM (models/comm_ops.py:59) + RMSNorm backward. */
+int dpfs_rs_rmsnorm_bwd_ag(const void* mc_partial, const float* x_l, const float* rstd_l, const float* scale,
+                           const float* dres_l, float* dx_l, void* mc_dx, float* dscale_out, float* dbias_out,
+                           int accumulate, float* scratch, int rows_per_rank, int D,
+                           const unsigned long long* flag_ptrs, int rank, int n, cudaStream_t stream);
+int dpfs_sp_blocks(int rows_per_rank, int D);
+
+
 /* Host-only (no GPU): the work items (heavy-first list positions) CTA `bid` of `grid` persistent attention CTAs
  * processes, in order; snake != 0 = the reversed-odd-rounds order of the opt-in kernels.  Returns the count. */
 int dpfs_debug_attn_items(int n_items, int grid, int bid, int snake, int* out, int cap);
@@ -193,6 +220,7 @@ int dpfs_cast_colsum(const float* x, void* y, float* colsum, int accumulate, flo
  * fixed array that is part of the library image, so nothing is allocated (no cudaMalloc / cudaFree / allocating
  * library call).  This entry point has no counterpart in the reference.
  *   - Limit: ceil(M / 64) * N <= DPFS_COLSUM_STATIC_MAX_FLOATS; larger problems return -25 and launch nothing.
+ *   - x must be 16-byte aligned (-26 otherwise: the kernel reads 16-byte vectors) and M <= 65535 * 64 rows (-27).
  *   - Cost: the array (8 MiB) is resident on every GPU that loads the library until the process exits.
  *   - The first call on a device resolves the array's device address; make that first call before any stream
  *     capture on that device.
@@ -215,6 +243,10 @@ int dpfs_embedding_fwd_mc(const long long* ids, const float* weight, void* out_m
 int dpfs_embedding_bwd(const long long* ids, const float* dout, float* dweight, int zero_first,
                        long long local_vocab, int M, int D, long long vocab_start, long long vocab_end,
                        cudaStream_t stream);
+/* same, dout is bf16 [M][D] */
+int dpfs_embedding_bwd_bf16(const long long* ids, const void* dout_bf16, float* dweight, int zero_first,
+                            long long local_vocab, int M, int D, long long vocab_start, long long vocab_end,
+                            cudaStream_t stream);
 
 /* ---- Vocab-parallel softmax cross-entropy ------------------------------------------------------------------------
  * Phase 1 (dpfs_ce_stats): stats[m] = {max, sum exp(x - max), target logit if owned} over the local shard

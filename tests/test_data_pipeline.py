@@ -26,7 +26,7 @@ def test_preprocess_tokenizer_pretokenize(tmp_path):
     pd.DataFrame({"text": docs, "other": range(len(docs))}).to_parquet(pq)
     out = _run([os.path.join(REPO, "preprocess_data.py"), str(pq), str(tmp_path / "data.json"), "--seed", "0"],
                str(tmp_path))
-    assert "Training samples:" in out
+    assert "train:" in out and "validation:" in out and "documents" in out
     data = json.load(open(tmp_path / "data.json"))
     assert set(data) == {"train", "validation"} and len(data["train"]) + len(data["validation"]) == len(docs) - 1
     assert len(data["validation"]) >= 1 and all(len(d) <= 2000 for d in data["train"])
@@ -37,7 +37,7 @@ def test_preprocess_tokenizer_pretokenize(tmp_path):
     assert [tok.token_to_id(t) for t in ("<BOS>", "<EOS>", "<UNK>")] == [0, 1, 2] and tok.get_vocab_size() <= 300
     out = _run([os.path.join(REPO, "pre_tokenize.py"), "-i", "data.json", "-o", "tokens.json", "-t", "tok.json"],
                str(tmp_path))
-    assert "Split: train" in out and "Avg num_tokens" in out
+    assert "train:" in out and "mean" in out and "longest" in out
     tk = json.load(open(tmp_path / "tokens.json"))
     assert set(tk) == {"train", "validation", "special_ids", "vocab_size"}
     assert tk["special_ids"] == {"<BOS>": 0, "<EOS>": 1, "<UNK>": 2} and tk["vocab_size"] == tok.get_vocab_size()

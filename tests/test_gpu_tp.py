@@ -53,11 +53,16 @@ def _comm_worker(rank, world):
     for (M, N, K, bmn) in [(1000, 512, 256, False), (4096, 512, 768, True)]:
         a = torch.randn(M, K, device="cuda").to(torch.bfloat16)
         w = (torch.randn(K, N, device="cuda") if bmn else torch.randn(N, K, device="cuda")).to(torch.bfloat16)
-        ref = gemm_nt(a, w, b_mn_major=bmn, out_dtype=torch.float32)
+        # oracle: plain PyTorch fp32 matmul of the same bf16 operands + NCCL sum
+        ref = a.float() @ (w.float() if bmn else w.float().t())
         dist.all_reduce(ref)
-        for _ in range(3):      # repeated calls reuse the same semaphores
-            out = symm.gemm_allreduce(a, w, b_mn_major=bmn).clone()
-        assert (out.float() - ref).abs().max().item() < 0.03 * ref.abs().max().item()
+        for mode in (["p2p", "nvls"] if symm.mc_base else ["p2p"]):
+            symm.mode = mode
+            assert symm.can_fuse_gemm_ar(a, w, bmn), mode
+            for _ in range(3):      # repeated calls reuse the same semaphores
+                out = symm.gemm_allreduce(a, w, b_mn_major=bmn).clone()
+            assert (out.float() - ref).abs().max().item() < 0.03 * ref.abs().max().item(), mode
+        symm.mode = "p2p"
 
 
 def _fused_rs_worker(rank, world):
@@ -74,7 +79,7 @@ def _fused_rs_worker(rank, world):
                                (128 * world, 256, 64, False)]:
             a = torch.randn(M, K, device="cuda").to(torch.bfloat16)
             w = (torch.randn(K, N, device="cuda") if bmn else torch.randn(N, K, device="cuda")).to(torch.bfloat16)
-            ref = gemm_nt(a, w, b_mn_major=bmn, out_dtype=torch.float32)
+            ref = a.float() @ (w.float() if bmn else w.float().t())     # fp32 PyTorch oracle
             dist.all_reduce(ref)
             rows = M // world
             ref = ref[rank * rows:(rank + 1) * rows]
@@ -135,6 +140,65 @@ def _push_worker(rank, world):
     torch.cuda.synchronize()
 
 
+def _handoff_worker(rank, world):
+    """One-kernel sequence-parallel hand-offs (reduce-scatter -> row op -> all-gather, csrc/sp_fused.cu) against the
+    same maths in plain PyTorch fp32 on the NCCL-summed partials; several rounds re-use the barrier semaphores."""
+    import torch.distributed as dist
+    from distributed_pytorch_from_scratch_b200.ops import fused
+    from distributed_pytorch_from_scratch_b200.parallel.symm import try_enable_symm
+    symm = try_enable_symm(required=True)
+    if not symm.mc_base:
+        return      # no NVLS multicast on this box
+    torch.manual_seed(400 + rank)
+
+    def gather(t):
+        out = torch.empty((world * t.shape[0],) + tuple(t.shape[1:]), dtype=t.dtype, device=t.device)
+        dist.all_gather_into_tensor(out, t.contiguous())
+        return out
+
+    for (Ml, D) in [(250, 512), (129, 256), (64, 1024)]:
+        M = Ml * world
+        zones = symm.alloc_zones(2, M * D * 2)
+        for rnd in range(3):
+            part = symm.buffer((M, D), torch.bfloat16)
+            mine = torch.randn(M, D, device="cuda").to(torch.bfloat16)
+            part.copy_(mine)
+            total = mine.float()
+            dist.all_reduce(total)
+            y_l = total[rank * Ml:(rank + 1) * Ml].to(torch.bfloat16).float()    # the switch rounds the sum to bf16
+            x_l = torch.randn(Ml, D, device="cuda")
+            bias, scale = torch.randn(D, device="cuda"), torch.rand(D, device="cuda") + 0.5
+            # ---- forward
+            xo, h, rstd = fused.rs_add_rmsnorm_ag(symm, part, x_l, bias, scale, 1e-5, zones[0])
+            xo_ref = x_l + y_l + bias
+            rstd_ref = torch.rsqrt(xo_ref.pow(2).mean(-1) + 1e-5)
+            h_ref = gather((xo_ref * rstd_ref[:, None] * scale).to(torch.bfloat16))
+            # the in-switch fp32 sum may round differently from NCCL's: allow one bf16 ulp of the partial sum
+            assert (xo - xo_ref).abs().max().item() < 0.07, (Ml, D, rnd)
+            assert (rstd - rstd_ref).abs().max().item() < 2e-3 * rstd_ref.abs().max().item()
+            assert (h.float() - h_ref.float()).abs().max().item() < 0.06, (Ml, D, rnd)
+            assert torch.equal(h, gather(h[rank * Ml:(rank + 1) * Ml])), "ranks disagree on the gathered rows"
+            # embedding hand-off: no residual, no bias
+            part.copy_(mine)
+            xo2, h2, _ = fused.rs_add_rmsnorm_ag(symm, part, None, None, scale, 1e-5, zones[1])
+            assert (xo2 - y_l).abs().max().item() < 0.07
+            # ---- backward
+            part.copy_(mine)
+            dres = torch.randn(Ml, D, device="cuda")
+            ds, db = torch.empty(D, device="cuda"), torch.empty(D, device="cuda")
+            dx_l, dx = fused.rs_rmsnorm_bwd_ag(symm, part, x_l, rstd_ref, scale, dres, zones[1], ds, db)
+            xh = x_l * rstd_ref[:, None]
+            g = y_l * scale
+            dx_ref = dres + rstd_ref[:, None] * (g - xh * (g * xh).mean(-1, keepdim=True))
+            assert (dx_l - dx_ref).abs().max().item() < 0.05 * max(1.0, dx_ref.abs().max().item()), (Ml, D, rnd)
+            assert (dx.float() - gather(dx_ref.to(torch.bfloat16)).float()).abs().max().item() \
+                < 0.05 * max(1.0, dx_ref.abs().max().item())
+            ds_ref, db_ref = (y_l * xh).sum(0), dx_ref.sum(0)
+            assert (ds - ds_ref).abs().max().item() < 0.02 * ds_ref.abs().max().item() + 0.05
+            assert (db - db_ref).abs().max().item() < 0.02 * db_ref.abs().max().item() + 0.05
+    torch.cuda.synchronize()
+
+
 def _model_worker(rank, world, comm, sp=False):
     import process_manager as pm
     from distributed_pytorch_from_scratch_b200.engine import TrainStep
@@ -154,9 +218,10 @@ def _model_worker(rank, world, comm, sp=False):
     torch.set_rng_state(state); torch.cuda.set_rng_state(cstate)
     van.reset_parameters()
     g = torch.Generator().manual_seed(1)
-    ids = torch.randint(3, 1024, (4, 200), generator=g).cuda()
-    tgt = torch.randint(3, 1024, (4, 200), generator=g).cuda()
-    pos = torch.arange(200, device="cuda").unsqueeze(0).repeat(4, 1)
+    B = 4 if world <= 4 else 8          # >= 128 rows per rank so the fused GEMM -> reduce-scatter path is eligible
+    ids = torch.randint(3, 1024, (B, 200), generator=g).cuda()
+    tgt = torch.randint(3, 1024, (B, 200), generator=g).cuda()
+    pos = torch.arange(200, device="cuda").unsqueeze(0).repeat(B, 1)
     ref_logits = van(ids, pos)
     ref = torch.nn.functional.cross_entropy(ref_logits.view(-1, 1024), tgt.view(-1))
     ref.backward()
@@ -175,7 +240,7 @@ def _model_worker(rank, world, comm, sp=False):
     assert (model.norm.scale.grad - van.norm.scale.grad).norm().item() / van.norm.scale.grad.norm().item() < 0.05
     with torch.no_grad():
         lg = model(ids, pos).float()
-    assert lg.shape == (4, 200, 1024) and (lg - ref_logits).abs().max().item() < 0.08
+    assert lg.shape == (B, 200, 1024) and (lg - ref_logits).abs().max().item() < 0.08
     # a few optimizer steps through the engine (CUDA graph when our own collectives are active); a fresh model, as
     # in train.py: the step is captured before any eager backward has run on the default stream
     del model
@@ -190,39 +255,39 @@ def _model_worker(rank, world, comm, sp=False):
     assert losses[-1] < losses[0] - 0.2, losses
 
 
-@pytest.mark.skipif(_ngpu() < 2, reason="needs >= 2 GPUs")
-def test_symm_collectives_and_fused_gemm_allreduce():
-    run_distributed(_comm_worker, 2, free_port(), backend="nccl")
+def _worlds():
+    """TP sizes to run: every power of two the box has GPUs for (the driver's test lease has one GPU -> all skipped
+    there; the committed logs under profiles/ are from 2- and 8-GPU boxes)."""
+    return [pytest.param(n, marks=pytest.mark.skipif(_ngpu() < n, reason=f"needs >= {n} GPUs")) for n in (2, 4, 8)]
 
 
-@pytest.mark.skipif(_ngpu() < 2, reason="needs >= 2 GPUs")
-@pytest.mark.skipif(os.environ.get("DPFS_TEST_EXPERIMENTAL", "0") != "1",
-                    reason="fused GEMM -> reduce-scatter is opt-in (DPFS_FUSE_RS=1) and has not been run on hardware "
-                           "yet: set DPFS_TEST_EXPERIMENTAL=1 to include it")
-def test_fused_gemm_reduce_scatter():
-    run_distributed(_fused_rs_worker, 2, free_port(), backend="nccl")
+@pytest.mark.parametrize("world", _worlds())
+def test_symm_collectives_and_fused_gemm_allreduce(world):
+    run_distributed(_comm_worker, world, free_port(), backend="nccl")
 
 
-@pytest.mark.skipif(_ngpu() < 2, reason="needs >= 2 GPUs")
-@pytest.mark.skipif(os.environ.get("DPFS_TEST_EXPERIMENTAL", "0") != "1",
-                    reason="pushed all-gathers are opt-in (DPFS_FUSE_AG=1) and have not been run on hardware yet: "
-                           "set DPFS_TEST_EXPERIMENTAL=1 to include them")
-def test_push_allgather_producers():
-    run_distributed(_push_worker, 2, free_port(), backend="nccl")
+@pytest.mark.parametrize("world", _worlds())
+def test_fused_gemm_reduce_scatter(world):
+    run_distributed(_fused_rs_worker, world, free_port(), backend="nccl")
 
 
-@pytest.mark.skipif(_ngpu() < 2, reason="needs >= 2 GPUs")
+@pytest.mark.parametrize("world", _worlds())
+def test_push_allgather_producers(world):
+    run_distributed(_push_worker, world, free_port(), backend="nccl")
+
+
+@pytest.mark.parametrize("world", _worlds())
+def test_sp_handoff_kernels(world):
+    run_distributed(_handoff_worker, world, free_port(), backend="nccl")
+
+
+@pytest.mark.parametrize("world", _worlds())
 @pytest.mark.parametrize("comm", ["nccl", "fused"])
-def test_tp2_fused_transformer_matches_oracle(comm):
-    run_distributed(_model_worker, 2, free_port(), backend="nccl", args=(comm,))
+def test_fused_transformer_matches_oracle(world, comm):
+    run_distributed(_model_worker, world, free_port(), backend="nccl", args=(comm,))
 
 
-@pytest.mark.skipif(_ngpu() < 2, reason="needs >= 2 GPUs")
+@pytest.mark.parametrize("world", _worlds())
 @pytest.mark.parametrize("comm", ["nccl", "fused"])
-def test_tp2_sequence_parallel_matches_oracle(comm):
-    run_distributed(_model_worker, 2, free_port(), backend="nccl", args=(comm, True))
-
-
-@pytest.mark.skipif(_ngpu() < 4, reason="needs >= 4 GPUs")
-def test_tp4_fused_transformer_matches_oracle():
-    run_distributed(_model_worker, 4, free_port(), backend="nccl", args=("fused",))
+def test_sequence_parallel_matches_oracle(world, comm):
+    run_distributed(_model_worker, world, free_port(), backend="nccl", args=(comm, True))

@@ -110,6 +110,62 @@ def test_fused_adam_equals_torch_adam_on_model():
     assert torch.equal(arena.shadow, arena.params.to(torch.bfloat16))
 
 
+def test_fused_adam_no_host_sync_matches_torch_adam_onecycle():
+    """48 optimizer steps enqueued WITHOUT any host synchronisation (the host runs far ahead of the GPU, as it does
+    under CUDA-graph replay) must use each step's own lr / beta1 / bias corrections: compare with torch.optim.Adam +
+    OneCycleLR (reference train.py:83-84,106-109) fed the same gradients.  A single reused pinned staging buffer fails
+    this (the async H2D copy reads the host memory when it executes, not when it is enqueued)."""
+    from distributed_pytorch_from_scratch_b200.ops.optim import FusedAdam
+    m = _model(seed=7)
+    m.compute_dtype = torch.bfloat16
+    opt = FusedAdam.for_model(m, lr=3e-4)
+    arena = opt.arena
+    assert arena is not None
+    steps, total = 48, 60
+    sched = torch.optim.lr_scheduler.OneCycleLR(opt, 3e-4, total, pct_start=0.25)
+    opt._opt_called = True
+    ref = torch.nn.Parameter(arena.params.detach().clone())
+    ropt = torch.optim.Adam([ref], lr=3e-4)
+    rsched = torch.optim.lr_scheduler.OneCycleLR(ropt, 3e-4, total, pct_start=0.25)
+    gen = torch.Generator(device="cuda").manual_seed(11)
+    grads = [torch.randn(arena.numel, device="cuda", generator=gen) * 0.01 for _ in range(steps)]
+    # something long-running in front, so every one of the 48 hyper-parameter uploads is enqueued before the first runs
+    big = torch.randn(8192, 8192, device="cuda")
+    for _ in range(20):
+        big = big @ big * 1e-4
+    for t in range(steps):          # no .item(), no synchronize inside the loop
+        arena.grads.copy_(grads[t])
+        opt.update_hyper()
+        opt.launch()
+        sched.step()
+    for t in range(steps):
+        ref.grad = grads[t].clone()
+        ropt.step()
+        rsched.step()
+    torch.cuda.synchronize()
+    err = (arena.params - ref.data).abs().max().item()
+    assert torch.allclose(arena.params, ref.data, atol=2e-6, rtol=1e-5), err     # a stale-hyper step is off by ~1e-4
+    # and through the engine: graph replay without host syncs == the same run with a sync after every step
+    from distributed_pytorch_from_scratch_b200.engine import TrainStep
+    ids, pos, tgt = _batch()
+    finals = []
+    for sync in (False, True):
+        m2 = _model(seed=9)
+        m2.compute_dtype = torch.bfloat16
+        o2 = FusedAdam.for_model(m2, lr=1e-3)
+        s2 = torch.optim.lr_scheduler.OneCycleLR(o2, 1e-3, 64, pct_start=0.25)
+        o2._opt_called = True
+        step = TrainStep(m2, o2, s2, use_graph=True)
+        shape, bufs = step.load_batch(ids, pos, tgt)
+        for _ in range(40):
+            step.run_loaded(shape, bufs)
+            if sync:
+                torch.cuda.synchronize()
+        torch.cuda.synchronize()
+        finals.append(o2.arena.params.detach().clone())
+    assert torch.equal(finals[0], finals[1]), (finals[0] - finals[1]).abs().max().item()
+
+
 def test_checkpoint_roundtrip_from_arena(tmp_path):
     from distributed_pytorch_from_scratch_b200.utils import checkpoint as C
     m = _model(seed=7)

@@ -1,9 +1,14 @@
-"""Per-kernel time breakdown of one eager (no CUDA graph) training step of the default model at TP=1.
+"""Per-kernel time breakdown of one training step of the default model at TP = WORLD_SIZE (1 when run without torchrun).
 
-Uses torch.profiler (CUPTI activity records, a few percent overhead) only to apportion time between kernels;
-the step time itself is always taken from bench.py, never from a profiled run.
-Writes gpurun_out/step_profile.md.
+    python tools/gpu_step_profile.py [--sp on|off|auto] [--eager] [--tag NAME]
+    python -m torch.distributed.run --nproc-per-node 8 --master-addr 127.0.0.1 tools/gpu_step_profile.py --sp on
+
+Uses torch.profiler (CUPTI activity records, a few percent overhead) only to apportion time between kernels; the
+step time itself is always taken from bench.py, never from a profiled run.  By default the profiled step is a CUDA
+graph replay (what bench.py times): in-kernel waits for peers are then the real skew, not Python launch jitter.
+Rank 0 writes gpurun_out/step_profile_tp{N}{tag}.md.
 """
+import argparse
 import os
 import re
 import sys
@@ -28,59 +33,87 @@ def short(name: str) -> str:
     name = re.sub(r"^void\s+", "", name)
     name = name.replace("dpfs::", "").replace("(anonymous namespace)::", "")
     name = re.sub(r"\(.*$", "", name)
-    name = name.replace("__nv_bfloat16", "bf16").replace("(bool)1", "MN").replace("(bool)0", "K").replace("(int)", "")
-    return name[:90]
+    name = name.replace("__nv_bfloat16", "bf16").replace("(bool)1", "T").replace("(bool)0", "F").replace("(int)", "")
+    return name[:110]
 
 
 def main():
-    torch.cuda.set_device(0)
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--sp", default="auto")
+    ap.add_argument("--eager", action="store_true")
+    ap.add_argument("--tag", default="")
+    args = ap.parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
     os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
     os.environ.setdefault("MASTER_PORT", "29617")
-    torch.distributed.init_process_group("nccl", rank=0, world_size=1)
+    torch.distributed.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", local))
     set_seed(0)
-    pm.init_pgm(1)
+    pm.init_pgm(world)
+    if world > 1:
+        from distributed_pytorch_from_scratch_b200.parallel.symm import try_enable_symm
+        try_enable_symm(required=True)
+    sp = world > 1 and (args.sp == "on" or (args.sp == "auto" and world >= 8))
     margs = ModelArgumments()
-    model = Transformer(**asdict(margs)).cuda()
+    model = Transformer(**asdict(margs), sequence_parallel=sp).cuda()
     model.reset_parameters()
     model.compute_dtype = torch.bfloat16
     model.train()
     opt = FusedAdam.for_model(model, lr=3e-4)
     sched = OneCycleLR(opt, 3e-4, 10000, pct_start=0.04)
     opt._opt_called = True
-    step = TrainStep(model, opt, sched, ignore_index=IGNORE_INDEX, use_graph=False)
+    step = TrainStep(model, opt, sched, ignore_index=IGNORE_INDEX, use_graph=not args.eager)
     B, T = 32, 1000
     g = torch.Generator().manual_seed(1234)
     ids = torch.randint(3, margs.vocab_size, (B, T), generator=g)
     pos = torch.arange(T).repeat(B, 1)
     tgt = torch.roll(ids, -1, dims=1)
     shape, bufs = step.load_batch(ids, pos, tgt)
-    for _ in range(3):
+    for _ in range(4):
         step.run_loaded(shape, bufs)
     torch.cuda.synchronize()
+    torch.distributed.barrier()
+    torch.cuda.synchronize()
     from torch.profiler import ProfilerActivity, profile
+    nprof = 3
     with profile(activities=[ProfilerActivity.CUDA]) as prof:
-        step.run_loaded(shape, bufs)
+        for _ in range(nprof):
+            step.run_loaded(shape, bufs)
         torch.cuda.synchronize()
     tot = defaultdict(lambda: [0.0, 0])
+    t_first, t_last = None, None
     for ev in prof.events():
         if ev.device_type == torch.autograd.DeviceType.CUDA:
             d = getattr(ev, "device_time", None)
             if d is None:
                 d = ev.cuda_time
-            tot[short(ev.name)][0] += d
+            tot[short(ev.name)][0] += d / nprof
             tot[short(ev.name)][1] += 1
+            tr = ev.time_range
+            t_first = tr.start if t_first is None else min(t_first, tr.start)
+            t_last = tr.end if t_last is None else max(t_last, tr.end)
     total = sum(v[0] for v in tot.values())
-    lines = ["# Kernel-time breakdown of one eager training step (TP=1, default model, b32 x t1000, bf16)", "",
-             f"CUPTI activity records via torch.profiler; sum of kernel time {total / 1e3:.2f} ms over "
-             f"{sum(v[1] for v in tot.values())} device activities.", "",
-             "| time (ms) | share | launches | us / launch | kernel |", "|---|---|---|---|---|"]
+    span = (t_last - t_first) / nprof if t_first is not None else 0.0
+    mode = "eager" if args.eager else "CUDA-graph replay"
+    lines = [f"# Kernel-time breakdown of one training step (TP={world}{'+SP' if sp else ''}, rank 0, {mode}, default "
+             f"model, b32 x t1000, bf16)", "",
+             f"CUPTI activity records via torch.profiler, mean of {nprof} steps; sum of kernel time "
+             f"{total / 1e3:.2f} ms, first-to-last activity span {span / 1e3:.2f} ms per step, "
+             f"{sum(v[1] for v in tot.values()) // nprof} device activities per step.  Environment switches: "
+             + (", ".join(f"{k}={v}" for k, v in sorted(os.environ.items()) if k.startswith("DPFS_")) or "none") + ".",
+             "", "| time (ms) | share | launches | us / launch | kernel |", "|---|---|---|---|---|"]
     for name, (t, n) in sorted(tot.items(), key=lambda kv: -kv[1][0]):
-        lines.append(f"| {t / 1e3:.3f} | {100 * t / total:.1f}% | {n} | {t / n:.1f} | {name} |")
-    os.makedirs(os.path.join(REPO, "gpurun_out"), exist_ok=True)
+        n1 = n / nprof
+        lines.append(f"| {t / 1e3:.3f} | {100 * t / total:.1f}% | {n1:g} | {t / n1:.1f} | {name} |")
     out = "\n".join(lines) + "\n"
-    with open(os.path.join(REPO, "gpurun_out", "step_profile.md"), "w") as f:
-        f.write(out)
-    print(out)
+    if rank == 0:
+        os.makedirs(os.path.join(REPO, "gpurun_out"), exist_ok=True)
+        with open(os.path.join(REPO, "gpurun_out", f"step_profile_tp{world}{args.tag}.md"), "w") as f:
+            f.write(out)
+        print(out)
+    torch.distributed.barrier()
     torch.distributed.destroy_process_group()
 
 
