@@ -160,7 +160,9 @@ __device__ __forceinline__ uint4 add_bf16x8(uint4 a, uint4 b) {
 }
 __global__ void __launch_bounds__(512) allreduce_exp_kernel(CommCtx c, PeerPtrs peers, uint8_t* mc_base, long long off,
                                                             long long units, int mode) {
-  sync_ranks(c, blockIdx.x);
+  const bool nosync = (mode & 16) != 0;   // timing experiments on concurrent streams: no barriers (flags are per block)
+  mode &= 15;
+  if (!nosync) sync_ranks(c, blockIdx.x);
   const long long per = (units + c.n - 1) / c.n;
   const long long u0 = per * c.rank;
   const long long u1 = min(units, u0 + per);
@@ -205,7 +207,7 @@ __global__ void __launch_bounds__(512) allreduce_exp_kernel(CommCtx c, PeerPtrs 
       }
     }
   }
-  sync_ranks(c, blockIdx.x);
+  if (!nosync) sync_ranks(c, blockIdx.x);
 }
 
 // all-gather over plain peer stores (used when the buffers have no multicast mapping)
@@ -223,6 +225,10 @@ __global__ void __launch_bounds__(512) allgather_p2p_kernel(CommCtx c, PeerPtrs 
 
 // rank-wide barrier only (used by tests and to order non-kernel accesses)
 __global__ void barrier_kernel(CommCtx c) { sync_ranks(c, blockIdx.x); }
+// `reps` back-to-back barriers in every block (micro-benchmark of the barrier itself)
+__global__ void barrier_reps_kernel(CommCtx c, int reps) {
+  for (int i = 0; i < reps; ++i) sync_ranks(c, blockIdx.x);
+}
 
 static CommCtx make_ctx(const unsigned long long* flag_ptrs, int rank, int n) {
   CommCtx c;
@@ -369,6 +375,14 @@ extern "C" int dpfs_comm_barrier(const unsigned long long* flag_ptrs, int rank, 
   if (n < 2 || n > kMaxRanks) return -50;
   CommCtx c = make_ctx(flag_ptrs, rank, n);
   barrier_kernel<<<(DPFS_COUNT(), 1), 32, 0, stream>>>(c);
+  return static_cast<int>(cudaGetLastError());
+}
+
+extern "C" int dpfs_comm_barrier_ex(const unsigned long long* flag_ptrs, int rank, int n, int blocks, int threads,
+                                    int reps, cudaStream_t stream) {
+  if (n < 2 || n > kMaxRanks || blocks < 1 || blocks > kMaxBlocks || threads < 32 || threads > 1024) return -50;
+  CommCtx c = make_ctx(flag_ptrs, rank, n);
+  barrier_reps_kernel<<<(DPFS_COUNT(), blocks), threads, 0, stream>>>(c, reps);
   return static_cast<int>(cudaGetLastError());
 }
 

@@ -629,11 +629,12 @@ __global__ void colsum_partial_kernel(const __nv_bfloat16* __restrict__ x, long 
 __global__ void __launch_bounds__(128) swiglu_bwd_colsum_kernel(const __nv_bfloat16* __restrict__ dact,
                                                                 const __nv_bfloat16* __restrict__ gu,
                                                                 __nv_bfloat16* __restrict__ dgu,
-                                                                float* __restrict__ scratch, int M, int F) {
+                                                                float* __restrict__ scratch, int M, int F,
+                                                                int strip_rows) {
   const int cg = blockIdx.x * blockDim.x + threadIdx.x;
   if (cg * 8 >= F) return;
-  const int r0 = blockIdx.y * kColsumRowsPerBlock;
-  const int r1 = min(M, r0 + kColsumRowsPerBlock);
+  const int r0 = blockIdx.y * strip_rows;
+  const int r1 = min(M, r0 + strip_rows);
   float sg[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f}, su[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
 #pragma unroll 4
   for (int r = r0; r < r1; ++r) {
@@ -978,15 +979,32 @@ extern "C" int dpfs_colsum_bf16(const void* x, long long ld, float* out, int acc
 
 
 // dgu = swiglu backward; bias_grad[2F] (+)= column sums of dgu.  scratch: dpfs_colsum_scratch_floats(M, 2F) floats.
+// Strip height of the fused SwiGLU backward: a thread walks one 8-column group down a strip, so a narrow F (high TP
+// degree) has few threads per strip -- shorter strips keep the number of threads in flight up (F = 256: 32 threads per
+// strip, 16-row strips -> 2000 blocks for M = 32000 instead of 500 three-quarters-empty ones).
+static inline int swiglu_strip_rows(int F) {
+  const int groups = F / 8;
+  if (groups >= 128) return kColsumRowsPerBlock;
+  const int r = kColsumRowsPerBlock * groups / 128;
+  return r < 8 ? 8 : r;
+}
+extern "C" int dpfs_swiglu_bwd_scratch_floats(int M, int F) {
+  const int rows = swiglu_strip_rows(F);
+  return ((M + rows - 1) / rows) * 2 * F;
+}
 extern "C" int dpfs_swiglu_bwd_bias(const void* dact, const void* gu, void* dgu, float* bias_grad, int accumulate,
                                     float* scratch, int M, int F, cudaStream_t stream) {
   if (F % 8 != 0) return -21;
   if (M <= 0) return 0;
-  const int strips = (M + kColsumRowsPerBlock - 1) / kColsumRowsPerBlock;
-  dim3 grid((F / 8 + 127) / 128, strips);
-  swiglu_bwd_colsum_kernel<<<(DPFS_COUNT(), grid), 128, 0, stream>>>((const __nv_bfloat16*)dact,
-                                                                    (const __nv_bfloat16*)gu, (__nv_bfloat16*)dgu,
-                                                                    scratch, M, F);
+  const int rows = swiglu_strip_rows(F);
+  const int strips = (M + rows - 1) / rows;
+  if (strips > 65535) return -27;
+  const int groups = F / 8;
+  const int threads = groups >= 128 ? 128 : ((groups + 31) / 32) * 32;
+  dim3 grid((groups + threads - 1) / threads, strips);
+  swiglu_bwd_colsum_kernel<<<(DPFS_COUNT(), grid), threads, 0, stream>>>((const __nv_bfloat16*)dact,
+                                                                        (const __nv_bfloat16*)gu, (__nv_bfloat16*)dgu,
+                                                                        scratch, M, F, rows);
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) return static_cast<int>(e);
   reduce_partials_kernel<<<(DPFS_COUNT(), (2 * F + 31) / 32), kReduceGroups * 32, 0, stream>>>(scratch, bias_grad, strips, 2 * F,

@@ -21,6 +21,57 @@ namespace dpfs {
 
 int num_sms();
 
+// ---- rank barrier of a whole grid ---------------------------------------------------------------------------------
+// sync_ranks (comm.cuh) pairs block b of every rank: n remote atomics per block, ~1000 per barrier at 125 blocks.
+// Here the blocks of ONE grid first meet on a local counter; the last one to arrive does a single n-way exchange with
+// its peers and then releases the others -- 8 remote atomics per rank per barrier.  Needs every block of the grid
+// resident at once (sp_grid caps the grid at the occupancy limit).  bar_mode: 0 = per-block barriers, 1 = this one,
+// 2 = none (timing experiments only: the result is garbage).
+__device__ unsigned int g_grid_count = 0;
+__device__ unsigned int g_grid_gen = 0;
+
+__device__ __forceinline__ unsigned int ld_acquire_gpu(const unsigned int* p) {
+  unsigned int v;
+  asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void sync_ranks_grid(const CommCtx& c) {
+  __shared__ int s_last;
+  __threadfence_system();  // this thread's stores (plain and multimem) are performed system-wide
+  __syncthreads();
+  unsigned int gen = 0;
+  if (threadIdx.x == 0) {
+    gen = ld_acquire_gpu(&g_grid_gen);  // read before arriving: the release of THIS barrier flips it
+    unsigned int prev;
+    asm volatile("atom.acq_rel.gpu.global.add.u32 %0, [%1], 1;" : "=r"(prev) : "l"(&g_grid_count) : "memory");
+    s_last = prev == gridDim.x - 1;
+  }
+  __syncthreads();
+  if (s_last) {
+    if (threadIdx.x < c.n) {
+      const int peer = threadIdx.x;
+      put_signal(c.flags[peer] + c.rank);   // slot 0 of the block-barrier region
+      wait_signal(c.flags[c.rank] + peer);
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      g_grid_count = 0;
+      __threadfence();
+      asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(&g_grid_gen), "r"(gen + 1) : "memory");
+    }
+  } else if (threadIdx.x == 0) {
+    const uint64_t t0 = globaltimer_ns();
+    while (ld_acquire_gpu(&g_grid_gen) == gen) {
+      if (globaltimer_ns() - t0 > kSpinTimeoutNs) __trap();
+    }
+  }
+  __syncthreads();
+}
+__device__ __forceinline__ void sp_barrier(const CommCtx& c, int bar_mode) {
+  if (bar_mode == 0) sync_ranks(c, blockIdx.x);
+  else if (bar_mode == 1) sync_ranks_grid(c);
+}
+
 // Block shape: T threads = T / 32 warps, each owns whole rows (512 threads for D <= 512, 256 for the wider rows, whose
 // per-lane accumulators need more than 128 registers).
 
@@ -53,13 +104,12 @@ __device__ __forceinline__ void st8f(float* p, const float (&f)[8]) {
 //   mc_part : multicast alias of the partial matrix [n * rpr][D] bf16 (row r0 + i of it is this rank's row i)
 //   x_l     : fp32 [rpr][D] residual or nullptr (treated as zero: the embedding hand-off)
 //   mc_h    : multicast alias of the landing zone [n * rpr][D] bf16, or nullptr (no norm wanted)
-//   h_local : optional private bf16 [rpr][D] copy of this rank's h rows (nullptr = none)
 template <int NC, int R, int T>
 __global__ void __launch_bounds__(T) rs_add_rmsnorm_ag_kernel(
     CommCtx c, const uint8_t* __restrict__ mc_part, const float* __restrict__ x_l, const float* __restrict__ bias,
     const float* __restrict__ scale, float* __restrict__ xout_l, float* __restrict__ rstd_l, uint8_t* mc_h, int rpr,
-    int D, float eps) {
-  sync_ranks(c, blockIdx.x);  // every rank's partial matrix is complete; every rank is done with the landing zone
+    int D, float eps, int bar_mode) {
+  sp_barrier(c, bar_mode);  // every rank's partial matrix is complete; every rank is done with the landing zone
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   constexpr int wpb = T / 32;
   const int nchunk = D >> 3;
@@ -136,7 +186,7 @@ __global__ void __launch_bounds__(T) rs_add_rmsnorm_ag_kernel(
       }
     }
   }
-  sync_ranks(c, blockIdx.x);  // every rank's h rows have landed everywhere; nobody still reads the partials
+  sp_barrier(c, bar_mode);  // every rank's h rows have landed everywhere; nobody still reads the partials
 }
 
 // ------------------------------------------------------------------------------------------------ backward
@@ -148,9 +198,9 @@ template <int NC, int R, int T>
 __global__ void __launch_bounds__(T) rs_rmsnorm_bwd_ag_kernel(
     CommCtx c, const uint8_t* __restrict__ mc_part, const float* __restrict__ x_l, const float* __restrict__ rstd_l,
     const float* __restrict__ scale, const float* __restrict__ dres_l, float* __restrict__ dx_l, uint8_t* mc_dx,
-    float* __restrict__ scratch, int rpr, int D) {
+    float* __restrict__ scratch, int rpr, int D, int bar_mode) {
   __shared__ float red[T / 32][32 * 8];
-  sync_ranks(c, blockIdx.x);
+  sp_barrier(c, bar_mode);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   constexpr int wpb = T / 32;
   const int nchunk = D >> 3;
@@ -256,7 +306,7 @@ __global__ void __launch_bounds__(T) rs_rmsnorm_bwd_ag_kernel(
       }
     }
   }
-  sync_ranks(c, blockIdx.x);
+  sp_barrier(c, bar_mode);
 }
 
 // out0[c] (+)= sum_b scratch[b][c], out1[c] (+)= sum_b scratch[b][D + c]: fixed order, deterministic.
@@ -288,14 +338,27 @@ static CommCtx sp_ctx(const unsigned long long* flag_ptrs, int rank, int n) {
   return c;
 }
 
-// One row per warp-slot: enough blocks that (for the model's shapes) every row of the rank is in flight at once, capped
-// at two resident 512-thread blocks per SM.
-static int sp_grid(int rpr, int R, int T) {
+// Debug / tuning knobs (tools/bench_handoff.py): grid cap (0 = automatic) and barrier flavour.
+static int g_sp_grid_cap = 0;
+static int g_sp_bar_mode = 1;
+
+// One row-slot per warp: enough blocks that (for the model's shapes) every row of the rank is in flight at once, never
+// more than can be resident together (`resident` = SMs x blocks per SM from the occupancy calculator: the grid-wide
+// barrier spins until every block has arrived).
+static int sp_grid(int rpr, int R, int T, int resident) {
   const int rows_per_block = (T / 32) * R;
   int b = (rpr + rows_per_block - 1) / rows_per_block;
-  const int cap = 2 * num_sms() < kMaxBlocks ? 2 * num_sms() : kMaxBlocks;
+  int cap = resident < kMaxBlocks ? resident : kMaxBlocks;
+  if (g_sp_grid_cap > 0 && g_sp_grid_cap < cap) cap = g_sp_grid_cap;
   if (b > cap) b = cap;
   return b < 1 ? 1 : b;
+}
+
+template <typename K>
+static int resident_blocks(K kfn, int threads) {
+  int per_sm = 0;
+  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kfn, threads, 0) != cudaSuccess || per_sm < 1) per_sm = 1;
+  return per_sm * num_sms();
 }
 
 }  // namespace dpfs
@@ -304,7 +367,16 @@ using namespace dpfs;
 
 // upper bound of the backward kernel's grid (sizes its [blocks][2 * D] partial-sum scratch)
 extern "C" int dpfs_sp_blocks(int rows_per_rank, int D) {
-  return D <= 512 ? sp_grid(rows_per_rank, 2, 512) : sp_grid(rows_per_rank, 1, 256);
+  const int rows_per_block = D <= 512 ? 32 : 8;
+  const int b = (rows_per_rank + rows_per_block - 1) / rows_per_block;
+  return b < kMaxBlocks ? (b < 1 ? 1 : b) : kMaxBlocks;
+}
+
+// tuning hook for the micro-benchmarks: grid_cap (0 = automatic), bar_mode (0 per-block, 1 grid-wide, 2 none)
+extern "C" int dpfs_sp_debug_config(int grid_cap, int bar_mode) {
+  g_sp_grid_cap = grid_cap;
+  g_sp_bar_mode = bar_mode;
+  return 0;
 }
 
 extern "C" int dpfs_rs_add_rmsnorm_ag(const void* mc_partial, const float* x_l, const float* bias, const float* scale,
@@ -317,12 +389,16 @@ extern "C" int dpfs_rs_add_rmsnorm_ag(const void* mc_partial, const float* x_l, 
   CommCtx c = sp_ctx(flag_ptrs, rank, n);
   const uint8_t* part = static_cast<const uint8_t*>(mc_partial);
   uint8_t* h = static_cast<uint8_t*>(mc_h);
-#define DPFS_SP_FWD(NC, R, T)                                                                          \
-  rs_add_rmsnorm_ag_kernel<NC, R, T><<<(DPFS_COUNT(), sp_grid(rows_per_rank, R, T)), T, 0, stream>>>(  \
-      c, part, x_l, bias, scale, xout_l, rstd_l, h, rows_per_rank, D, eps)
-  if (D <= 256) DPFS_SP_FWD(1, 2, 512);
-  else if (D <= 512) DPFS_SP_FWD(2, 2, 512);
-  else DPFS_SP_FWD(4, 1, 256);
+#define DPFS_SP_FWD(NC, R, T)                                                                               \
+  {                                                                                                         \
+    auto kfn = rs_add_rmsnorm_ag_kernel<NC, R, T>;                                                          \
+    static const int resident = resident_blocks(kfn, T);                                                    \
+    kfn<<<(DPFS_COUNT(), sp_grid(rows_per_rank, R, T, resident)), T, 0, stream>>>(                          \
+        c, part, x_l, bias, scale, xout_l, rstd_l, h, rows_per_rank, D, eps, g_sp_bar_mode);                \
+  }
+  if (D <= 256) DPFS_SP_FWD(1, 2, 512)
+  else if (D <= 512) DPFS_SP_FWD(2, 2, 512)
+  else DPFS_SP_FWD(4, 1, 256)
 #undef DPFS_SP_FWD
   return static_cast<int>(cudaGetLastError());
 }
@@ -339,10 +415,14 @@ extern "C" int dpfs_rs_rmsnorm_bwd_ag(const void* mc_partial, const float* x_l, 
   const uint8_t* part = static_cast<const uint8_t*>(mc_partial);
   uint8_t* dx = static_cast<uint8_t*>(mc_dx);
   int grid = 0;
-#define DPFS_SP_BWD(NC, R, T)                                                         \
-  grid = sp_grid(rows_per_rank, R, T);                                                \
-  rs_rmsnorm_bwd_ag_kernel<NC, R, T><<<(DPFS_COUNT(), grid), T, 0, stream>>>(         \
-      c, part, x_l, rstd_l, scale, dres_l, dx_l, dx, scratch, rows_per_rank, D)
+#define DPFS_SP_BWD(NC, R, T)                                                                      \
+  {                                                                                                \
+    auto kfn = rs_rmsnorm_bwd_ag_kernel<NC, R, T>;                                                 \
+    static const int resident = resident_blocks(kfn, T);                                           \
+    grid = sp_grid(rows_per_rank, R, T, resident);                                                 \
+    kfn<<<(DPFS_COUNT(), grid), T, 0, stream>>>(c, part, x_l, rstd_l, scale, dres_l, dx_l, dx,     \
+                                                scratch, rows_per_rank, D, g_sp_bar_mode);         \
+  }
   if (D <= 256) { DPFS_SP_BWD(1, 2, 512); }
   else if (D <= 512) { DPFS_SP_BWD(2, 2, 512); }
   else { DPFS_SP_BWD(4, 1, 256); }

@@ -58,6 +58,7 @@ SIGS = {
     "dpfs_swiglu_fwd": (c_p, c_p, c_int, c_int, c_p),
     "dpfs_swiglu_bwd": (c_p, c_p, c_p, c_int, c_int, c_p),
     "dpfs_swiglu_bwd_bias": (c_p, c_p, c_p, c_p, c_int, c_p, c_int, c_int, c_p),
+    "dpfs_swiglu_bwd_scratch_floats": (c_int, c_int),
     "dpfs_cast_colsum": (c_p, c_p, c_p, c_int, c_p, c_int, c_int, c_p),
     "dpfs_gelu_fwd": (c_p, c_p, c_ll, c_p),
     "dpfs_gelu_bwd": (c_p, c_p, c_p, c_ll, c_p),
@@ -74,6 +75,8 @@ SIGS = {
     "dpfs_rs_rmsnorm_bwd_ag": (c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_int, c_p, c_int, c_int, c_p, c_int,
                                c_int, c_p),
     "dpfs_sp_blocks": (c_int, c_int),
+    "dpfs_sp_debug_config": (c_int, c_int),
+    "dpfs_comm_barrier_ex": (c_p, c_int, c_int, c_int, c_int, c_int, c_p),
     "dpfs_ce_stats": (c_p, c_int, c_ll, c_p, c_p, c_p, c_int, c_int, c_ll, c_ll, c_p),
     "dpfs_ce_loss": (c_p, c_p, c_int, c_p, c_p, c_int, c_ll, c_p),
     "dpfs_ce_grad": (c_p, c_int, c_ll, c_p, c_p, c_int, c_p, c_ll, c_p, c_p, c_int, c_int, c_ll, c_ll, c_p),

@@ -285,7 +285,7 @@ def swiglu_bwd_bias(dact: torch.Tensor, gu: torch.Tensor, bias_grad: torch.Tenso
     assert bias_grad.dtype == F32 and bias_grad.numel() == F2 and bias_grad.is_contiguous()
     dgu = torch.empty_like(gu)
     lib = _lib.lib()
-    scratch = _scratch(gu.device, "colsum", lib.dpfs_colsum_scratch_floats(M, F2))
+    scratch = _scratch(gu.device, "colsum", lib.dpfs_swiglu_bwd_scratch_floats(M, F2 // 2))
     rc = lib.dpfs_swiglu_bwd_bias(dact.data_ptr(), gu.data_ptr(), dgu.data_ptr(), bias_grad.data_ptr(), 0,
                                   scratch.data_ptr(), M, F2 // 2, _lib.stream())
     _lib.check(rc, "dpfs_swiglu_bwd_bias")

@@ -87,6 +87,13 @@ int dpfs_rs_rmsnorm_bwd_ag(const void* mc_partial, const float* x_l, const float
                            int accumulate, float* scratch, int rows_per_rank, int D,
                            const unsigned long long* flag_ptrs, int rank, int n, cudaStream_t stream);
 int dpfs_sp_blocks(int rows_per_rank, int D);
+/* Tuning hook of the two kernels above (tools/bench_handoff.py): grid_cap = most blocks to launch (0 = as many as are
+ * resident at once), bar_mode = 0 one rank barrier per block (n remote atomics each), 1 grid-wide barrier with a
+ * single n-way exchange per rank (default), 2 no barrier (timing of the data phase only; results are undefined). */
+int dpfs_sp_debug_config(int grid_cap, int bar_mode);
+/* `reps` rank barriers in each of `blocks` blocks of `threads` threads: the cost of the barrier itself. */
+int dpfs_comm_barrier_ex(const unsigned long long* flag_ptrs, int rank, int n, int blocks, int threads, int reps,
+                         cudaStream_t stream);
 
 
 /* Host-only (no GPU): the work items (heavy-first list positions) CTA `bid` of `grid` persistent attention CTAs
@@ -191,6 +198,8 @@ int dpfs_swiglu_bwd(const void* dact, const void* gu, void* dgu, int M, int F, c
  * scratch: dpfs_colsum_scratch_floats(M, 2F) floats.  ref: autograd of models/model.py:95 + models/layers.py:96. */
 int dpfs_swiglu_bwd_bias(const void* dact, const void* gu, void* dgu, float* bias_grad, int accumulate,
                          float* scratch, int M, int F, cudaStream_t stream);
+/* scratch floats dpfs_swiglu_bwd_bias needs for an [M][2F] gate|up activation (strip height depends on F) */
+int dpfs_swiglu_bwd_scratch_floats(int M, int F);
 /* tanh-GELU on bf16, n % 8 == 0 (no counterpart in the reference model; named by the project brief). */
 int dpfs_gelu_fwd(const void* x, void* y, long long n, cudaStream_t stream);
 int dpfs_gelu_bwd(const void* dy, const void* x, void* dx, long long n, cudaStream_t stream);
