@@ -204,9 +204,9 @@ def run_ours(args):
         try_enable_symm(required=(args.comm == "fused"))
     mk, desc = apply_config(args)
     margs = ModelArgumments() if mk is None else ModelArgumments(**mk)
-    # sequence parallelism pays off once the replicated norm / residual work outweighs the extra collectives:
-    # measured 15.9 vs 17.3 ms at TP=8 and 21.9 vs 20.9 ms at TP=2 (profiles/), so "auto" turns it on from TP=8
-    sp = world > 1 and (args.sp == "on" or (args.sp == "auto" and world >= 8))
+    # Sequence parallelism with the one-kernel hand-offs (csrc/sp_fused.cu) beats the all-reduce form at every TP size
+    # measured: 15.7 vs 16.3 ms at TP=2, 10.9 vs 13.7 ms at TP=8 (profiles/), so "auto" turns it on for every N > 1.
+    sp = world > 1 and (args.sp == "on" or (args.sp == "auto" and pm.pgm.symm is not None))
     model = Transformer(**asdict(margs), sequence_parallel=sp).cuda()
     model.reset_parameters()
     model.compute_dtype = torch.bfloat16

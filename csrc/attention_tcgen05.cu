@@ -1753,10 +1753,12 @@ extern "C" int dpfs_attn_fwd(const void* qkv, void* out, float* lse, int B, int 
     const char* e = getenv("DPFS_ATTN_PERSISTENT");
     persistent = e ? atoi(e) : 1;
   }
-  static int pingpong = -1;   // experimental two-q-tile kernel (hd = 64), see attn_fwd_pp_kernel
+  // two-q-tile ping-pong kernel (hd = 64), see attn_fwd_pp_kernel: 128.5 -> 102.6 us on b32 h8 t1000 (B200,
+  // profiles/attn_variants_r2.md), default since it passed the fp32 oracle on hardware; DPFS_ATTN_FWD_PP=0 turns it off
+  static int pingpong = -1;
   if (pingpong < 0) {
     const char* e = getenv("DPFS_ATTN_FWD_PP");
-    pingpong = e ? atoi(e) : 0;
+    pingpong = e ? atoi(e) : 1;
   }
   if (pingpong && HD == 64) return launch_fwd_pp(tm, out, lse, B, T, H, scale, stream);
   if (persistent)
@@ -1800,11 +1802,15 @@ extern "C" int dpfs_attn_bwd(const void* qkv, const void* out, const void* d_out
     CUtensorMap tm_dkv;
     rc = make_tmap_dkv(&tm_dkv, dqkv, 3 * Dl, T, B);
     if (rc) return rc;
-    static int v2 = -1;
-    if (v2 < 0) {
+    // V2 math path (mask predicates only on the diagonal step): measured on B200 (profiles/attn_variants_r2.md)
+    // 4 % faster at hd = 128 (717 -> 687 us, b8 h16 t2048) but 4 % slower at hd = 64, where its S / dP look-ahead
+    // does not pay (250 -> 260 us, b32 h8 t1000).  Default: V2 for hd = 128 only; DPFS_ATTN_BWD_V2=0/1 forces a choice.
+    static int v2_env = -2;
+    if (v2_env == -2) {
       const char* e = getenv("DPFS_ATTN_BWD_V2");
-      v2 = e ? atoi(e) : 0;
+      v2_env = e ? atoi(e) : -1;
     }
+    const bool v2 = v2_env >= 0 ? v2_env != 0 : HD == 128;
     if (v2)
       rc = HD == 64 ? launch_bwd_persistent<64, true>(tm_qkv, tm_do, tm_dq, tm_dkv, lse, delta, dqkv, B, T, H, scale,
                                                       stream)

@@ -5,6 +5,8 @@
 //   data   : one buffer per rank, mapped in every peer (P2P) and through one multicast address (NVLS)
 //   flags  : uint32 per rank; region 0 = [kMaxBlocks][kMaxRanks] block-barrier semaphores,
 //            region 1 = [kMaxTiles][kMaxRanks] "partial tile ready" semaphores of the fused GEMM + all-reduce
+//            region 2 = [kMaxTiles][kMaxRanks] "partial tile ready" EPOCH words of the fused GEMM + hand-off
+//                       (gemm_handoff.cu: written with plain release stores, never reset)
 // Every flag is a binary semaphore between one sender and one receiver (sender flips 0->1 with release semantics,
 // receiver flips 1->0 with acquire semantics), so there are no epochs to keep and CUDA-graph replays stay correct.
 #pragma once
@@ -16,7 +18,7 @@ namespace dpfs {
 constexpr int kMaxRanks = 8;
 constexpr int kMaxBlocks = 1024;
 constexpr int kMaxTiles = 16384;
-constexpr int kFlagWords = (kMaxBlocks + kMaxTiles) * kMaxRanks;
+constexpr int kFlagWords = (kMaxBlocks + 2 * kMaxTiles) * kMaxRanks;
 
 struct CommCtx {
   uint32_t* flags[kMaxRanks];  // flags[r] = rank r's flag buffer (peer-mapped)

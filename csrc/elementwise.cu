@@ -455,25 +455,48 @@ __global__ void __launch_bounds__(kNormThreads) layernorm_bwd_kernel(
 // --------------------------------------------------------------------------------------------- SwiGLU / GELU
 // gu: [M][2F] bf16 with the gate in columns [0,F) and the up projection in [F,2F) (concatenated weights);
 // act = silu(gate) * up   (reference models/model.py:95).
-__global__ void swiglu_fwd_kernel(const __nv_bfloat16* __restrict__ gu, __nv_bfloat16* __restrict__ act, int M,
-                                  int F) {
-  const long long total = static_cast<long long>(M) * (F / 8);
-  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
-       i += static_cast<long long>(gridDim.x) * blockDim.x) {
-    const int row = static_cast<int>(i / (F / 8));
-    const int c = static_cast<int>(i % (F / 8)) * 8;
-    const uint4 gv = *reinterpret_cast<const uint4*>(gu + static_cast<long long>(row) * 2 * F + c);
-    const uint4 uv = *reinterpret_cast<const uint4*>(gu + static_cast<long long>(row) * 2 * F + F + c);
-    const uint32_t gw[4] = {gv.x, gv.y, gv.z, gv.w}, uw[4] = {uv.x, uv.y, uv.z, uv.w};
-    uint32_t ow[4];
+// sigmoid through the two SFU approximations (ex2, rcp: ~1 ulp each, far below bf16 resolution) instead of an
+// IEEE division: the elementwise SwiGLU kernels were instruction-bound on the division's Newton steps.
+__device__ __forceinline__ float fast_sigmoid(float x) {
+  // sigmoid(x) = 0.5 * tanh(x / 2) + 0.5: ONE SFU op (tanh.approx, rel. error 2^-11) instead of ex2 + rcp -- the
+  // elementwise SwiGLU kernels sit on the SFU pipe (16 ops / clk / SM) otherwise
+  float t;
+  asm("tanh.approx.f32 %0, %1;" : "=f"(t) : "f"(0.5f * x));
+  return fmaf(0.5f, t, 0.5f);
+}
+
+// Row-blocked: blockIdx.y walks rows, threads cover the F / 8 column groups -- no 64-bit division per element, and two
+// rows per thread keep 4 x 16 B loads in flight.
+__global__ void __launch_bounds__(256) swiglu_fwd_kernel(const __nv_bfloat16* __restrict__ gu,
+                                                         __nv_bfloat16* __restrict__ act, int M, int F) {
+  const int groups = F >> 3;
+  const int cg = blockIdx.x * blockDim.x + threadIdx.x;
+  if (cg >= groups) return;
+  const int c = cg * 8;
+  for (int row = blockIdx.y * 2; row < M; row += gridDim.y * 2) {
+    uint4 gv[2], uv[2];
 #pragma unroll
-    for (int j = 0; j < 4; ++j) {
-      const float2 g = unpack_bf16(gw[j]), u = unpack_bf16(uw[j]);
-      const float a0 = g.x / (1.f + __expf(-g.x)) * u.x;
-      const float a1 = g.y / (1.f + __expf(-g.y)) * u.y;
-      ow[j] = pack_bf16(a0, a1);
+    for (int r = 0; r < 2; ++r) {
+      if (row + r < M) {
+        const __nv_bfloat16* p = gu + static_cast<long long>(row + r) * 2 * F + c;
+        gv[r] = *reinterpret_cast<const uint4*>(p);
+        uv[r] = *reinterpret_cast<const uint4*>(p + F);
+      }
     }
-    *reinterpret_cast<uint4*>(act + static_cast<long long>(row) * F + c) = make_uint4(ow[0], ow[1], ow[2], ow[3]);
+#pragma unroll
+    for (int r = 0; r < 2; ++r) {
+      if (row + r < M) {
+        const uint32_t gw[4] = {gv[r].x, gv[r].y, gv[r].z, gv[r].w}, uw[4] = {uv[r].x, uv[r].y, uv[r].z, uv[r].w};
+        uint32_t ow[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const float2 g = unpack_bf16(gw[j]), u = unpack_bf16(uw[j]);
+          ow[j] = pack_bf16(g.x * fast_sigmoid(g.x) * u.x, g.y * fast_sigmoid(g.y) * u.y);
+        }
+        *reinterpret_cast<uint4*>(act + static_cast<long long>(row + r) * F + c) =
+            make_uint4(ow[0], ow[1], ow[2], ow[3]);
+      }
+    }
   }
 }
 
@@ -495,7 +518,7 @@ __global__ void swiglu_bwd_kernel(const __nv_bfloat16* __restrict__ dact, const 
 #pragma unroll
     for (int j = 0; j < 4; ++j) {
       const float2 g = unpack_bf16(gw[j]), u = unpack_bf16(uw[j]), d = unpack_bf16(dw[j]);
-      const float s0 = 1.f / (1.f + __expf(-g.x)), s1 = 1.f / (1.f + __expf(-g.y));
+      const float s0 = fast_sigmoid(g.x), s1 = fast_sigmoid(g.y);
       const float dg0 = d.x * u.x * s0 * (1.f + g.x * (1.f - s0));
       const float dg1 = d.y * u.y * s1 * (1.f + g.y * (1.f - s1));
       og[j] = pack_bf16(dg0, dg1);
@@ -626,49 +649,67 @@ __global__ void colsum_partial_kernel(const __nv_bfloat16* __restrict__ x, long 
 // finishes the sum.
 
 // dgu = swiglu'(dact, gu) and partial column sums of dgu (= gradient of the gate|up biases)
-__global__ void __launch_bounds__(128) swiglu_bwd_colsum_kernel(const __nv_bfloat16* __restrict__ dact,
+constexpr int kSwigluRowLanes = 4;
+__global__ void __launch_bounds__(256) swiglu_bwd_colsum_kernel(const __nv_bfloat16* __restrict__ dact,
                                                                 const __nv_bfloat16* __restrict__ gu,
                                                                 __nv_bfloat16* __restrict__ dgu,
                                                                 float* __restrict__ scratch, int M, int F,
                                                                 int strip_rows) {
-  const int cg = blockIdx.x * blockDim.x + threadIdx.x;
-  if (cg * 8 >= F) return;
+  // block = blockDim.x column groups x 4 row lanes: lane ty walks rows r0 + ty, r0 + ty + 4, ... of the strip, the four
+  // partial sums of a column meet in shared memory in a fixed order (4x the threads in flight of one walker per column)
+  __shared__ float red[kSwigluRowLanes][64][17];
+  const int tx = threadIdx.x, ty = threadIdx.y;
+  const int cg = blockIdx.x * blockDim.x + tx;
+  const bool active = cg * 8 < F;
   const int r0 = blockIdx.y * strip_rows;
   const int r1 = min(M, r0 + strip_rows);
   float sg[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f}, su[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+  if (active) {
 #pragma unroll 4
-  for (int r = r0; r < r1; ++r) {
-    const long long go = static_cast<long long>(r) * 2 * F + cg * 8;
-    const uint4 gv = *reinterpret_cast<const uint4*>(gu + go);
-    const uint4 uv = *reinterpret_cast<const uint4*>(gu + go + F);
-    const uint4 dv = *reinterpret_cast<const uint4*>(dact + static_cast<long long>(r) * F + cg * 8);
-    const uint32_t gw[4] = {gv.x, gv.y, gv.z, gv.w}, uw[4] = {uv.x, uv.y, uv.z, uv.w},
-                   dw[4] = {dv.x, dv.y, dv.z, dv.w};
-    uint32_t og[4], ou[4];
+    for (int r = r0 + ty; r < r1; r += kSwigluRowLanes) {
+      const long long go = static_cast<long long>(r) * 2 * F + cg * 8;
+      const uint4 gv = *reinterpret_cast<const uint4*>(gu + go);
+      const uint4 uv = *reinterpret_cast<const uint4*>(gu + go + F);
+      const uint4 dv = *reinterpret_cast<const uint4*>(dact + static_cast<long long>(r) * F + cg * 8);
+      const uint32_t gw[4] = {gv.x, gv.y, gv.z, gv.w}, uw[4] = {uv.x, uv.y, uv.z, uv.w},
+                     dw[4] = {dv.x, dv.y, dv.z, dv.w};
+      uint32_t og[4], ou[4];
 #pragma unroll
-    for (int j = 0; j < 4; ++j) {
-      const float2 g = unpack_bf16(gw[j]), u = unpack_bf16(uw[j]), d = unpack_bf16(dw[j]);
-      const float s0 = 1.f / (1.f + __expf(-g.x)), s1 = 1.f / (1.f + __expf(-g.y));
-      const float dg0 = d.x * u.x * s0 * (1.f + g.x * (1.f - s0));
-      const float dg1 = d.y * u.y * s1 * (1.f + g.y * (1.f - s1));
-      const float du0 = d.x * g.x * s0, du1 = d.y * g.y * s1;
-      og[j] = pack_bf16(dg0, dg1);
-      ou[j] = pack_bf16(du0, du1);
-      // sum what is actually stored (bf16-rounded), like a separate colsum pass over dgu would
-      const float2 rg = unpack_bf16(og[j]), ru = unpack_bf16(ou[j]);
-      sg[2 * j] += rg.x;
-      sg[2 * j + 1] += rg.y;
-      su[2 * j] += ru.x;
-      su[2 * j + 1] += ru.y;
+      for (int j = 0; j < 4; ++j) {
+        const float2 g = unpack_bf16(gw[j]), u = unpack_bf16(uw[j]), d = unpack_bf16(dw[j]);
+        const float s0 = fast_sigmoid(g.x), s1 = fast_sigmoid(g.y);
+        const float dg0 = d.x * u.x * s0 * (1.f + g.x * (1.f - s0));
+        const float dg1 = d.y * u.y * s1 * (1.f + g.y * (1.f - s1));
+        const float du0 = d.x * g.x * s0, du1 = d.y * g.y * s1;
+        og[j] = pack_bf16(dg0, dg1);
+        ou[j] = pack_bf16(du0, du1);
+        // sum what is actually stored (bf16-rounded), like a separate colsum pass over dgu would
+        const float2 rg = unpack_bf16(og[j]), ru = unpack_bf16(ou[j]);
+        sg[2 * j] += rg.x;
+        sg[2 * j + 1] += rg.y;
+        su[2 * j] += ru.x;
+        su[2 * j + 1] += ru.y;
+      }
+      *reinterpret_cast<uint4*>(dgu + go) = make_uint4(og[0], og[1], og[2], og[3]);
+      *reinterpret_cast<uint4*>(dgu + go + F) = make_uint4(ou[0], ou[1], ou[2], ou[3]);
     }
-    *reinterpret_cast<uint4*>(dgu + go) = make_uint4(og[0], og[1], og[2], og[3]);
-    *reinterpret_cast<uint4*>(dgu + go + F) = make_uint4(ou[0], ou[1], ou[2], ou[3]);
   }
-  float* o = scratch + static_cast<long long>(blockIdx.y) * 2 * F + cg * 8;
-  *reinterpret_cast<float4*>(o) = make_float4(sg[0], sg[1], sg[2], sg[3]);
-  *reinterpret_cast<float4*>(o + 4) = make_float4(sg[4], sg[5], sg[6], sg[7]);
-  *reinterpret_cast<float4*>(o + F) = make_float4(su[0], su[1], su[2], su[3]);
-  *reinterpret_cast<float4*>(o + F + 4) = make_float4(su[4], su[5], su[6], su[7]);
+#pragma unroll
+  for (int e = 0; e < 8; ++e) {
+    red[ty][tx][e] = sg[e];
+    red[ty][tx][8 + e] = su[e];
+  }
+  __syncthreads();
+  if (ty == 0 && active) {
+    float o[16];
+#pragma unroll
+    for (int e = 0; e < 16; ++e) o[e] = ((red[0][tx][e] + red[1][tx][e]) + red[2][tx][e]) + red[3][tx][e];
+    float* dst = scratch + static_cast<long long>(blockIdx.y) * 2 * F + cg * 8;
+    *reinterpret_cast<float4*>(dst) = make_float4(o[0], o[1], o[2], o[3]);
+    *reinterpret_cast<float4*>(dst + 4) = make_float4(o[4], o[5], o[6], o[7]);
+    *reinterpret_cast<float4*>(dst + F) = make_float4(o[8], o[9], o[10], o[11]);
+    *reinterpret_cast<float4*>(dst + F + 4) = make_float4(o[12], o[13], o[14], o[15]);
+  }
 }
 
 // y = bf16(x) and partial column sums of y
@@ -918,8 +959,15 @@ extern "C" int dpfs_layernorm_bwd(const void* dy, int dy_bf16, const void* x, in
 extern "C" int dpfs_swiglu_fwd(const void* gu, void* act, int M, int F, cudaStream_t stream) {
   if (F % 8 != 0) return -21;
   if (M <= 0) return 0;
-  const long long total = static_cast<long long>(M) * (F / 8);
-  swiglu_fwd_kernel<<<(DPFS_COUNT(), ew_grid(total, 256)), 256, 0, stream>>>((const __nv_bfloat16*)gu, (__nv_bfloat16*)act, M, F);
+  const int groups = F / 8;
+  const int threads = groups >= 256 ? 256 : ((groups + 31) / 32) * 32;
+  const int gx = (groups + threads - 1) / threads;
+  long long gy = (static_cast<long long>(M) + 1) / 2;
+  const long long cap = static_cast<long long>(num_sms()) * 8 * 256 / (static_cast<long long>(threads) * gx);
+  if (gy > cap) gy = cap < 1 ? 1 : cap;
+  if (gy > 65535) gy = 65535;
+  swiglu_fwd_kernel<<<(DPFS_COUNT(), dim3(gx, static_cast<unsigned>(gy))), threads, 0, stream>>>(
+      (const __nv_bfloat16*)gu, (__nv_bfloat16*)act, M, F);
   return static_cast<int>(cudaGetLastError());
 }
 
@@ -984,9 +1032,9 @@ extern "C" int dpfs_colsum_bf16(const void* x, long long ld, float* out, int acc
 // strip, 16-row strips -> 2000 blocks for M = 32000 instead of 500 three-quarters-empty ones).
 static inline int swiglu_strip_rows(int F) {
   const int groups = F / 8;
-  if (groups >= 128) return kColsumRowsPerBlock;
-  const int r = kColsumRowsPerBlock * groups / 128;
-  return r < 8 ? 8 : r;
+  if (groups >= 64) return kColsumRowsPerBlock;
+  const int r = kColsumRowsPerBlock * groups / 64;
+  return r < 16 ? 16 : r;
 }
 extern "C" int dpfs_swiglu_bwd_scratch_floats(int M, int F) {
   const int rows = swiglu_strip_rows(F);
@@ -1000,11 +1048,11 @@ extern "C" int dpfs_swiglu_bwd_bias(const void* dact, const void* gu, void* dgu,
   const int strips = (M + rows - 1) / rows;
   if (strips > 65535) return -27;
   const int groups = F / 8;
-  const int threads = groups >= 128 ? 128 : ((groups + 31) / 32) * 32;
-  dim3 grid((groups + threads - 1) / threads, strips);
-  swiglu_bwd_colsum_kernel<<<(DPFS_COUNT(), grid), threads, 0, stream>>>((const __nv_bfloat16*)dact,
-                                                                        (const __nv_bfloat16*)gu, (__nv_bfloat16*)dgu,
-                                                                        scratch, M, F, rows);
+  const int tx = groups >= 64 ? 64 : ((groups + 31) / 32) * 32;   // <= 64: the smem reduction is sized for it
+  dim3 grid((groups + tx - 1) / tx, strips), block(tx, kSwigluRowLanes);
+  swiglu_bwd_colsum_kernel<<<(DPFS_COUNT(), grid), block, 0, stream>>>((const __nv_bfloat16*)dact,
+                                                                      (const __nv_bfloat16*)gu, (__nv_bfloat16*)dgu,
+                                                                      scratch, M, F, rows);
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) return static_cast<int>(e);
   reduce_partials_kernel<<<(DPFS_COUNT(), (2 * F + 31) / 32), kReduceGroups * 32, 0, stream>>>(scratch, bias_grad, strips, 2 * F,

@@ -16,6 +16,9 @@
 // Copy.backward all-reduce (models/comm_ops.py:59 <- models/layers.py:91) + RMSNorm backward.
 #include "comm.cuh"
 #include "dpfs_b200.h"
+#include "sp_rowops.cuh"
+
+#include <stdlib.h>
 
 namespace dpfs {
 
@@ -35,13 +38,18 @@ __device__ __forceinline__ unsigned int ld_acquire_gpu(const unsigned int* p) {
   asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
   return v;
 }
+// ALLFENCE = false: one system-scope fence per block, issued by thread 0 after the block barrier (the pattern of
+// cooperative-groups grid sync: the barrier orders every thread's stores before thread 0's cumulative fence).
+// ALLFENCE = true: every thread fences its own stores first (kept for A/B timing; 64 K system fences per barrier).
+template <bool ALLFENCE>
 __device__ __forceinline__ void sync_ranks_grid(const CommCtx& c) {
   __shared__ int s_last;
-  __threadfence_system();  // this thread's stores (plain and multimem) are performed system-wide
+  if (ALLFENCE) __threadfence_system();
   __syncthreads();
   unsigned int gen = 0;
   if (threadIdx.x == 0) {
-    gen = ld_acquire_gpu(&g_grid_gen);  // read before arriving: the release of THIS barrier flips it
+    if (!ALLFENCE) __threadfence_system();  // this block's stores (plain and multimem) are performed system-wide
+    gen = ld_acquire_gpu(&g_grid_gen);      // read before arriving: the release of THIS barrier flips it
     unsigned int prev;
     asm volatile("atom.acq_rel.gpu.global.add.u32 %0, [%1], 1;" : "=r"(prev) : "l"(&g_grid_count) : "memory");
     s_last = prev == gridDim.x - 1;
@@ -69,32 +77,12 @@ __device__ __forceinline__ void sync_ranks_grid(const CommCtx& c) {
 }
 __device__ __forceinline__ void sp_barrier(const CommCtx& c, int bar_mode) {
   if (bar_mode == 0) sync_ranks(c, blockIdx.x);
-  else if (bar_mode == 1) sync_ranks_grid(c);
+  else if (bar_mode == 1) sync_ranks_grid<false>(c);
+  else if (bar_mode == 3) sync_ranks_grid<true>(c);
 }
 
 // Block shape: T threads = T / 32 warps, each owns whole rows (512 threads for D <= 512, 256 for the wider rows, whose
 // per-lane accumulators need more than 128 registers).
-
-__device__ __forceinline__ void unpack8(const uint4& u, float (&f)[8]) {
-  const uint32_t w[4] = {u.x, u.y, u.z, u.w};
-#pragma unroll
-  for (int i = 0; i < 4; ++i) {
-    const float2 t = unpack_bf16(w[i]);
-    f[2 * i] = t.x;
-    f[2 * i + 1] = t.y;
-  }
-}
-__device__ __forceinline__ uint4 pack8(const float (&f)[8]) {
-  return make_uint4(pack_bf16(f[0], f[1]), pack_bf16(f[2], f[3]), pack_bf16(f[4], f[5]), pack_bf16(f[6], f[7]));
-}
-__device__ __forceinline__ void ld8f(const float* p, float (&f)[8]) {
-  const float4 a = *reinterpret_cast<const float4*>(p), b = *reinterpret_cast<const float4*>(p + 4);
-  f[0] = a.x, f[1] = a.y, f[2] = a.z, f[3] = a.w, f[4] = b.x, f[5] = b.y, f[6] = b.z, f[7] = b.w;
-}
-__device__ __forceinline__ void st8f(float* p, const float (&f)[8]) {
-  *reinterpret_cast<float4*>(p) = make_float4(f[0], f[1], f[2], f[3]);
-  *reinterpret_cast<float4*>(p + 4) = make_float4(f[4], f[5], f[6], f[7]);
-}
 
 // A lane owns the 16-byte chunks (8 bf16 columns) j * 32 + lane, j < NC, of a row: D <= NC * 256.
 // R rows per warp are in flight together (the loads of all R rows are issued before the first use).
@@ -114,78 +102,13 @@ __global__ void __launch_bounds__(T) rs_add_rmsnorm_ag_kernel(
   constexpr int wpb = T / 32;
   const int nchunk = D >> 3;
   float sc[NC][8], bs[NC][8];
-#pragma unroll
-  for (int j = 0; j < NC; ++j) {
-    const int ch = j * 32 + lane;
-#pragma unroll
-    for (int e = 0; e < 8; ++e) sc[j][e] = bs[j][e] = 0.f;
-    if (ch < nchunk) {
-      if (scale) ld8f(scale + ch * 8, sc[j]);
-      if (bias) ld8f(bias + ch * 8, bs[j]);
-    }
-  }
+  sp_load_cols<NC>(scale, nchunk, lane, sc);
+  sp_load_cols<NC>(bias, nchunk, lane, bs);
   const long long r0 = static_cast<long long>(c.rank) * rpr;
   const long long rowb = static_cast<long long>(D) * 2;
-  for (int row = (blockIdx.x * wpb + warp) * R; row < rpr; row += gridDim.x * wpb * R) {
-    uint4 p[R][NC];
-    float v[R][NC][8];
-#pragma unroll
-    for (int r = 0; r < R; ++r) {
-      if (row + r < rpr) {
-#pragma unroll
-        for (int j = 0; j < NC; ++j) {
-          const int ch = j * 32 + lane;
-          if (ch < nchunk) p[r][j] = multimem_ld_reduce_bf16x8(mc_part + (r0 + row + r) * rowb + ch * 16);
-        }
-      }
-    }
-#pragma unroll
-    for (int r = 0; r < R; ++r) {
-      if (row + r < rpr) {
-#pragma unroll
-        for (int j = 0; j < NC; ++j) {
-          const int ch = j * 32 + lane;
-#pragma unroll
-          for (int e = 0; e < 8; ++e) v[r][j][e] = 0.f;
-          if (ch < nchunk && x_l) ld8f(x_l + static_cast<long long>(row + r) * D + ch * 8, v[r][j]);
-        }
-      }
-    }
-#pragma unroll
-    for (int r = 0; r < R; ++r) {
-      if (row + r >= rpr) continue;
-      float ss = 0.f;
-#pragma unroll
-      for (int j = 0; j < NC; ++j) {
-        const int ch = j * 32 + lane;
-        if (ch < nchunk) {
-          float y[8];
-          unpack8(p[r][j], y);
-#pragma unroll
-          for (int e = 0; e < 8; ++e) {
-            v[r][j][e] += y[e] + bs[j][e];
-            ss += v[r][j][e] * v[r][j][e];
-          }
-          st8f(xout_l + static_cast<long long>(row + r) * D + ch * 8, v[r][j]);
-        }
-      }
-      if (mc_h) {
-        ss = warp_sum(ss);
-        const float rstd = rsqrtf(ss / D + eps);
-        if (lane == 0) rstd_l[row + r] = rstd;
-#pragma unroll
-        for (int j = 0; j < NC; ++j) {
-          const int ch = j * 32 + lane;
-          if (ch < nchunk) {
-            float o[8];
-#pragma unroll
-            for (int e = 0; e < 8; ++e) o[e] = v[r][j][e] * rstd * sc[j][e];
-            multimem_st_16B(mc_h + (r0 + row + r) * rowb + ch * 16, pack8(o));
-          }
-        }
-      }
-    }
-  }
+  for (int row = (blockIdx.x * wpb + warp) * R; row < rpr; row += gridDim.x * wpb * R)
+    sp_fwd_rows<NC, R>(mc_part + (r0 + row) * rowb, mc_h ? mc_h + (r0 + row) * rowb : nullptr, x_l, xout_l, rstd_l, row,
+                       rpr, D, eps, lane, sc, bs);
   sp_barrier(c, bar_mode);  // every rank's h rows have landed everywhere; nobody still reads the partials
 }
 
@@ -205,107 +128,17 @@ __global__ void __launch_bounds__(T) rs_rmsnorm_bwd_ag_kernel(
   constexpr int wpb = T / 32;
   const int nchunk = D >> 3;
   float sc[NC][8], ds[NC][8], cs[NC][8];
-#pragma unroll
-  for (int j = 0; j < NC; ++j) {
-    const int ch = j * 32 + lane;
-#pragma unroll
-    for (int e = 0; e < 8; ++e) sc[j][e] = ds[j][e] = cs[j][e] = 0.f;
-    if (ch < nchunk) ld8f(scale + ch * 8, sc[j]);
-  }
+  sp_load_cols<NC>(scale, nchunk, lane, sc);
+  sp_load_cols<NC>(nullptr, nchunk, lane, ds);
+  sp_load_cols<NC>(nullptr, nchunk, lane, cs);
   const long long r0 = static_cast<long long>(c.rank) * rpr;
   const long long rowb = static_cast<long long>(D) * 2;
-  for (int row = (blockIdx.x * wpb + warp) * R; row < rpr; row += gridDim.x * wpb * R) {
-    uint4 p[R][NC];
-    float xh[R][NC][8], rs[R][NC][8];
-    float rstd[R];
-#pragma unroll
-    for (int r = 0; r < R; ++r) {
-      rstd[r] = 0.f;
-      if (row + r < rpr) {
-#pragma unroll
-        for (int j = 0; j < NC; ++j) {
-          const int ch = j * 32 + lane;
-          if (ch < nchunk) p[r][j] = multimem_ld_reduce_bf16x8(mc_part + (r0 + row + r) * rowb + ch * 16);
-        }
-      }
-    }
-#pragma unroll
-    for (int r = 0; r < R; ++r) {
-      if (row + r < rpr) {
-        rstd[r] = rstd_l[row + r];
-#pragma unroll
-        for (int j = 0; j < NC; ++j) {
-          const int ch = j * 32 + lane;
-#pragma unroll
-          for (int e = 0; e < 8; ++e) xh[r][j][e] = rs[r][j][e] = 0.f;
-          if (ch < nchunk) {
-            const long long off = static_cast<long long>(row + r) * D + ch * 8;
-            ld8f(x_l + off, xh[r][j]);
-            if (dres_l) ld8f(dres_l + off, rs[r][j]);
-          }
-        }
-      }
-    }
-#pragma unroll
-    for (int r = 0; r < R; ++r) {
-      if (row + r >= rpr) continue;
-      float g[NC][8];
-      float dot = 0.f;
-#pragma unroll
-      for (int j = 0; j < NC; ++j) {
-        const int ch = j * 32 + lane;
-        if (ch < nchunk) {
-          float dh[8];
-          unpack8(p[r][j], dh);
-#pragma unroll
-          for (int e = 0; e < 8; ++e) {
-            const float xv = xh[r][j][e] * rstd[r];
-            xh[r][j][e] = xv;
-            g[j][e] = dh[e] * sc[j][e];
-            ds[j][e] += dh[e] * xv;
-            dot += g[j][e] * xv;
-          }
-        }
-      }
-      dot = warp_sum(dot) / D;
-#pragma unroll
-      for (int j = 0; j < NC; ++j) {
-        const int ch = j * 32 + lane;
-        if (ch < nchunk) {
-          float o[8];
-#pragma unroll
-          for (int e = 0; e < 8; ++e) {
-            o[e] = rstd[r] * (g[j][e] - xh[r][j][e] * dot) + rs[r][j][e];
-            cs[j][e] += o[e];
-          }
-          if (dx_l) st8f(dx_l + static_cast<long long>(row + r) * D + ch * 8, o);
-          if (mc_dx) multimem_st_16B(mc_dx + (r0 + row + r) * rowb + ch * 16, pack8(o));
-        }
-      }
-    }
-  }
+  for (int row = (blockIdx.x * wpb + warp) * R; row < rpr; row += gridDim.x * wpb * R)
+    sp_bwd_rows<NC, R>(mc_part + (r0 + row) * rowb, mc_dx ? mc_dx + (r0 + row) * rowb : nullptr, x_l, rstd_l, dres_l,
+                       dx_l, row, rpr, D, lane, sc, ds, cs);
   // block-level reduction of the two partial-sum rows: warps -> smem -> warp 0 sums in a fixed order
-  float* srow = scratch + static_cast<long long>(blockIdx.x) * 2 * D;
-#pragma unroll
-  for (int which = 0; which < 2; ++which) {
-#pragma unroll
-    for (int j = 0; j < NC; ++j) {
-      __syncthreads();
-#pragma unroll
-      for (int e = 0; e < 8; ++e) red[warp][lane * 8 + e] = which ? cs[j][e] : ds[j][e];
-      __syncthreads();
-      if (warp == 0) {
-        const int ch = j * 32 + lane;
-        if (ch < nchunk) {
-          float o[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-          for (int w = 0; w < wpb; ++w)
-#pragma unroll
-            for (int e = 0; e < 8; ++e) o[e] += red[w][lane * 8 + e];
-          st8f(srow + which * D + ch * 8, o);
-        }
-      }
-    }
-  }
+  sp_bwd_block_reduce<NC, wpb>(red, scratch + static_cast<long long>(blockIdx.x) * 2 * D, D, warp, lane, ds, cs,
+                               [] { __syncthreads(); });
   sp_barrier(c, bar_mode);
 }
 
@@ -341,6 +174,14 @@ static CommCtx sp_ctx(const unsigned long long* flag_ptrs, int rank, int n) {
 // Debug / tuning knobs (tools/bench_handoff.py): grid cap (0 = automatic) and barrier flavour.
 static int g_sp_grid_cap = 0;
 static int g_sp_bar_mode = 1;
+static void sp_env_init() {   // DPFS_SP_GRID_CAP / DPFS_SP_BAR_MODE, read once per process
+  static const bool done = [] {
+    if (const char* e = getenv("DPFS_SP_GRID_CAP")) g_sp_grid_cap = atoi(e);
+    if (const char* e = getenv("DPFS_SP_BAR_MODE")) g_sp_bar_mode = atoi(e);
+    return true;
+  }();
+  (void)done;
+}
 
 // One row-slot per warp: enough blocks that (for the model's shapes) every row of the rank is in flight at once, never
 // more than can be resident together (`resident` = SMs x blocks per SM from the occupancy calculator: the grid-wide
@@ -374,6 +215,7 @@ extern "C" int dpfs_sp_blocks(int rows_per_rank, int D) {
 
 // tuning hook for the micro-benchmarks: grid_cap (0 = automatic), bar_mode (0 per-block, 1 grid-wide, 2 none)
 extern "C" int dpfs_sp_debug_config(int grid_cap, int bar_mode) {
+  sp_env_init();
   g_sp_grid_cap = grid_cap;
   g_sp_bar_mode = bar_mode;
   return 0;
@@ -386,6 +228,7 @@ extern "C" int dpfs_rs_add_rmsnorm_ag(const void* mc_partial, const float* x_l, 
   if (D % 8 != 0 || D > 1024 || rows_per_rank <= 0) return -60;
   if (!mc_partial || !xout_l || (mc_h && (!scale || !rstd_l))) return -61;
   if ((reinterpret_cast<uintptr_t>(mc_partial) & 15) || (reinterpret_cast<uintptr_t>(mc_h) & 15)) return -51;
+  sp_env_init();
   CommCtx c = sp_ctx(flag_ptrs, rank, n);
   const uint8_t* part = static_cast<const uint8_t*>(mc_partial);
   uint8_t* h = static_cast<uint8_t*>(mc_h);
@@ -411,6 +254,7 @@ extern "C" int dpfs_rs_rmsnorm_bwd_ag(const void* mc_partial, const float* x_l, 
   if (D % 8 != 0 || D > 1024 || rows_per_rank <= 0) return -60;
   if (!mc_partial || !x_l || !rstd_l || !scale || !scratch) return -61;
   if ((reinterpret_cast<uintptr_t>(mc_partial) & 15) || (reinterpret_cast<uintptr_t>(mc_dx) & 15)) return -51;
+  sp_env_init();
   CommCtx c = sp_ctx(flag_ptrs, rank, n);
   const uint8_t* part = static_cast<const uint8_t*>(mc_partial);
   uint8_t* dx = static_cast<uint8_t*>(mc_dx);

@@ -39,6 +39,7 @@ class TrainStep:
         self.max_graphs = max_graphs
         self._graphs: Dict[Tuple[int, int], dict] = {}
         self._pool = None
+        self._cap_stream = None
         self._static: Dict[Tuple[int, int], tuple] = {}
         self.kernels_per_step = 0
         self.steps = 0
@@ -81,6 +82,11 @@ class TrainStep:
         before = _lib.lib().dpfs_launch_count() if _lib.available() else 0
         # thread_local: NCCL's watchdog thread may poll events while we capture (it never touches our stream)
         kw = {"capture_error_mode": "thread_local"}
+        # capture on a high-priority stream: kernels that the model forks onto its (default-priority) side stream -- the
+        # weight-gradient GEMMs of the sequence-parallel hand-off path -- then only take SMs the critical path leaves idle
+        if self._cap_stream is None:
+            self._cap_stream = torch.cuda.Stream(priority=-1)
+        kw["stream"] = self._cap_stream
         if self._pool is not None:
             kw["pool"] = self._pool
         with torch.cuda.graph(g, **kw):

@@ -33,8 +33,27 @@ from ..ops.attention import attn_bwd, attn_fwd
 from ..ops.gemm import gemm_nt
 from ..parallel import comm_ops
 from ..parallel import process_manager as pm
+from ..utils.logging import nvtx_range
 
 BF16, F32 = torch.bfloat16, torch.float32
+
+
+def _nvtx(label):
+    """NVTX range around one phase of the hand-scheduled step (shows up in nsys / as ncu --nvtx-include windows).
+    ``label`` may contain ``{i}``: the layer index of the LayerPack found among the call's arguments / ctx."""
+    def deco(fn):
+        def wrapped(*a, **k):
+            idx = ""
+            if "{i}" in label:
+                pack = next((x for x in a if isinstance(x, LayerPack)), None) or getattr(a[0], "pack", None)
+                idx = getattr(pack, "index", "")
+            with nvtx_range(label.format(i=idx)):
+                return fn(*a, **k)
+        wrapped.__name__ = fn.__name__
+        return wrapped
+    return deco
+
+
 _ALIGN = 64  # elements; keeps every group 256 B (fp32) / 128 B (bf16) aligned for TMA and vector access
 
 
@@ -230,6 +249,7 @@ def _wgrad(dy_bf16, x_bf16, out):
 
 class FusedLayerFn(torch.autograd.Function):
     @staticmethod
+    @_nvtx("layer{i}.fwd")
     def forward(ctx, x, pos, rt, pack: LayerPack, meta: Meta, *params):
         m = meta
         h1, rstd1 = fused.rmsnorm_fwd(x, pack.s1, rt.eps)
@@ -245,6 +265,7 @@ class FusedLayerFn(torch.autograd.Function):
         return x3
 
     @staticmethod
+    @_nvtx("layer{i}.bwd")
     def backward(ctx, dx3):
         x, pos, h1, rstd1, qkv, attn, lse, x2, h2, rstd2, gu, act = ctx.saved_tensors
         pack, m, rt = ctx.pack, ctx.meta, ctx.rt
@@ -287,6 +308,7 @@ class FusedLayerFn(torch.autograd.Function):
 
 class FusedEmbedFn(torch.autograd.Function):
     @staticmethod
+    @_nvtx("embed.fwd")
     def forward(ctx, ids_flat, rt, weight):
         emb = rt.model.embedding
         if pm.pgm.tp_size == 1:
@@ -314,6 +336,7 @@ class FusedEmbedFn(torch.autograd.Function):
         return out
 
     @staticmethod
+    @_nvtx("embed.bwd")
     def backward(ctx, dx):
         (ids_flat,) = ctx.saved_tensors
         rt = ctx.rt
@@ -327,6 +350,7 @@ class FusedHeadLossFn(torch.autograd.Function):
     """final RMSNorm -> vocab-parallel lm_head GEMM -> vocab-parallel softmax cross-entropy (mean over valid)."""
 
     @staticmethod
+    @_nvtx("head.fwd")
     def forward(ctx, x, targets_flat, rt, ignore_index, *params):
         n = pm.pgm.tp_size
         head = rt.model.lm_head
@@ -347,6 +371,7 @@ class FusedHeadLossFn(torch.autograd.Function):
         return loss
 
     @staticmethod
+    @_nvtx("head.bwd")
     def backward(ctx, gout):
         x, targets_flat, h, rstd, logits, all_stats, loss_acc = ctx.saved_tensors
         rt = ctx.rt
@@ -385,6 +410,8 @@ class FusedRuntime:
         self._fwd_handoff = None      # (x_l, gathered normalised input of the next block, its rstd)
         self._zones = None            # symmetric activation zones of the hand-off path (allocated on first use)
         self._zone_rows = 0
+        self._bz, self._bz_events = 0, [None, None]
+        self._side, self._side_keep, self._side_dirty = None, [], False
         head, emb = model.lm_head, model.embedding
         Vl = head.odim_partition
         self.wlm, self.g_wlm = A.view(A.shadow, head.weight, Vl, d), A.view(A.grads, head.weight, Vl, d)
@@ -450,10 +477,53 @@ class FusedRuntime:
             return False
         if self._zones is None or M > self._zone_rows:
             # h1 / h2 of every layer and the final norm's output stay resident for the backward pass (2L + 1 zones);
-            # one more zone carries the gathered bf16 residual-stream gradient during the backward pass
-            self._zones = symm.alloc_zones(2 * len(self.packs) + 2, M * self.d * 2)
+            # two more zones alternate as the landing buffer of the gathered bf16 residual-stream gradient (two, so a
+            # weight-gradient GEMM on the side stream may still read one while the next hand-off fills the other)
+            self._zones = symm.alloc_zones(2 * len(self.packs) + 3, M * self.d * 2)
             self._zone_rows = M
+            self._bz = 0
         return True
+
+    # Weight-gradient GEMMs never feed the rest of the backward pass; on the hand-off path they run on a side stream so
+    # they fill the SMs that the NVLink-bound hand-off kernels leave idle (those run on a fraction of the SMs).
+    #   * next_bzone(): the landing zone for the next gathered gradient; before handing a zone out again, the main
+    #     stream waits for the side-stream work that read it two hand-offs ago.
+    #   * on_side(fn, keep): run fn on the side stream after everything enqueued so far; ``keep`` are the tensors it
+    #     reads, held until join_side() so the caching allocator cannot hand their memory to a later main-stream tensor.
+    def side_enabled(self) -> bool:
+        return os.environ.get("DPFS_SP_SIDE_WGRAD", "1") == "1"
+
+    def next_bzone(self):
+        self._bz ^= 1
+        ev = self._bz_events[self._bz]
+        if ev is not None:
+            torch.cuda.current_stream().wait_event(ev)
+            self._bz_events[self._bz] = None
+        return self._zones[-1 - self._bz]
+
+    def on_side(self, fn, keep=(), reads_bzone: bool = False) -> None:
+        if not self.side_enabled():
+            fn()
+            return
+        if self._side is None:
+            self._side = torch.cuda.Stream()
+        main = torch.cuda.current_stream()
+        self._side.wait_stream(main)
+        with torch.cuda.stream(self._side):
+            fn()
+            if reads_bzone:
+                ev = torch.cuda.Event()
+                ev.record(self._side)
+                self._bz_events[self._bz] = ev
+        self._side_keep.extend(keep)
+        self._side_dirty = True
+
+    def join_side(self) -> None:
+        if self._side_dirty:
+            torch.cuda.current_stream().wait_stream(self._side)
+            self._side_dirty = False
+        self._side_keep.clear()
+        self._bz_events = [None, None]
 
     def put_handoff(self, x_l, h, rstd) -> None:
         self._fwd_handoff = (x_l, h, rstd)
@@ -558,6 +628,7 @@ def _rowpar_rs(a_bf16, w_bf16, b_mn_major=False):
 
 class FusedLayerSPFn(torch.autograd.Function):
     @staticmethod
+    @_nvtx("layer{i}.sp.fwd")
     def forward(ctx, x_l, pos, rt, pack: LayerPack, meta: Meta, *params):
         m = meta
         push = _push_comm(x_l)
@@ -586,6 +657,7 @@ class FusedLayerSPFn(torch.autograd.Function):
         return x3_l
 
     @staticmethod
+    @_nvtx("layer{i}.sp.bwd")
     def backward(ctx, dx3_l):
         x_l, pos, h1, rstd1, qkv, attn, lse, x2_l, h2, rstd2, gu, act = ctx.saved_tensors
         pack, m, rt = ctx.pack, ctx.meta, ctx.rt
@@ -625,6 +697,7 @@ class FusedLayerSPFn(torch.autograd.Function):
 
 class FusedEmbedSPFn(torch.autograd.Function):
     @staticmethod
+    @_nvtx("embed.sp.fwd")
     def forward(ctx, ids_flat, rt, weight):
         emb = rt.model.embedding
         M, D = ids_flat.numel(), weight.shape[1]
@@ -636,6 +709,7 @@ class FusedEmbedSPFn(torch.autograd.Function):
         return x_l
 
     @staticmethod
+    @_nvtx("embed.sp.bwd")
     def backward(ctx, dx_l):
         (ids_flat,) = ctx.saved_tensors
         rt = ctx.rt
@@ -650,6 +724,7 @@ class FusedEmbedSPFn(torch.autograd.Function):
 
 class FusedHeadLossSPFn(torch.autograd.Function):
     @staticmethod
+    @_nvtx("head.sp.fwd")
     def forward(ctx, x_l, targets_flat, rt, ignore_index, *params):
         n = pm.pgm.tp_size
         head = rt.model.lm_head
@@ -668,6 +743,7 @@ class FusedHeadLossSPFn(torch.autograd.Function):
         return loss
 
     @staticmethod
+    @_nvtx("head.sp.bwd")
     def backward(ctx, gout):
         x_l, targets_flat, h, rstd, logits, all_stats, loss_acc = ctx.saved_tensors
         rt = ctx.rt
@@ -690,8 +766,35 @@ class FusedHeadLossSPFn(torch.autograd.Function):
 # The norm that OPENS a block is therefore computed by the kernel that CLOSES the previous one: autograd carries only
 # the fp32 local rows x_l between the Functions; the gathered activations travel through the runtime (put_handoff /
 # take_handoff forward, put_stash / take_stash backward) and are checked against the tensor they belong to.
+# GEMM + hand-off as ONE kernel (csrc/gemm_handoff.cu: tile flags instead of the opening barrier, the reduction of the
+# first row-blocks under the GEMM of the later ones) or as 2-SM GEMM + stand-alone hand-off kernel.
+def _fused_gemm_handoff() -> bool:
+    return os.environ.get("DPFS_SP_FUSED_GEMM", "0") == "1"
+
+
+def _handoff_fwd(a, w, x_l, bias, scale, eps, zone):
+    """(x_out_l, h gathered, rstd) of x_out_l = x_l + reduce_scatter(a @ w^T) + bias, h = rmsnorm(x_out_l) * scale."""
+    symm = pm.pgm.symm
+    if _fused_gemm_handoff() and fused.can_gemm_handoff(symm, a, w):
+        return fused.gemm_handoff_fwd(symm, a, w, False, x_l, bias, scale, eps, zone)
+    part = symm.buffer((a.shape[0], w.shape[0]), BF16)
+    gemm_nt(a, w, out=part)
+    return fused.rs_add_rmsnorm_ag(symm, part, x_l, bias, scale, eps, zone)
+
+
+def _handoff_bwd(dy, w, x_l, rstd, scale, dres_l, zone, dscale_out, dbias_out):
+    """(dx_l, dx gathered) of dx_l = dres_l + rmsnorm'(reduce_scatter(dy @ w)) (column-parallel dgrad + hand-off)."""
+    symm = pm.pgm.symm
+    if _fused_gemm_handoff() and fused.can_gemm_handoff(symm, dy, w, True):
+        return fused.gemm_handoff_bwd(symm, dy, w, True, x_l, rstd, scale, dres_l, zone, dscale_out, dbias_out)
+    part = symm.buffer((dy.shape[0], w.shape[1]), BF16)
+    gemm_nt(dy, w, b_mn_major=True, out=part)
+    return fused.rs_rmsnorm_bwd_ag(symm, part, x_l, rstd, scale, dres_l, zone, dscale_out, dbias_out)
+
+
 class HandoffEmbedFn(torch.autograd.Function):
     @staticmethod
+    @_nvtx("embed.handoff.fwd")
     def forward(ctx, ids_flat, rt, weight):
         emb = rt.model.embedding
         symm = pm.pgm.symm
@@ -706,6 +809,7 @@ class HandoffEmbedFn(torch.autograd.Function):
         return x_l
 
     @staticmethod
+    @_nvtx("embed.handoff.bwd")
     def backward(ctx, dx_l):
         (ids_flat,) = ctx.saved_tensors
         rt = ctx.rt
@@ -716,11 +820,13 @@ class HandoffEmbedFn(torch.autograd.Function):
                             zero_first=True)
         # last node of the backward pass: complete the gradients of the replicated parameters (partial sums over rows)
         comm_ops.all_reduce_sum_(rt.arena.norm_grads)
+        rt.join_side()                    # the weight gradients computed on the side stream are complete from here on
         return None, None, None
 
 
 class HandoffLayerFn(torch.autograd.Function):
     @staticmethod
+    @_nvtx("layer{i}.handoff.fwd")
     def forward(ctx, x_l, pos, rt, pack: LayerPack, meta: Meta, *params):
         m = meta
         symm = pm.pgm.symm
@@ -729,54 +835,48 @@ class HandoffLayerFn(torch.autograd.Function):
         qkv = gemm_nt(h1, pack.wqkv, bias=pack.bqkv, out_dtype=BF16)
         fused.rope_inplace(qkv, pos, rt.cos_half, rt.sin_half, 2, m.Dl, m.Hl, m.hd, inverse=False)
         attn, lse = attn_fwd(qkv, m.B, m.T, m.Hl, m.hd, m.scale)
-        part = symm.buffer((m.M, m.d), BF16)
-        gemm_nt(attn, pack.wo, out=part)
-        x2_l, h2, rstd2 = fused.rs_add_rmsnorm_ag(symm, part, x_l, pack.bo, pack.s2, rt.eps, rt._zones[2 * li + 1])
+        x2_l, h2, rstd2 = _handoff_fwd(attn, pack.wo, x_l, pack.bo, pack.s2, rt.eps, rt._zones[2 * li + 1])
         gu = gemm_nt(h2, pack.wgu, bias=pack.bgu, out_dtype=BF16)
         act = fused.swiglu_fwd(gu)
-        gemm_nt(act, pack.wd, out=part)
         nxt = rt.packs[li + 1].s1 if li + 1 < len(rt.packs) else rt.sN      # the norm that opens the next block
-        x3_l, hn, rstdn = fused.rs_add_rmsnorm_ag(symm, part, x2_l, pack.bd, nxt, rt.eps, rt._zones[2 * li + 2])
+        x3_l, hn, rstdn = _handoff_fwd(act, pack.wd, x2_l, pack.bd, nxt, rt.eps, rt._zones[2 * li + 2])
         rt.put_handoff(x3_l, hn, rstdn)
         ctx.save_for_backward(x_l, pos, h1, rstd1, qkv, attn, lse, x2_l, h2, rstd2, gu, act)
         ctx.pack, ctx.meta, ctx.rt = pack, meta, rt
         return x3_l
 
     @staticmethod
+    @_nvtx("layer{i}.handoff.bwd")
     def backward(ctx, dx3_l):
         x_l, pos, h1, rstd1, qkv, attn, lse, x2_l, h2, rstd2, gu, act = ctx.saved_tensors
         pack, m, rt = ctx.pack, ctx.meta, ctx.rt
         symm = pm.pgm.symm
-        bzone = rt._zones[-1]
         dx3_l = dx3_l.contiguous()
         dx3 = rt.take_stash(dx3_l)        # gathered bf16 [M, d] from the hand-off that closed the block above
         assert dx3 is not None
         dact = gemm_nt(dx3, pack.wd, b_mn_major=True, out_dtype=BF16)
-        _wgrad(dx3, act, pack.g_wd)
+        rt.on_side(lambda: _wgrad(dx3, act, pack.g_wd), keep=(dx3, act), reads_bzone=True)
         dgu = fused.swiglu_bwd_bias(dact, gu, pack.g_bgu)
         del dact
-        part = symm.buffer((m.M, m.d), BF16)
-        gemm_nt(dgu, pack.wgu, b_mn_major=True, out=part)
-        _wgrad(dgu, h2, pack.g_wgu)
-        del dgu
+        rt.on_side(lambda: _wgrad(dgu, h2, pack.g_wgu), keep=(dgu, h2))
         # dx2 is the output gradient of wo's residual add: its (local) column sums are the wo bias gradient
-        dx2_l, dx2 = fused.rs_rmsnorm_bwd_ag(symm, part, x2_l, rstd2, pack.s2, dx3_l, bzone, pack.g_s2, pack.g_bo)
+        dx2_l, dx2 = _handoff_bwd(dgu, pack.wgu, x2_l, rstd2, pack.s2, dx3_l, rt.next_bzone(), pack.g_s2, pack.g_bo)
         dattn = gemm_nt(dx2, pack.wo, b_mn_major=True, out_dtype=BF16)
-        _wgrad(dx2, attn, pack.g_wo)
+        rt.on_side(lambda: _wgrad(dx2, attn, pack.g_wo), keep=(dx2, attn), reads_bzone=True)
         dqkv = attn_bwd(qkv, attn, dattn, lse, m.B, m.T, m.Hl, m.hd, m.scale)
         fused.rope_inplace(dqkv, pos, rt.cos_half, rt.sin_half, 2, m.Dl, m.Hl, m.hd, inverse=True)
-        gemm_nt(dqkv, pack.wqkv, b_mn_major=True, out=part)
-        _wgrad(dqkv, h1, pack.g_wqkv)
+        rt.on_side(lambda: _wgrad(dqkv, h1, pack.g_wqkv), keep=(dqkv, h1))
         fused.colsum(dqkv, out=pack.g_bqkv)
         # dx is the output gradient of the block below (its down_proj bias gradient comes from the same pass)
         prev_bd = pack.prev.g_bd if pack.prev is not None else None
-        dx_l, dx = fused.rs_rmsnorm_bwd_ag(symm, part, x_l, rstd1, pack.s1, dx2_l, bzone, pack.g_s1, prev_bd)
+        dx_l, dx = _handoff_bwd(dqkv, pack.wqkv, x_l, rstd1, pack.s1, dx2_l, rt.next_bzone(), pack.g_s1, prev_bd)
         rt.put_stash(dx_l, dx)
         return (dx_l, None, None, None, None) + (None,) * len(pack.params)
 
 
 class HandoffHeadLossFn(torch.autograd.Function):
     @staticmethod
+    @_nvtx("head.handoff.fwd")
     def forward(ctx, x_l, targets_flat, rt, ignore_index, *params):
         n = pm.pgm.tp_size
         head = rt.model.lm_head
@@ -794,6 +894,7 @@ class HandoffHeadLossFn(torch.autograd.Function):
         return loss
 
     @staticmethod
+    @_nvtx("head.handoff.bwd")
     def backward(ctx, gout):
         x_l, targets_flat, h, rstd, logits, all_stats, loss_acc = ctx.saved_tensors
         rt = ctx.rt
@@ -802,12 +903,8 @@ class HandoffHeadLossFn(torch.autograd.Function):
         up = gout.detach().reshape(1).float().contiguous()
         dlogits = fused.ce_grad(logits, targets_flat, all_stats, n, loss_acc, ctx.vocab_start, ctx.ignore_index,
                                 upstream=up)
-        M, d = h.shape
-        part = symm.buffer((M, d), BF16)
-        gemm_nt(dlogits, rt.wlm, b_mn_major=True, out=part)
-        _wgrad(dlogits, h, rt.g_wlm)
+        rt.on_side(lambda: _wgrad(dlogits, h, rt.g_wlm), keep=(dlogits, h))
         fused.colsum(dlogits, out=rt.g_blm)
-        dx_l, dx = fused.rs_rmsnorm_bwd_ag(symm, part, x_l, rstd, rt.sN, None, rt._zones[-1], rt.g_sN,
-                                           rt.packs[-1].g_bd)
+        dx_l, dx = _handoff_bwd(dlogits, rt.wlm, x_l, rstd, rt.sN, None, rt.next_bzone(), rt.g_sN, rt.packs[-1].g_bd)
         rt.put_stash(dx_l, dx)
         return (dx_l, None, None, None) + (None,) * 3

@@ -74,6 +74,11 @@ SIGS = {
     "dpfs_rs_add_rmsnorm_ag": (c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_int, c_int, c_f, c_p, c_int, c_int, c_p),
     "dpfs_rs_rmsnorm_bwd_ag": (c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_int, c_p, c_int, c_int, c_p, c_int,
                                c_int, c_p),
+    "dpfs_gemm_handoff_fwd": (c_p, c_ll, c_p, c_ll, c_int, c_p, c_p, c_int, c_int, c_int, c_p, c_p, c_p, c_p, c_p, c_p,
+                              c_f, c_p, c_int, c_int, c_p),
+    "dpfs_gemm_handoff_bwd": (c_p, c_ll, c_p, c_ll, c_int, c_p, c_p, c_int, c_int, c_int, c_p, c_p, c_p, c_p, c_p, c_p,
+                              c_p, c_p, c_p, c_p, c_int, c_int, c_p),
+    "dpfs_gemm_handoff_scratch_rows": (),
     "dpfs_sp_blocks": (c_int, c_int),
     "dpfs_sp_debug_config": (c_int, c_int),
     "dpfs_comm_barrier_ex": (c_p, c_int, c_int, c_int, c_int, c_int, c_p),

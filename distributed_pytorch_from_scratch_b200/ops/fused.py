@@ -228,6 +228,60 @@ def rs_rmsnorm_bwd_ag(symm, part: torch.Tensor, x_l: torch.Tensor, rstd: torch.T
     return dx_l, (zone.view((M, D), BF16) if zone is not None else None)
 
 
+def can_gemm_handoff(symm, a: torch.Tensor, w: torch.Tensor, b_mn_major: bool = False) -> bool:
+    """Whether GEMM + hand-off can run as ONE kernel (csrc/gemm_handoff.cu) for a @ w^T (or a @ w)."""
+    M = a.shape[0]
+    N = w.shape[1] if b_mn_major else w.shape[0]
+    tiles = ((M + 127) // 128) * ((N + 255) // 256)
+    return (bool(symm.mc_base) and not symm.closed and a.dtype == BF16 and w.dtype == BF16 and N % 8 == 0
+            and N <= 1024 and M % symm.n == 0 and M // symm.n >= 128 and a.stride(0) % 8 == 0
+            and w.stride(0) % 8 == 0 and a.stride(1) == 1 and w.stride(1) == 1 and tiles <= 16384
+            and M * N * 2 <= symm.ag_off)
+
+
+def gemm_handoff_fwd(symm, a: torch.Tensor, w: torch.Tensor, b_mn_major: bool, x_l: Optional[torch.Tensor],
+                     bias: Optional[torch.Tensor], scale: torch.Tensor, eps: float, zone):
+    """ONE kernel: x_out_l = x_l + reduce_scatter(a @ w^T) + bias; h = all_gather(rmsnorm(x_out_l) * scale).
+    Returns (x_out_l fp32 [M/n, N], h bf16 [M, N] (view of ``zone``), rstd fp32 [M/n])."""
+    M, K = a.shape
+    N = w.shape[1] if b_mn_major else w.shape[0]
+    n = symm.n
+    Ml = M // n
+    part = symm.buffer((M, N), BF16)
+    mc_part = symm.mc_base + (part.data_ptr() - symm.base)
+    x_out = torch.empty((Ml, N), dtype=F32, device=a.device)
+    rstd = torch.empty(Ml, dtype=F32, device=a.device)
+    rc = _lib.lib().dpfs_gemm_handoff_fwd(a.data_ptr(), a.stride(0), w.data_ptr(), w.stride(0), int(b_mn_major),
+                                          part.data_ptr(), mc_part, M, N, K, _lib.ptr(x_l), _lib.ptr(bias),
+                                          scale.data_ptr(), x_out.data_ptr(), rstd.data_ptr(), zone.mc, eps,
+                                          symm.flag_ptrs, symm.rank, n, _lib.stream())
+    _lib.check(rc, "dpfs_gemm_handoff_fwd")
+    return x_out, zone.view((M, N), BF16), rstd
+
+
+def gemm_handoff_bwd(symm, a: torch.Tensor, w: torch.Tensor, b_mn_major: bool, x_l: torch.Tensor, rstd: torch.Tensor,
+                     scale: torch.Tensor, dres_l: Optional[torch.Tensor], zone, dscale_out: torch.Tensor,
+                     dbias_out: Optional[torch.Tensor] = None):
+    """ONE kernel: dx_l = dres_l + rmsnorm'(reduce_scatter(a @ w)); bf16(dx) all-gathered into ``zone``.
+    Returns (dx_l fp32 [M/n, N], dx bf16 [M, N] view)."""
+    M, K = a.shape
+    N = w.shape[1] if b_mn_major else w.shape[0]
+    n = symm.n
+    Ml = M // n
+    lib = _lib.lib()
+    part = symm.buffer((M, N), BF16)
+    mc_part = symm.mc_base + (part.data_ptr() - symm.base)
+    dx_l = torch.empty((Ml, N), dtype=F32, device=a.device)
+    scratch = _scratch(a.device, "gh_norm", lib.dpfs_gemm_handoff_scratch_rows() * 2 * N)
+    rc = lib.dpfs_gemm_handoff_bwd(a.data_ptr(), a.stride(0), w.data_ptr(), w.stride(0), int(b_mn_major),
+                                   part.data_ptr(), mc_part, M, N, K, x_l.data_ptr(), rstd.data_ptr(),
+                                   scale.data_ptr(), _lib.ptr(dres_l), dx_l.data_ptr(), zone.mc,
+                                   _lib.ptr(dscale_out), _lib.ptr(dbias_out), scratch.data_ptr(), symm.flag_ptrs,
+                                   symm.rank, n, _lib.stream())
+    _lib.check(rc, "dpfs_gemm_handoff_bwd")
+    return dx_l, zone.view((M, N), BF16)
+
+
 # ------------------------------------------------------------------------------------------------ LayerNorm
 def layernorm_fwd(x, gamma, beta, eps: float, out_dtype=BF16):
     D = x.shape[-1]

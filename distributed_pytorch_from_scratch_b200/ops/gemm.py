@@ -22,12 +22,14 @@ _USE_2SM = os.environ.get("DPFS_GEMM_2SM", "1") == "1"
 
 
 def _workspace(device, nfloats: int) -> torch.Tensor:
-    ws = _WS.get(device)
+    # one workspace per (device, stream): GEMMs on different streams may run concurrently
+    key = (device, torch.cuda.current_stream(device).cuda_stream)
+    ws = _WS.get(key)
     if ws is None or ws.numel() < nfloats:
         if ws is not None:
             _WS_RETIRED.append(ws)
         ws = torch.empty(max(nfloats, 1 << 22), dtype=torch.float32, device=device)
-        _WS[device] = ws
+        _WS[key] = ws
     return ws
 
 

@@ -74,6 +74,9 @@ class SymmComm:
             self._push_zone = 0
         self.closed = False
         self._zone_allocs = []
+        self._poison = os.environ.get("DPFS_SYMM_POISON", "0") == "1"
+        self._poison_half = (self.ag_off // 2) // 256 * 256
+        self._poison_side, self._poison_used = 0, 0
         # data path of the reduce: "p2p" (plain NVLink loads/stores, rank-ordered fp32 sums) or "nvls" (multimem.*)
         # Measured (profiles/comm_paths_r1.md): P2P wins at TP=2 (100 vs 116 us for 32.8 MB), NVLS wins at TP=8 (123 vs
         # 143 us; NCCL 158 us) because the switch-side reduction moves S(1+1/n) bytes instead of 2S(n-1)/n.
@@ -136,6 +139,16 @@ class SymmComm:
             numel *= s
         nbytes = numel * torch.empty((), dtype=dtype).element_size()
         assert offset_bytes % 256 == 0 and offset_bytes + nbytes <= self.ag_off, "symmetric buffer too small"
+        if self._poison and offset_bytes == 0 and nbytes <= self._poison_half:
+            # Debug mode (DPFS_SYMM_POISON=1): results handed out as views of this buffer are only valid until the next
+            # collective.  Alternate between the two halves and fill the one retired by this call with NaNs, so a
+            # consumer that reads a stale view gets NaNs (and a NaN loss) instead of silently reading newer data.
+            self._poison_side ^= 1
+            offset_bytes = self._poison_side * self._poison_half
+            old = (1 - self._poison_side) * self._poison_half
+            if self._poison_used:
+                self.data[old:old + self._poison_used].view(torch.int16).fill_(0x7FC0)      # bf16 NaN pattern
+            self._poison_used = (nbytes + 1) // 2 * 2
         return self.data[offset_bytes:offset_bytes + nbytes].view(dtype).view(*shape)
 
     def _inside(self, t: torch.Tensor) -> bool:

@@ -87,7 +87,25 @@ int dpfs_rs_rmsnorm_bwd_ag(const void* mc_partial, const float* x_l, const float
                            int accumulate, float* scratch, int rows_per_rank, int D,
                            const unsigned long long* flag_ptrs, int rank, int n, cudaStream_t stream);
 int dpfs_sp_blocks(int rows_per_rank, int D);
-/* Tuning hook of the two kernels above (tools/bench_handoff.py): grid_cap = most blocks to launch (0 = as many as are
+/* The same hand-offs with the row-parallel GEMM in front of them in the SAME kernel (csrc/gemm_handoff.cu): the 1-SM
+ * tcgen05 GEMM writes bf16 partial tiles into `partial` (this rank's symmetric buffer, multicast alias mc_partial) and
+ * flags them to the owners of their rows; comm warps of the same CTAs pull / row-op / push 16-row slices as soon as all
+ * n ranks have flagged their tiles.  No opening barrier (tile flags carry a launch epoch kept in device memory, so the
+ * call is CUDA-graph replayable), one closing grid-wide rank barrier.  A: bf16 [M][lda] (K-major); B: [N][ldb] or, with
+ * b_mn_major, [K][ldb]; N = model width, N % 8 == 0, N <= 1024, M % n == 0, M / n >= 128.  Other arguments as above;
+ * the backward's scratch holds dpfs_gemm_handoff_scratch_rows() x 2N floats.  No counterpart in the reference beyond
+ * the call sites cited above (it runs cuBLAS, then NCCL, then ATen kernels). */
+int dpfs_gemm_handoff_fwd(const void* A, long long lda, const void* B, long long ldb, int b_mn_major, void* partial,
+                          const void* mc_partial, int M, int N, int K, const float* x_l, const float* bias,
+                          const float* scale, float* xout_l, float* rstd_l, void* mc_h, float eps,
+                          const unsigned long long* flag_ptrs, int rank, int n, cudaStream_t stream);
+int dpfs_gemm_handoff_bwd(const void* A, long long lda, const void* B, long long ldb, int b_mn_major, void* partial,
+                          const void* mc_partial, int M, int N, int K, const float* x_l, const float* rstd_l,
+                          const float* scale, const float* dres_l, float* dx_l, void* mc_dx, float* dscale_out,
+                          float* dbias_out, float* scratch, const unsigned long long* flag_ptrs, int rank, int n,
+                          cudaStream_t stream);
+int dpfs_gemm_handoff_scratch_rows(void);
+/* Tuning hook of the two stand-alone kernels above (tools/bench_handoff.py): grid_cap = most blocks to launch (0 = as many as are
  * resident at once), bar_mode = 0 one rank barrier per block (n remote atomics each), 1 grid-wide barrier with a
  * single n-way exchange per rank (default), 2 no barrier (timing of the data phase only; results are undefined). */
 int dpfs_sp_debug_config(int grid_cap, int bar_mode);

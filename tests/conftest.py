@@ -12,6 +12,7 @@ os.environ.setdefault("DPFS_NO_TQDM", "1")
 
 def pytest_configure(config):
     config.addinivalue_line("markers", "gpu: needs a CUDA GPU (B200); run with `-m gpu` on the GPU box")
+    config.addinivalue_line("markers", "slow: the reference's full-depth grids / 1000-step histories (minutes)")
 
 
 def pytest_collection_modifyitems(config, items):

@@ -199,8 +199,114 @@ def _handoff_worker(rank, world):
     torch.cuda.synchronize()
 
 
-def _model_worker(rank, world, comm, sp=False):
+def _gemm_handoff_worker(rank, world):
+    """GEMM + hand-off in ONE kernel (csrc/gemm_handoff.cu) against fp32 PyTorch matmul + NCCL sum + the row op in
+    plain PyTorch: row ranges that straddle the 128-row tiles, all three row widths, K-major and MN-major weights,
+    repeated calls (the tile flags carry a launch epoch that has to advance in step on every rank)."""
+    import torch.distributed as dist
+    from distributed_pytorch_from_scratch_b200.ops import fused
+    from distributed_pytorch_from_scratch_b200.parallel.symm import try_enable_symm
+    symm = try_enable_symm(required=True)
+    if not symm.mc_base:
+        return
+    torch.manual_seed(500 + rank)
+
+    def gather(t):
+        out = torch.empty((world * t.shape[0],) + tuple(t.shape[1:]), dtype=t.dtype, device=t.device)
+        dist.all_gather_into_tensor(out, t.contiguous())
+        return out
+
+    for (Ml, N, K) in [(500, 512, 256), (256, 1024, 128), (130, 256, 64), (4000, 512, 64)]:
+        M = Ml * world
+        zones = symm.alloc_zones(2, M * N * 2)
+        a = (torch.randn(M, K, device="cuda") * 0.5).to(torch.bfloat16)
+        w = (torch.randn(N, K, device="cuda") * 0.5).to(torch.bfloat16)          # forward: [N, K], K-major
+        wt = w.t().contiguous()                                                    # backward: [K, N], MN-major
+        assert fused.can_gemm_handoff(symm, a, w) and fused.can_gemm_handoff(symm, a, wt, True)
+        total = a.float() @ w.float().t()
+        dist.all_reduce(total)
+        y_l = total[rank * Ml:(rank + 1) * Ml]
+        sc_ = max(1.0, y_l.abs().max().item())
+        x_l = torch.randn(Ml, N, device="cuda")
+        bias, scale = torch.randn(N, device="cuda"), torch.rand(N, device="cuda") + 0.5
+        for rnd in range(3):
+            xo, h, rstd = fused.gemm_handoff_fwd(symm, a, w, False, x_l, bias, scale, 1e-5, zones[0])
+            xo_ref = x_l + y_l + bias
+            rstd_ref = torch.rsqrt(xo_ref.pow(2).mean(-1) + 1e-5)
+            h_ref = gather((xo_ref * rstd_ref[:, None] * scale).to(torch.bfloat16))
+            assert (xo - xo_ref).abs().max().item() < 0.03 * sc_, (Ml, N, K, rnd, (xo - xo_ref).abs().max().item())
+            assert (h.float() - h_ref.float()).abs().max().item() < 0.05, (Ml, N, K, rnd)
+            assert torch.equal(h, gather(h[rank * Ml:(rank + 1) * Ml])), "ranks disagree on the gathered rows"
+            dres = torch.randn(Ml, N, device="cuda")
+            ds, db = torch.empty(N, device="cuda"), torch.empty(N, device="cuda")
+            dx_l, dx = fused.gemm_handoff_bwd(symm, a, wt, True, x_l, rstd_ref, scale, dres, zones[1], ds, db)
+            xh = x_l * rstd_ref[:, None]
+            g = y_l * scale
+            dx_ref = dres + rstd_ref[:, None] * (g - xh * (g * xh).mean(-1, keepdim=True))
+            tol = 0.03 * max(1.0, dx_ref.abs().max().item())
+            assert (dx_l - dx_ref).abs().max().item() < tol, (Ml, N, K, rnd)
+            assert (dx.float() - gather(dx_ref.to(torch.bfloat16)).float()).abs().max().item() < tol
+            ds_ref, db_ref = (y_l * xh).sum(0), dx_ref.sum(0)
+            assert (ds - ds_ref).abs().max().item() < 0.02 * ds_ref.abs().max().item() + 0.5
+            assert (db - db_ref).abs().max().item() < 0.02 * db_ref.abs().max().item() + 0.5
+    torch.cuda.synchronize()
+
+
+def _layers_worker(rank, world):
+    """A toy model built ONLY from the public layer classes (no Transformer.loss): with the symmetric communicator on,
+    RowParallelLinear.forward and ColumnParallelLinear's backward run the one-kernel GEMM + all-reduce and the
+    embedding runs the native lookup (+ owner scatter); results match the same layers over NCCL collectives."""
     import process_manager as pm
+    from torch.profiler import ProfilerActivity, profile
+    from distributed_pytorch_from_scratch_b200.parallel.symm import try_enable_symm
+    from models.layers import ColumnParallelLinear, ParallelVocabularyEmbedding, RowParallelLinear
+
+    torch.manual_seed(7)
+    torch.cuda.manual_seed(7)
+    V, D, F_ = 1024, 512, 1024
+    emb, col, row = ParallelVocabularyEmbedding(V, D).cuda(), ColumnParallelLinear(D, F_, gather_output=False).cuda(), \
+        RowParallelLinear(F_, D, split_input=False).cuda()
+    for m in (emb, col, row):
+        m.reset_parameters()
+    with torch.no_grad():
+        col.bias.normal_(); row.bias.normal_()
+    ids = torch.randint(0, V, (8, 250), device="cuda")
+    torch.distributed.broadcast(ids, 0)
+
+    def run():
+        for m in (emb, col, row):
+            m.zero_grad(set_to_none=True)
+        with torch.autocast("cuda", dtype=torch.bfloat16):
+            y = row(torch.nn.functional.silu(col(emb(ids).to(torch.bfloat16))))
+        loss = y.float().pow(2).mean()
+        loss.backward()
+        return y.detach().float().clone(), [p.grad.detach().float().clone() for m in (emb, col, row)
+                                            for p in m.parameters()]
+
+    y_ref, g_ref = run()                      # NCCL collectives (pgm.symm is None)
+    symm = try_enable_symm(required=True)
+    run()
+    with profile(activities=[ProfilerActivity.CUDA]) as prof:
+        y, g = run()
+        torch.cuda.synchronize()
+    names = [e.name for e in prof.events() if e.device_type == torch.autograd.DeviceType.CUDA]
+    fused_ar = [n for n in names if "gemm_bf16_kernel" in n and "true, false>" in n.replace("(bool)1", "true")
+                .replace("(bool)0", "false")]
+    assert len(fused_ar) >= 2, names          # row-parallel forward + column-parallel dgrad
+    assert any("embedding_fwd" in n for n in names) and any("embedding_bwd" in n for n in names), names
+    assert not any("nccl" in n.lower() and "AllReduce" in n for n in names), names
+    assert (y - y_ref).abs().max().item() < 0.05 * max(1.0, y_ref.abs().max().item())
+    for a, b in zip(g, g_ref):
+        assert (a - b).norm().item() <= 0.03 * b.norm().item() + 1e-6
+    pm.pgm.symm = None
+
+
+def _model_worker(rank, world, comm, sp=False, poison=False, fused_gemm=False):
+    import process_manager as pm
+    if fused_gemm:   # GEMM + hand-off as one kernel (read at import of models.fused_transformer)
+        os.environ["DPFS_SP_FUSED_GEMM"] = "1"
+    if poison:      # debug mode: views of the symmetric buffer that outlive the next collective read as NaN
+        os.environ["DPFS_SYMM_POISON"] = "1"
     from distributed_pytorch_from_scratch_b200.engine import TrainStep
     from distributed_pytorch_from_scratch_b200.ops.optim import FusedAdam
     from distributed_pytorch_from_scratch_b200.parallel.symm import try_enable_symm
@@ -277,6 +383,16 @@ def test_push_allgather_producers(world):
 
 
 @pytest.mark.parametrize("world", _worlds())
+def test_gemm_handoff_one_kernel(world):
+    run_distributed(_gemm_handoff_worker, world, free_port(), backend="nccl")
+
+
+@pytest.mark.parametrize("world", _worlds())
+def test_public_layer_classes_run_fused_collectives(world):
+    run_distributed(_layers_worker, world, free_port(), backend="nccl")
+
+
+@pytest.mark.parametrize("world", _worlds())
 def test_sp_handoff_kernels(world):
     run_distributed(_handoff_worker, world, free_port(), backend="nccl")
 
@@ -285,6 +401,19 @@ def test_sp_handoff_kernels(world):
 @pytest.mark.parametrize("comm", ["nccl", "fused"])
 def test_fused_transformer_matches_oracle(world, comm):
     run_distributed(_model_worker, world, free_port(), backend="nccl", args=(comm,))
+
+
+@pytest.mark.skipif(_ngpu() < 2, reason="needs >= 2 GPUs")
+@pytest.mark.parametrize("sp", [False, True])
+def test_no_stale_symmetric_views_under_poison_mode(sp):
+    """DPFS_SYMM_POISON=1 NaN-fills every symmetric-buffer view as soon as the next collective retires it: the model
+    still matches the oracle and trains, so no consumer reads a result past its lifetime."""
+    run_distributed(_model_worker, 2, free_port(), backend="nccl", args=("fused", sp, True))
+
+
+@pytest.mark.parametrize("world", _worlds())
+def test_sequence_parallel_one_kernel_gemm_handoff_matches_oracle(world):
+    run_distributed(_model_worker, world, free_port(), backend="nccl", args=("fused", True, False, True))
 
 
 @pytest.mark.parametrize("world", _worlds())

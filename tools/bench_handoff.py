@@ -101,8 +101,8 @@ ds, db = torch.empty(D, device="cuda"), torch.empty(D, device="cuda")
 out("| kernel | barrier | grid cap | landing zone | us |")
 out("|---|---|---|---|---|")
 state = {"i": 0}
-for bar, bname in [(1, "grid-wide"), (0, "per block"), (2, "none")]:
-    for cap in (0, 74, 37):
+for bar, bname in [(1, "grid-wide, 1 fence / block"), (3, "grid-wide, fence / thread"), (0, "per block"), (2, "none")]:
+    for cap in (0, 74, 37, 24, 16):
         lib.dpfs_sp_debug_config(cap, bar)
         for rot in (False, True):
             def fwd():

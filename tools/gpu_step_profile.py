@@ -94,6 +94,19 @@ def main():
             tr = ev.time_range
             t_first = tr.start if t_first is None else min(t_first, tr.start)
             t_last = tr.end if t_last is None else max(t_last, tr.end)
+    # per-rank view of the last profiled step (all ranks): compute time outside the hand-off kernels shows a slow GPU,
+    # per-instance hand-off durations show who waits for whom (the rank that arrives last has the shortest kernel)
+    evs = sorted((ev for ev in prof.events() if ev.device_type == torch.autograd.DeviceType.CUDA),
+                 key=lambda e: e.time_range.start)
+    per_step = len(evs) // nprof
+    last = evs[-per_step:]
+    def dur(e):
+        d = getattr(e, "device_time", None)
+        return e.cuda_time if d is None else d
+    hand = [(short(e.name)[:24], dur(e)) for e in last if "_ag_kernel" in e.name]
+    other = sum(dur(e) for e in last if "_ag_kernel" not in e.name)
+    gathered = [None] * world
+    torch.distributed.all_gather_object(gathered, {"rank": rank, "other_us": other, "hand": hand})
     total = sum(v[0] for v in tot.values())
     span = (t_last - t_first) / nprof if t_first is not None else 0.0
     mode = "eager" if args.eager else "CUDA-graph replay"
@@ -107,6 +120,19 @@ def main():
     for name, (t, n) in sorted(tot.items(), key=lambda kv: -kv[1][0]):
         n1 = n / nprof
         lines.append(f"| {t / 1e3:.3f} | {100 * t / total:.1f}% | {n1:g} | {t / n1:.1f} | {name} |")
+    if world > 1 and gathered[0]["hand"]:
+        lines += ["", "## Per-rank view of one step", "",
+                  "| rank | kernel time outside the hand-off kernels (ms) | hand-off kernels (ms) |", "|---|---|---|"]
+        for g in gathered:
+            lines.append(f"| {g['rank']} | {g['other_us'] / 1e3:.3f} | {sum(d for _, d in g['hand']) / 1e3:.3f} |")
+        n_inst = min(len(g["hand"]) for g in gathered)
+        lines += ["", "Duration (us) of every hand-off kernel of the step, in launch order, on each rank (the rank with the "
+                  "shortest one arrived last at the opening barrier):", "",
+                  "| # | kernel | " + " | ".join(f"r{g['rank']}" for g in gathered) + " |",
+                  "|---|---|" + "---|" * world]
+        for i in range(n_inst):
+            lines.append(f"| {i} | {gathered[0]['hand'][i][0]} | "
+                         + " | ".join(f"{g['hand'][i][1]:.0f}" for g in gathered) + " |")
     out = "\n".join(lines) + "\n"
     if rank == 0:
         os.makedirs(os.path.join(REPO, "gpurun_out"), exist_ok=True)
