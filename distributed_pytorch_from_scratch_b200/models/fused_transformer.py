@@ -769,7 +769,9 @@ class FusedHeadLossSPFn(torch.autograd.Function):
 # GEMM + hand-off as ONE kernel (csrc/gemm_handoff.cu: tile flags instead of the opening barrier, the reduction of the
 # first row-blocks under the GEMM of the later ones) or as 2-SM GEMM + stand-alone hand-off kernel.
 def _fused_gemm_handoff() -> bool:
-    return os.environ.get("DPFS_SP_FUSED_GEMM", "0") == "1"
+    # default on: 14.19 vs 14.56 ms / step at TP=2 (profiles/bench_tp2_r2.md); DPFS_SP_FUSED_GEMM=0 selects the
+    # 2-SM GEMM + stand-alone hand-off kernel
+    return os.environ.get("DPFS_SP_FUSED_GEMM", "1") == "1"
 
 
 def _handoff_fwd(a, w, x_l, bias, scale, eps, zone):
