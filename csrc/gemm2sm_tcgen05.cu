@@ -38,11 +38,14 @@ constexpr int kOutBufs = 2;
 // columns), five stages -- for short K (<= 1024), where a 256x256 tile's main loop (2.2 us at K = 512) is shorter
 // than one warp set's epilogue and the epilogue paces the kernel.  (10 warps put 3 on one SM sub-partition, so the
 // compiler caps that shape at 168 registers: 16384 / 3 per warp.)
-template <int EW>
+// SWIGLU flavour (gate|up projection with the activation in the epilogue, see gemm2sm_kernel): three output slabs per
+// warp (gate, up, act) instead of a ring of two, paid for with one operand stage (K = d is short there anyway).
+template <int EW, bool SWIGLU = false>
 struct Cfg {
-  static constexpr int kStages = EW == 8 ? 5 : 6;
+  static constexpr int kStages = SWIGLU ? 4 : (EW == 8 ? 5 : 6);
   static constexpr int kThreads = 64 + EW * 32;
-  static constexpr int kOutStageBytes = EW * kOutBufs * 4096;
+  static constexpr int kBufs = SWIGLU ? 3 : kOutBufs;
+  static constexpr int kOutStageBytes = EW * kBufs * 4096;
   static constexpr int kSmem = kStages * kStageBytes + kOutStageBytes + 256 + 1024;
   static_assert(kSmem <= 232448, "exceeds the 227 KB shared-memory limit");
 };
@@ -56,6 +59,7 @@ struct Args {
   const float* bias;
   const float* residual;
   long long ldr;
+  int F;  // SWIGLU flavour: hidden units (N = 2 F: gate rows [0, F), up rows [F, 2F) of B)
 };
 
 __device__ __forceinline__ uint32_t cluster_ctarank() {
@@ -134,12 +138,20 @@ __device__ __forceinline__ void store32<__nv_bfloat16>(__nv_bfloat16* dst, const
   }
 }
 
-template <bool A_MN, bool B_MN, typename OutT, int EW>
-__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(Cfg<EW>::kThreads, 1)
+// SWIGLU (forward of the fused gate|up projection, EW = 8, K-major operands, bf16 out): the B tile of a CTA pair is
+// "128 gate rows | the 128 up rows of the SAME hidden units" (CTA 0 loads rows [128 j, +128), CTA 1 rows [F + 128 j,
+// +128) of the concatenated weight), so an accumulator row holds g in TMEM columns [0, 128) and u in [128, 256) and an
+// epilogue thread has both of a hidden unit in registers: it emits gate|up (+ bias, bf16: the backward needs it) AND
+// act = silu(g) * u (through tmAct) in one pass -- the 2 x M x F re-read of the stand-alone SwiGLU kernel disappears.
+// Parameters, checkpoints, wgrad and dgrad are untouched.  ref: models/model.py:95.
+template <bool A_MN, bool B_MN, typename OutT, int EW, bool SWIGLU = false>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(Cfg<EW, SWIGLU>::kThreads, 1)
 gemm2sm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
-               const __grid_constant__ CUtensorMap tmOut, const Args args) {
-  constexpr int kStages = Cfg<EW>::kStages;
-  constexpr int kOutStageBytes = Cfg<EW>::kOutStageBytes;
+               const __grid_constant__ CUtensorMap tmOut, const Args args,
+               const __grid_constant__ CUtensorMap tmAct) {
+  static_assert(!SWIGLU || (EW == 8 && !A_MN && !B_MN && sizeof(OutT) == 2), "SWIGLU: forward bf16 shape only");
+  constexpr int kStages = Cfg<EW, SWIGLU>::kStages;
+  constexpr int kOutStageBytes = Cfg<EW, SWIGLU>::kOutStageBytes;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* sA = smem;
@@ -157,7 +169,7 @@ gemm2sm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   const int cluster_id = blockIdx.x >> 1, n_clusters = gridDim.x >> 1;
 
   const int tiles_m = (args.M + 2 * BM - 1) / (2 * BM);
-  const int tiles_n = (args.N + BN - 1) / BN;
+  const int tiles_n = SWIGLU ? args.F / BNH : (args.N + BN - 1) / BN;
   const int tiles_mn = tiles_m * tiles_n;
   const int num_work = tiles_mn * args.splits;
   const int kb_total = (args.K + BK - 1) / BK;
@@ -166,6 +178,7 @@ gemm2sm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     prefetch_tmap(&tmA);
     prefetch_tmap(&tmB);
     prefetch_tmap(&tmOut);
+    if constexpr (SWIGLU) prefetch_tmap(&tmAct);
     for (int i = 0; i < kStages; ++i) {
       mbar_init(&full_bar[i], 1);
       mbar_init(&empty_bar[i], 1);
@@ -193,7 +206,8 @@ gemm2sm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         const int split = w / tiles_mn;
         const int t = w - split * tiles_mn;
         const int m0 = (t / tiles_n) * (2 * BM) + cta * BM;   // this CTA's 128 rows of the 256-row tile
-        const int n0 = (t % tiles_n) * BN + cta * BNH;        // this CTA's half of the B tile
+        // this CTA's half of the B tile (SWIGLU: the gate rows of hidden units [128 j, +128) / their up rows)
+        const int n0 = SWIGLU ? (t % tiles_n) * BNH + static_cast<int>(cta) * args.F : (t % tiles_n) * BN + cta * BNH;
         const int kb0 = split * args.kb_per_split;
         const int kb1 = min(kb_total, kb0 + args.kb_per_split);
         for (int kb = kb0; kb < kb1; ++kb) {
@@ -268,6 +282,89 @@ gemm2sm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     // staging 32 rows x 128 B per warp and letting the TMA unit write them gives full-line, coalesced writes, clips the
     // M / N edges for free, and takes the store instructions off the epilogue's critical path.
     const int q = warp & 3;   // the hardware ties a warp to TMEM lanes [32 * (warp % 4), +32)
+    if constexpr (SWIGLU) {
+      // warps 2-5: hidden-unit chunks 0, 1 of the tile (gate columns [0, 64) + up columns [128, 192));
+      // warps 6-9: chunks 2, 3.  Three slabs per warp: gate, up, act (32 rows x 64 bf16 columns each).
+      const int half = (warp - 2) >> 2;
+      uint8_t* slab_g = sOut + (warp - 2) * 3 * 4096;
+      uint8_t* slab_u = slab_g + 4096;
+      uint8_t* slab_a = slab_u + 4096;
+      int as = 0;
+      uint32_t aphase = 0;
+      for (int w = cluster_id; w < num_work; w += n_clusters) {
+        const int t = w;   // splits == 1
+        const int m0 = (t / tiles_n) * (2 * BM) + cta * BM;
+        const int j0 = (t % tiles_n) * BNH;   // first hidden unit of the tile
+        if (lane == 0) tma_store_wait_read<0>();   // the three slabs of the previous tile have been read out
+        __syncwarp();
+        mbar_wait(&tmem_full[as], aphase);
+        tc_fence_after();
+        const uint32_t t_addr = tmem_base + as * BN + (static_cast<uint32_t>(q * 32) << 16);
+#pragma unroll 1
+        for (int cc = 0; cc < 2; ++cc) {
+          const int c = half * 2 + cc;   // chunk of 32 hidden units inside the tile
+          uint32_t rg[32], ru[32];
+          tmem_ld32(t_addr + c * 32, rg);
+          tmem_ld32(t_addr + BNH + c * 32, ru);
+          float4 bg[8], bu[8];
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            bg[i] = args.bias ? __ldg(reinterpret_cast<const float4*>(args.bias + j0 + c * 32) + i)
+                              : make_float4(0.f, 0.f, 0.f, 0.f);
+            bu[i] = args.bias ? __ldg(reinterpret_cast<const float4*>(args.bias + args.F + j0 + c * 32) + i)
+                              : make_float4(0.f, 0.f, 0.f, 0.f);
+          }
+          tmem_ld_wait();
+          uint8_t* row_g = slab_g + lane * 128;
+          uint8_t* row_u = slab_u + lane * 128;
+          uint8_t* row_a = slab_a + lane * 128;
+#pragma unroll
+          for (int i = 0; i < 4; ++i) {   // 8 hidden units at a time -> one 16-byte unit of each slab row
+            const float bgv[8] = {bg[2 * i].x, bg[2 * i].y, bg[2 * i].z, bg[2 * i].w,
+                                  bg[2 * i + 1].x, bg[2 * i + 1].y, bg[2 * i + 1].z, bg[2 * i + 1].w};
+            const float buv[8] = {bu[2 * i].x, bu[2 * i].y, bu[2 * i].z, bu[2 * i].w,
+                                  bu[2 * i + 1].x, bu[2 * i + 1].y, bu[2 * i + 1].z, bu[2 * i + 1].w};
+            uint32_t pg[4], pu[4], pa[4];
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+              const float g0 = __uint_as_float(rg[8 * i + 2 * k]) + bgv[2 * k];
+              const float g1 = __uint_as_float(rg[8 * i + 2 * k + 1]) + bgv[2 * k + 1];
+              const float u0 = __uint_as_float(ru[8 * i + 2 * k]) + buv[2 * k];
+              const float u1 = __uint_as_float(ru[8 * i + 2 * k + 1]) + buv[2 * k + 1];
+              pg[k] = pack_bf16(g0, g1);
+              pu[k] = pack_bf16(u0, u1);
+              // the activation is computed from the ROUNDED gate / up, i.e. from exactly what the backward will read
+              const float2 gr = unpack_bf16(pg[k]), ur = unpack_bf16(pu[k]);
+              float t0, t1;
+              asm("tanh.approx.f32 %0, %1;" : "=f"(t0) : "f"(0.5f * gr.x));
+              asm("tanh.approx.f32 %0, %1;" : "=f"(t1) : "f"(0.5f * gr.y));
+              pa[k] = pack_bf16(gr.x * fmaf(0.5f, t0, 0.5f) * ur.x, gr.y * fmaf(0.5f, t1, 0.5f) * ur.y);
+            }
+            const int idx = ((cc * 4 + i) ^ (lane & 7)) << 4;   // 128B swizzle of the slab row
+            *reinterpret_cast<uint4*>(row_g + idx) = make_uint4(pg[0], pg[1], pg[2], pg[3]);
+            *reinterpret_cast<uint4*>(row_u + idx) = make_uint4(pu[0], pu[1], pu[2], pu[3]);
+            *reinterpret_cast<uint4*>(row_a + idx) = make_uint4(pa[0], pa[1], pa[2], pa[3]);
+          }
+        }
+        tc_fence_before();
+        fence_proxy_async_smem();
+        __syncwarp();
+        if (lane == 0) {
+          mbar_arrive_leader(&tmem_empty[as]);
+          const int col = j0 + half * 64, row = m0 + q * 32;
+          tma_store_3d(&tmOut, slab_g, col, row, 0);
+          tma_store_3d(&tmOut, slab_u, args.F + col, row, 0);
+          tma_store_3d(&tmAct, slab_a, col, row, 0);
+          tma_store_commit();
+        }
+        __syncwarp();
+        if (++as == 2) {
+          as = 0;
+          aphase ^= 1;
+        }
+      }
+      if (lane == 0) tma_store_wait<0>();
+    } else {
     // EW = 8: warps 2-5 take columns [0, 128) of the tile, warps 6-9 take [128, 256)
     const int c_begin = (EW == 8) ? ((warp - 2) >> 2) * (BN / 64) : 0;
     const int c_end = (EW == 8) ? c_begin + BN / 64 : BN / 32;
@@ -402,6 +499,7 @@ gemm2sm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       }
     }
     if (lane == 0) tma_store_wait<0>();  // all output tiles have landed before the CTA exits
+    }
   }
 
   tc_fence_before();
@@ -464,11 +562,11 @@ static int launch(const CUtensorMap& tmA, const CUtensorMap& tmB, const Args& ar
   if (epi8) {
     auto kfn = gemm2sm_kernel<A_MN, B_MN, OutT, 8>;
     DPFS_ENSURE_DYN_SMEM(kfn, Cfg<8>::kSmem);
-    kfn<<<(DPFS_COUNT(), 2 * clusters), Cfg<8>::kThreads, Cfg<8>::kSmem, stream>>>(tmA, tmB, tmOut, args);
+    kfn<<<(DPFS_COUNT(), 2 * clusters), Cfg<8>::kThreads, Cfg<8>::kSmem, stream>>>(tmA, tmB, tmOut, args, tmOut);
   } else {
     auto kfn = gemm2sm_kernel<A_MN, B_MN, OutT, 4>;
     DPFS_ENSURE_DYN_SMEM(kfn, Cfg<4>::kSmem);
-    kfn<<<(DPFS_COUNT(), 2 * clusters), Cfg<4>::kThreads, Cfg<4>::kSmem, stream>>>(tmA, tmB, tmOut, args);
+    kfn<<<(DPFS_COUNT(), 2 * clusters), Cfg<4>::kThreads, Cfg<4>::kSmem, stream>>>(tmA, tmB, tmOut, args, tmOut);
   }
   return static_cast<int>(cudaGetLastError());
 }
@@ -581,4 +679,43 @@ extern "C" int dpfs_gemm2sm_bf16(const void* A, long long lda, int a_mn_major, c
     rc = static_cast<int>(cudaGetLastError());
   }
   return rc;
+}
+
+// Fused gate|up projection + SwiGLU (forward): gu[M][2F] = x W^T + b (bf16), act[M][F] = silu(gu[:, :F]) * gu[:, F:].
+// W is the concatenated [2F][ldb] weight (gate rows, then up rows), K-major; F % 128 == 0.
+extern "C" int dpfs_gemm2sm_swiglu_bf16(const void* A, long long lda, const void* B, long long ldb, void* gu, void* act,
+                                        const float* bias, int M, int F, int K, cudaStream_t stream) {
+  using namespace dpfs::sm2;
+  if (M <= 0 || F <= 0 || K <= 0) return 0;
+  if (F % BNH != 0 || (lda % 8) != 0 || (ldb % 8) != 0) return -10;
+  CUtensorMap tmA, tmB, tmOut, tmAct;
+  int rc = make_tmap_bf16_2d(&tmA, A, K, M, lda, 64, BM);
+  if (rc) return rc;
+  rc = make_tmap_bf16_2d(&tmB, B, K, 2 * F, ldb, 64, BNH);
+  if (rc) return rc;
+  rc = make_out_tmap(&tmOut, gu, false, M, 2 * F, 2LL * F, 1, 0);
+  if (rc) return rc;
+  rc = make_out_tmap(&tmAct, act, false, M, F, F, 1, 0);
+  if (rc) return rc;
+  Args args;
+  args.M = M;
+  args.N = 2 * F;
+  args.K = K;
+  args.splits = 1;
+  args.kb_per_split = (K + BK - 1) / BK;
+  args.out = gu;
+  args.ldo = 2LL * F;
+  args.split_stride = 0;
+  args.bias = bias;
+  args.residual = nullptr;
+  args.ldr = 0;
+  args.F = F;
+  const int work = ((M + 2 * BM - 1) / (2 * BM)) * (F / BNH);
+  int clusters = num_sms() / 2;
+  if (work < clusters) clusters = work;
+  auto kfn = gemm2sm_kernel<false, false, __nv_bfloat16, 8, true>;
+  DPFS_ENSURE_DYN_SMEM(kfn, (Cfg<8, true>::kSmem));
+  kfn<<<(DPFS_COUNT(), 2 * clusters), Cfg<8, true>::kThreads, Cfg<8, true>::kSmem, stream>>>(tmA, tmB, tmOut, args,
+                                                                                              tmAct);
+  return static_cast<int>(cudaGetLastError());
 }

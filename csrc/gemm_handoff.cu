@@ -23,6 +23,7 @@
 #include "sp_rowops.cuh"
 
 #include <cudaTypedefs.h>
+#include <stdlib.h>
 
 namespace dpfs {
 
@@ -65,6 +66,7 @@ struct Args {
   const float* dres_l;         // fp32 [rpr][N] (nullable)
   float* dx_l;                 // fp32 [rpr][N] (nullable)
   float* scratch;              // fp32 [gridDim.x][2 * N] partial sums
+  int comm_ctas;               // CTAs whose comm warps work (the others only run the GEMM), see launch()
 };
 
 // same owner-interleaved tile order as the fused reduce-scatter (gemm_tcgen05.cu): the j-th row-block of owner 0, of
@@ -275,7 +277,8 @@ gemm_handoff_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     sp_load_cols<NC>(OP == 0 ? args.bias : nullptr, nchunk, lane, c1);
     sp_load_cols<NC>(nullptr, nchunk, lane, c2);
     const int n_items = (rpr + IR - 1) / IR;
-    for (int it = blockIdx.x; it < n_items; it += gridDim.x) {
+    const int comm_ctas = min(args.comm_ctas, static_cast<int>(gridDim.x));
+    for (int it = blockIdx.x < comm_ctas ? blockIdx.x : n_items; it < n_items; it += comm_ctas) {
       const int r_lo = it * IR, r_hi = min(rpr, r_lo + IR);                 // local rows of this item
       const int mb_lo = static_cast<int>((g_row0 + r_lo) / BM), mb_hi = static_cast<int>((g_row0 + r_hi - 1) / BM);
       const int per_blk = tiles_n * n;
@@ -365,8 +368,25 @@ __global__ void __launch_bounds__(256) reduce_partials2_kernel(const float* __re
   }
 }
 
+// How many CTAs lend their comm warps to the pull / row op / push.  The NVLS data phase runs at the same rate with 16
+// blocks of pulls in flight as with 148 (profiles/handoff_microbench_tp8_r2.md) and every extra puller only adds
+// contention, so the rows are dealt to the first `comm_ctas` CTAs: about eight 16-row items each, at least 16 CTAs
+// (DPFS_GH_COMM_CTAS overrides).
+static int comm_ctas_for(int rpr, int rows_per_item) {
+  static const int env = [] {
+    const char* e = getenv("DPFS_GH_COMM_CTAS");
+    return e ? atoi(e) : 0;
+  }();
+  if (env > 0) return env;
+  const int items = (rpr + rows_per_item - 1) / rows_per_item;
+  int c = (items + 7) / 8;
+  return c < 16 ? 16 : c;
+}
+
 template <bool B_MN, int OP, int NC>
-static int launch(const CUtensorMap& tmA, const CUtensorMap& tmB, const Args& args, int grid, cudaStream_t stream) {
+static int launch(const CUtensorMap& tmA, const CUtensorMap& tmB, const Args& args_in, int grid, cudaStream_t stream) {
+  Args args = args_in;
+  args.comm_ctas = comm_ctas_for(args.rpr, kCommWarps * (NC <= 2 ? 2 : 1));
   auto kfn = gemm_handoff_kernel<B_MN, OP, NC>;
   DPFS_ENSURE_DYN_SMEM(kfn, kSmem);
   kfn<<<(DPFS_COUNT(), grid), kThreads, kSmem, stream>>>(tmA, tmB, args);

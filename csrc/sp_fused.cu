@@ -183,12 +183,17 @@ static void sp_env_init() {   // DPFS_SP_GRID_CAP / DPFS_SP_BAR_MODE, read once 
   (void)done;
 }
 
-// One row-slot per warp: enough blocks that (for the model's shapes) every row of the rank is in flight at once, never
-// more than can be resident together (`resident` = SMs x blocks per SM from the occupancy calculator: the grid-wide
-// barrier spins until every block has arrived).
+// Grid: about eight passes of rows per block.  Measured on 8 x B200 (profiles/handoff_microbench_tp8_r2.md): with
+// [32000, 512] the kernel takes 118 us with one pass on 125 blocks, 101 us on 37 blocks and 95 us on 16 -- the data
+// phase is bound by the NVLS pull / push rate whatever the grid, and every extra block adds to the grid-wide barrier
+// (and takes an SM away from the weight-gradient GEMMs that run beside it).  Never more blocks than can be resident
+// together (`resident` = SMs x blocks per SM from the occupancy calculator): the grid barrier spins until all arrived.
 static int sp_grid(int rpr, int R, int T, int resident) {
   const int rows_per_block = (T / 32) * R;
-  int b = (rpr + rows_per_block - 1) / rows_per_block;
+  int b = (rpr + 8 * rows_per_block - 1) / (8 * rows_per_block);
+  if (b < 16) b = 16;
+  const int one_pass = (rpr + rows_per_block - 1) / rows_per_block;
+  if (b > one_pass) b = one_pass;
   int cap = resident < kMaxBlocks ? resident : kMaxBlocks;
   if (g_sp_grid_cap > 0 && g_sp_grid_cap < cap) cap = g_sp_grid_cap;
   if (b > cap) b = cap;

@@ -30,7 +30,7 @@ import torch
 
 from ..ops import fused
 from ..ops.attention import attn_bwd, attn_fwd
-from ..ops.gemm import gemm_nt
+from ..ops.gemm import gemm_nt, gemm_swiglu
 from ..parallel import comm_ops
 from ..parallel import process_manager as pm
 from ..utils.logging import nvtx_range
@@ -257,8 +257,7 @@ class FusedLayerFn(torch.autograd.Function):
         fused.rope_inplace(qkv, pos, rt.cos_half, rt.sin_half, 2, m.Dl, m.Hl, m.hd, inverse=False)
         attn, lse = attn_fwd(qkv, m.B, m.T, m.Hl, m.hd, m.scale)
         x2, h2, rstd2 = _rowpar_residual(attn, pack.wo, pack.bo, x, pack.s2, rt.eps)
-        gu = gemm_nt(h2, pack.wgu, bias=pack.bgu, out_dtype=BF16)
-        act = fused.swiglu_fwd(gu)
+        gu, act = gemm_swiglu(h2, pack.wgu, pack.bgu)      # SwiGLU in the GEMM epilogue when the shape allows
         x3, _, _ = _rowpar_residual(act, pack.wd, pack.bd, x2)
         ctx.save_for_backward(x, pos, h1, rstd1, qkv, attn, lse, x2, h2, rstd2, gu, act)
         ctx.pack, ctx.meta, ctx.rt = pack, meta, rt
@@ -648,8 +647,7 @@ class FusedLayerSPFn(torch.autograd.Function):
         else:
             x2_l, h2_l, rstd2 = fused.add_rmsnorm_fwd(x_l, y_l, pack.bo, pack.s2, rt.eps)
             h2 = _all_gather_rows(h2_l, keep=True)
-        gu = gemm_nt(h2, pack.wgu, bias=pack.bgu, out_dtype=BF16)
-        act = fused.swiglu_fwd(gu)
+        gu, act = gemm_swiglu(h2, pack.wgu, pack.bgu)      # SwiGLU in the GEMM epilogue when the shape allows
         y_l = _rowpar_rs(act, pack.wd)
         x3_l, _, _ = fused.add_rmsnorm_fwd(x2_l, y_l, pack.bd, None, rt.eps, want_norm=False)
         ctx.save_for_backward(x_l, pos, h1, rstd1, qkv, attn, lse, x2_l, h2, rstd2, gu, act)
@@ -769,9 +767,13 @@ class FusedHeadLossSPFn(torch.autograd.Function):
 # GEMM + hand-off as ONE kernel (csrc/gemm_handoff.cu: tile flags instead of the opening barrier, the reduction of the
 # first row-blocks under the GEMM of the later ones) or as 2-SM GEMM + stand-alone hand-off kernel.
 def _fused_gemm_handoff() -> bool:
-    # default on: 14.19 vs 14.56 ms / step at TP=2 (profiles/bench_tp2_r2.md); DPFS_SP_FUSED_GEMM=0 selects the
-    # 2-SM GEMM + stand-alone hand-off kernel
-    return os.environ.get("DPFS_SP_FUSED_GEMM", "1") == "1"
+    """GEMM + hand-off as one kernel?  DPFS_SP_FUSED_GEMM=0/1 forces the choice; by default the measured winner per TP
+    size: one kernel up to TP=4 (14.19 vs 14.56 ms / step at TP=2), 2-SM GEMM + stand-alone hand-off kernel at TP=8
+    (9.06 vs 10.43 ms, profiles/bench_tp8_r2.md)."""
+    env = os.environ.get("DPFS_SP_FUSED_GEMM")
+    if env is not None:
+        return env == "1"
+    return pm.pgm.tp_size <= 4
 
 
 def _handoff_fwd(a, w, x_l, bias, scale, eps, zone):
@@ -838,8 +840,7 @@ class HandoffLayerFn(torch.autograd.Function):
         fused.rope_inplace(qkv, pos, rt.cos_half, rt.sin_half, 2, m.Dl, m.Hl, m.hd, inverse=False)
         attn, lse = attn_fwd(qkv, m.B, m.T, m.Hl, m.hd, m.scale)
         x2_l, h2, rstd2 = _handoff_fwd(attn, pack.wo, x_l, pack.bo, pack.s2, rt.eps, rt._zones[2 * li + 1])
-        gu = gemm_nt(h2, pack.wgu, bias=pack.bgu, out_dtype=BF16)
-        act = fused.swiglu_fwd(gu)
+        gu, act = gemm_swiglu(h2, pack.wgu, pack.bgu)      # SwiGLU in the GEMM epilogue when the shape allows
         nxt = rt.packs[li + 1].s1 if li + 1 < len(rt.packs) else rt.sN      # the norm that opens the next block
         x3_l, hn, rstdn = _handoff_fwd(act, pack.wd, x2_l, pack.bd, nxt, rt.eps, rt._zones[2 * li + 2])
         rt.put_handoff(x3_l, hn, rstdn)

@@ -102,3 +102,31 @@ def gemm_nt(a: torch.Tensor, b: torch.Tensor, *, a_mn_major: bool = False, b_mn_
         residual.stride(0) if residual is not None else 0, M, N, K, splits, _lib.ptr(ws), bn, _lib.stream())
     _lib.check(rc, "dpfs_gemm_bf16")
     return out
+
+
+_FUSE_SWIGLU = os.environ.get("DPFS_GEMM_SWIGLU", "1") == "1"
+
+
+def gemm_swiglu(x: torch.Tensor, w_gate_up: torch.Tensor, bias: Optional[torch.Tensor]):
+    """gu = x @ W^T + b (bf16 [M, 2F], gate columns then up columns) and act = silu(gate) * up (bf16 [M, F]).
+
+    One kernel when the 2-SM GEMM's SwiGLU epilogue applies (F % 128 == 0, M >= 256: csrc/gemm2sm_tcgen05.cu); the
+    activation is computed in the epilogue registers from the rounded gate / up values, so the stand-alone SwiGLU
+    kernel's re-read of the [M, 2F] tensor disappears.  Otherwise GEMM + swiglu_fwd.  ref: models/model.py:95."""
+    assert x.dim() == 2 and x.dtype == torch.bfloat16 and w_gate_up.dtype == torch.bfloat16
+    M, K = x.shape
+    F2 = w_gate_up.shape[0]
+    F = F2 // 2
+    if (_FUSE_SWIGLU and _USE_2SM and M >= 256 and F % 128 == 0 and x.stride(1) == 1 and w_gate_up.stride(1) == 1
+            and x.stride(0) % 8 == 0 and w_gate_up.stride(0) % 8 == 0 and w_gate_up.shape[1] == K):
+        gu = torch.empty((M, F2), dtype=torch.bfloat16, device=x.device)
+        act = torch.empty((M, F), dtype=torch.bfloat16, device=x.device)
+        if bias is not None:
+            assert bias.dtype == torch.float32 and bias.numel() == F2 and bias.is_contiguous()
+        rc = _lib.lib().dpfs_gemm2sm_swiglu_bf16(x.data_ptr(), x.stride(0), w_gate_up.data_ptr(), w_gate_up.stride(0),
+                                                 gu.data_ptr(), act.data_ptr(), _lib.ptr(bias), M, F, K, _lib.stream())
+        _lib.check(rc, "dpfs_gemm2sm_swiglu_bf16")
+        return gu, act
+    from . import fused
+    gu = gemm_nt(x, w_gate_up, bias=bias, out_dtype=torch.bfloat16)
+    return gu, fused.swiglu_fwd(gu)

@@ -37,6 +37,13 @@ int dpfs_gemm2sm_bf16(const void* A, long long lda, int a_mn_major, const void* 
                       void* out, long long ldo, int out_fp32, const float* bias, const float* residual,
                       long long ldr, int M, int N, int K, int splits, float* workspace, cudaStream_t stream);
 
+/* Fused gate|up projection + SwiGLU, forward (2-SM kernel with the activation in the epilogue): gu[M][2F] = A W^T + b
+ * (bf16; gate columns [0,F), up columns [F,2F): the backward reads it) and act[M][F] = silu(gate) * up, in ONE pass.
+ * W: bf16 [2F][ldb], gate rows then up rows (the two weights back to back), K-major; bias fp32 [2F] (nullable).
+ * F % 128 == 0.  ref: FFN.forward, models/model.py:95 (two cuBLAS GEMMs + two ATen kernels in the reference). */
+int dpfs_gemm2sm_swiglu_bf16(const void* A, long long lda, const void* B, long long ldb, void* gu, void* act,
+                             const float* bias, int M, int F, int K, cudaStream_t stream);
+
 /* Fused GEMM -> all-reduce over NVLink (one kernel): every rank computes its partial out = A_r B_r^T (bf16) into
  * its symmetric buffer `out` ([M][N], row stride N) and the ranks sum the tiles through the NVSwitch with
  * multimem.ld_reduce / multimem.st on `mc_out` (the multicast alias of `out`).  flag_ptrs: HOST array of the n ranks'

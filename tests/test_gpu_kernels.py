@@ -47,6 +47,25 @@ def test_gemm_tcgen05(a_mn, b_mn, shape):
     assert (out - (ref + bias)).abs().max().item() < 2e-3 * scale
 
 
+@pytest.mark.parametrize("shape", [(32000, 2048, 512), (1000, 256, 512), (520, 128, 192), (4096, 1024, 1024)])
+def test_gemm_swiglu_epilogue(shape):
+    """gate|up projection with SwiGLU in the 2-SM GEMM's epilogue vs fp32 PyTorch: gu = x W^T + b, act = silu(g) * u
+    computed from the bf16-rounded g, u (what the backward reads)."""
+    from distributed_pytorch_from_scratch_b200.ops.gemm import gemm_swiglu
+    M, F, K = shape
+    torch.manual_seed(0)
+    x, w = _bf(torch.randn(M, K, device=DEV)), _bf(torch.randn(2 * F, K, device=DEV) * K ** -0.5)
+    bias = torch.randn(2 * F, device=DEV)
+    gu, act = gemm_swiglu(x, w, bias)
+    ref = x.float() @ w.float().t() + bias
+    sc = ref.abs().max().item()
+    assert gu.shape == (M, 2 * F) and act.shape == (M, F)
+    assert (gu.float() - ref).abs().max().item() < 1e-2 * sc
+    g, u = gu.float()[:, :F], gu.float()[:, F:]
+    act_ref = torch.nn.functional.silu(g) * u
+    assert (act.float() - act_ref).abs().max().item() < 1e-2 * max(1.0, act_ref.abs().max().item())
+
+
 @pytest.mark.parametrize("B,T,H,HD", [(1, 128, 1, 64), (2, 200, 2, 64), (2, 1000, 2, 64), (2, 333, 2, 128)])
 def test_flash_attention_fwd_bwd(B, T, H, HD):
     from distributed_pytorch_from_scratch_b200.ops import attention as A

@@ -219,13 +219,16 @@ def _gemm_handoff_worker(rank, world):
     for (Ml, N, K) in [(500, 512, 256), (256, 1024, 128), (130, 256, 64), (4000, 512, 64)]:
         M = Ml * world
         zones = symm.alloc_zones(2, M * N * 2)
-        a = (torch.randn(M, K, device="cuda") * 0.5).to(torch.bfloat16)
-        w = (torch.randn(N, K, device="cuda") * 0.5).to(torch.bfloat16)          # forward: [N, K], K-major
+        amp = float(K * world) ** -0.25         # the reduced product has unit scale at every TP size
+        a = (torch.randn(M, K, device="cuda") * amp).to(torch.bfloat16)
+        w = (torch.randn(N, K, device="cuda") * amp).to(torch.bfloat16)          # forward: [N, K], K-major
         wt = w.t().contiguous()                                                    # backward: [K, N], MN-major
         assert fused.can_gemm_handoff(symm, a, w) and fused.can_gemm_handoff(symm, a, wt, True)
-        total = a.float() @ w.float().t()
+        # oracle with the kernel's rounding points: each rank's partial product is stored as bf16, the switch sums
+        # the n partials in fp32 and returns a bf16 row
+        total = (a.float() @ w.float().t()).to(torch.bfloat16).float()
         dist.all_reduce(total)
-        y_l = total[rank * Ml:(rank + 1) * Ml]
+        y_l = total[rank * Ml:(rank + 1) * Ml].to(torch.bfloat16).float()
         sc_ = max(1.0, y_l.abs().max().item())
         x_l = torch.randn(Ml, N, device="cuda")
         bias, scale = torch.randn(N, device="cuda"), torch.rand(N, device="cuda") + 0.5
@@ -234,8 +237,8 @@ def _gemm_handoff_worker(rank, world):
             xo_ref = x_l + y_l + bias
             rstd_ref = torch.rsqrt(xo_ref.pow(2).mean(-1) + 1e-5)
             h_ref = gather((xo_ref * rstd_ref[:, None] * scale).to(torch.bfloat16))
-            assert (xo - xo_ref).abs().max().item() < 0.03 * sc_, (Ml, N, K, rnd, (xo - xo_ref).abs().max().item())
-            assert (h.float() - h_ref.float()).abs().max().item() < 0.05, (Ml, N, K, rnd)
+            assert (xo - xo_ref).abs().max().item() < 0.02 * sc_, (Ml, N, K, rnd, (xo - xo_ref).abs().max().item())
+            assert (h.float() - h_ref.float()).abs().max().item() < 0.08, (Ml, N, K, rnd)
             assert torch.equal(h, gather(h[rank * Ml:(rank + 1) * Ml])), "ranks disagree on the gathered rows"
             dres = torch.randn(Ml, N, device="cuda")
             ds, db = torch.empty(N, device="cuda"), torch.empty(N, device="cuda")

@@ -103,8 +103,8 @@ def main():
     def dur(e):
         d = getattr(e, "device_time", None)
         return e.cuda_time if d is None else d
-    hand = [(short(e.name)[:24], dur(e)) for e in last if "_ag_kernel" in e.name]
-    other = sum(dur(e) for e in last if "_ag_kernel" not in e.name)
+    hand = [(short(e.name)[:24], dur(e)) for e in last if "_ag_kernel" in e.name or "handoff_kernel" in e.name]
+    other = sum(dur(e) for e in last if "_ag_kernel" not in e.name and "handoff_kernel" not in e.name)
     gathered = [None] * world
     torch.distributed.all_gather_object(gathered, {"rank": rank, "other_us": other, "hand": hand})
     total = sum(v[0] for v in tot.values())
