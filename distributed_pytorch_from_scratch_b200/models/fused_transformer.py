@@ -768,12 +768,13 @@ class FusedHeadLossSPFn(torch.autograd.Function):
 # first row-blocks under the GEMM of the later ones) or as 2-SM GEMM + stand-alone hand-off kernel.
 def _fused_gemm_handoff() -> bool:
     """GEMM + hand-off as one kernel?  DPFS_SP_FUSED_GEMM=0/1 forces the choice; by default the measured winner per TP
-    size: one kernel up to TP=4 (14.19 vs 14.56 ms / step at TP=2), 2-SM GEMM + stand-alone hand-off kernel at TP=8
-    (9.06 vs 10.43 ms, profiles/bench_tp8_r2.md)."""
+    size (profiles/bench_tp_r2.md): one kernel at TP=2 (13.83 vs 14.12 ms / step), 2-SM GEMM + stand-alone hand-off kernel at
+    TP=4 (10.53 vs 12.62 ms) and TP=8 (9.06 vs 10.43 ms) -- the fused kernel's GEMM is the 1-SM one and shares its SMs with
+    the comm warps, which costs more than the overlap returns once the per-rank GEMMs are short."""
     env = os.environ.get("DPFS_SP_FUSED_GEMM")
     if env is not None:
         return env == "1"
-    return pm.pgm.tp_size <= 4
+    return pm.pgm.tp_size <= 2
 
 
 def _handoff_fwd(a, w, x_l, bias, scale, eps, zone):

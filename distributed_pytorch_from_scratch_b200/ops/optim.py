@@ -122,12 +122,20 @@ class FusedAdam(torch.optim.Optimizer):
     def fused_state(self):
         if self.arena is None:
             return {"step": self.step_count, "state": self.state_dict()}
-        return {"step": self.step_count, "m": self._m.clone(), "v": self._v.clone()}
+        # "layout": the arena's (offset, numel) list -- m / v are flat arenas, only meaningful for the same layout
+        return {"step": self.step_count, "m": self._m.clone(), "v": self._v.clone(), "layout": self._layout_sig()}
+
+    def _layout_sig(self):
+        return [(off, p.numel()) for p, off in self.arena.entries] if self.arena is not None else None
 
     def load_fused_state(self, st):
         self.step_count = st["step"]
         if self.arena is None:
             self.load_state_dict(st["state"])
         else:
+            lay = st.get("layout")
+            if lay is not None and [tuple(x) for x in lay] != self._layout_sig():
+                raise RuntimeError("resume file was written with a different parameter-arena layout (another version "
+                                   "of the framework or another model): its Adam moments cannot be applied")
             self._m.copy_(st["m"])
             self._v.copy_(st["v"])

@@ -69,7 +69,9 @@ def save_resume_state(save_dir: str, rank: int, step: int, optimizer, scheduler,
           "rng_cpu": torch.get_rng_state(),
           "rng_cuda": torch.cuda.get_rng_state() if torch.cuda.is_available() else None, "extra": extra}
     path = os.path.join(save_dir, f"resume-tprank-{rank}.pt")
-    torch.save(st, path)
+    tmp = path + ".tmp"
+    torch.save(st, tmp)
+    os.replace(tmp, path)       # atomic: a crash mid-write leaves the previous resume file intact
     return path
 
 

@@ -154,13 +154,25 @@ def train(rank: int, args: Namespace):
 
     start_step, accum_loss = 0, 0.
     if args.resume:
+        # Weights come from the tprank-{r}_iter-{n}_... checkpoint, optimizer / scheduler / step from the resume file
+        # written right after it.  They must belong to the SAME step (a crash between the two writes, or a shard
+        # copied next to an old resume file, would pair step-N weights with step-M Adam moments): pick the checkpoint
+        # whose iteration equals the resume file's step, refuse otherwise.  The data order restarts at the beginning
+        # of an epoch on resume (the loader position is not part of the state).
         ckpts = list_checkpoints(args.save_dir, pm.pgm.tp_rank)
         if ckpts:
-            load_checkpoint(model, ckpts[-1])
+            import re as _re
             st = load_resume_state(args.save_dir, pm.pgm.tp_rank, optimizer, scheduler)
+            chosen = ckpts[-1]
             if st is not None:
+                by_iter = {int(_re.search(r"_iter-(\d+)_", os.path.basename(c)).group(1)): c for c in ckpts}
+                if st["step"] not in by_iter:
+                    raise RuntimeError(f"resume-tprank-{pm.pgm.tp_rank}.pt is from step {st['step']} but the checkpoints "
+                                       f"in {args.save_dir} are from steps {sorted(by_iter)}: refusing to mix them")
+                chosen = by_iter[st["step"]]
                 start_step, accum_loss = st["step"], st["accum_loss"]
-            print(f"[TP rank {rank}]: Resumed from {ckpts[-1]} at step {start_step}")
+            load_checkpoint(model, chosen)
+            print(f"[TP rank {rank}]: Resumed from {chosen} at step {start_step}")
 
     if fused_model:
         step_fn = TrainStep(model, optimizer, scheduler, ignore_index=IGNORE_INDEX, use_graph=args.cuda_graph)
