@@ -785,6 +785,14 @@ static inline int norm_grid(int M) {
 
 }  // namespace dpfs
 
+namespace dpfs {
+// out[c] = sum over nrows of partial[r][c] (fixed order); for other translation units that produce partial-sum rows
+int reduce_partials_rows(const float* partial, float* out, int nrows, int D, cudaStream_t stream) {
+  reduce_partials_kernel<<<(DPFS_COUNT(), (D + 31) / 32), kReduceGroups * 32, 0, stream>>>(partial, out, nrows, D, 0);
+  return static_cast<int>(cudaGetLastError());
+}
+}  // namespace dpfs
+
 using namespace dpfs;
 
 #define DISPATCH_NV(D, ...)                   \

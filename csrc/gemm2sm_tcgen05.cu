@@ -40,11 +40,13 @@ constexpr int kOutBufs = 2;
 // compiler caps that shape at 168 registers: 16384 / 3 per warp.)
 // SWIGLU flavour (gate|up projection with the activation in the epilogue, see gemm2sm_kernel): three output slabs per
 // warp (gate, up, act) instead of a ring of two, paid for with one operand stage (K = d is short there anyway).
-template <int EW, bool SWIGLU = false>
+// EPI: 0 plain epilogue, 1 SwiGLU forward (three slabs per warp), 2 SwiGLU backward (four slabs per warp: the gate and
+// up halves of two 64-column groups; three operand stages -- that kernel is bound by its 524 MB of epilogue traffic).
+template <int EW, int EPI = 0>
 struct Cfg {
-  static constexpr int kStages = SWIGLU ? 4 : (EW == 8 ? 5 : 6);
+  static constexpr int kStages = EPI == 1 ? 4 : EPI == 2 ? 3 : (EW == 8 ? 5 : 6);
   static constexpr int kThreads = 64 + EW * 32;
-  static constexpr int kBufs = SWIGLU ? 3 : kOutBufs;
+  static constexpr int kBufs = EPI == 1 ? 3 : EPI == 2 ? 4 : kOutBufs;
   static constexpr int kOutStageBytes = EW * kBufs * 4096;
   static constexpr int kSmem = kStages * kStageBytes + kOutStageBytes + 256 + 1024;
   static_assert(kSmem <= 232448, "exceeds the 227 KB shared-memory limit");
@@ -59,7 +61,9 @@ struct Args {
   const float* bias;
   const float* residual;
   long long ldr;
-  int F;  // SWIGLU flavour: hidden units (N = 2 F: gate rows [0, F), up rows [F, 2F) of B)
+  int F;  // SwiGLU flavours: hidden units (forward: N = 2 F, gate rows [0, F), up rows [F, 2F) of B; backward: N = F)
+  const __nv_bfloat16* gu;  // SwiGLU backward: the saved gate|up activation [M][2F]
+  float* colsum;            // SwiGLU backward: per-(32-row group) column sums of d(gate|up), [ceil(M/256)*8][2F]
 };
 
 __device__ __forceinline__ uint32_t cluster_ctarank() {
@@ -144,14 +148,23 @@ __device__ __forceinline__ void store32<__nv_bfloat16>(__nv_bfloat16* dst, const
 // epilogue thread has both of a hidden unit in registers: it emits gate|up (+ bias, bf16: the backward needs it) AND
 // act = silu(g) * u (through tmAct) in one pass -- the 2 x M x F re-read of the stand-alone SwiGLU kernel disappears.
 // Parameters, checkpoints, wgrad and dgrad are untouched.  ref: models/model.py:95.
-template <bool A_MN, bool B_MN, typename OutT, int EW, bool SWIGLU = false>
-__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(Cfg<EW, SWIGLU>::kThreads, 1)
+//
+// EPI = 2, SwiGLU BACKWARD in the epilogue of the down_proj dgrad (A = dy K-major, B = W_down MN-major, N = F): the
+// accumulator is dact = dy W_down; an epilogue thread (one row) reads the saved gate / up values of its 32 hidden units,
+// turns dact into d(gate) and d(up) in registers and emits both halves of d(gate|up) [M][2F] (bf16, through tmOut) plus
+// the column sums of each 32-row slab (the gate|up bias gradient, finished by a fixed-order reduction).  dact is
+// never written: the stand-alone SwiGLU-backward kernel's 131 MB write + 131 MB read per layer disappear.
+template <bool A_MN, bool B_MN, typename OutT, int EW, int EPI = 0>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(Cfg<EW, EPI>::kThreads, 1)
 gemm2sm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                const __grid_constant__ CUtensorMap tmOut, const Args args,
                const __grid_constant__ CUtensorMap tmAct) {
+  constexpr bool SWIGLU = EPI == 1;
+  constexpr bool SWIGLU_BWD = EPI == 2;
   static_assert(!SWIGLU || (EW == 8 && !A_MN && !B_MN && sizeof(OutT) == 2), "SWIGLU: forward bf16 shape only");
-  constexpr int kStages = Cfg<EW, SWIGLU>::kStages;
-  constexpr int kOutStageBytes = Cfg<EW, SWIGLU>::kOutStageBytes;
+  static_assert(!SWIGLU_BWD || (EW == 8 && !A_MN && B_MN && sizeof(OutT) == 2), "SWIGLU_BWD: dgrad bf16 shape only");
+  constexpr int kStages = Cfg<EW, EPI>::kStages;
+  constexpr int kOutStageBytes = Cfg<EW, EPI>::kOutStageBytes;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* sA = smem;
@@ -178,7 +191,11 @@ gemm2sm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     prefetch_tmap(&tmA);
     prefetch_tmap(&tmB);
     prefetch_tmap(&tmOut);
-    if constexpr (SWIGLU) prefetch_tmap(&tmAct);
+    if constexpr (SWIGLU || SWIGLU_BWD) prefetch_tmap(&tmAct);
+    if constexpr (SWIGLU_BWD) {   // one "gate|up slabs landed" barrier per epilogue warp, behind the pipeline barriers
+      uint64_t* gu_bar = reinterpret_cast<uint64_t*>(reinterpret_cast<uint8_t*>(full_bar) + 128);
+      for (int i = 0; i < EW; ++i) mbar_init(&gu_bar[i], 1);
+    }
     for (int i = 0; i < kStages; ++i) {
       mbar_init(&full_bar[i], 1);
       mbar_init(&empty_bar[i], 1);
@@ -282,7 +299,130 @@ gemm2sm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     // staging 32 rows x 128 B per warp and letting the TMA unit write them gives full-line, coalesced writes, clips the
     // M / N edges for free, and takes the store instructions off the epilogue's critical path.
     const int q = warp & 3;   // the hardware ties a warp to TMEM lanes [32 * (warp % 4), +32)
-    if constexpr (SWIGLU) {
+    if constexpr (SWIGLU_BWD) {
+      // warps 2-5: columns [0, 128) of the tile, warps 6-9: [128, 256) -- two groups of 64 hidden units each.  Four
+      // slabs per warp: (gate, up) x (group 0, group 1), 32 rows x 64 bf16 columns each.
+      const int half = (warp - 2) >> 2;
+      uint8_t* slabs = sOut + (warp - 2) * 4 * 4096;
+      uint64_t* gu_bar = reinterpret_cast<uint64_t*>(reinterpret_cast<uint8_t*>(full_bar) + 128) + (warp - 2);
+      uint32_t gphase = 0;
+      const int F = args.F;
+      int as = 0;
+      uint32_t aphase = 0;
+      for (int w = cluster_id; w < num_work; w += n_clusters) {
+        const int t = w;   // splits == 1
+        const int m0 = (t / tiles_n) * (2 * BM) + cta * BM;
+        const int n0 = (t % tiles_n) * BN;
+        // The saved gate / up values of this warp's 32 rows x 2 x 64 hidden units are fetched by TMA straight into the
+        // four output slabs (same 128B-swizzled layout as the store), under the tile's main loop; each thread then
+        // turns its own slab row into d(gate) / d(up) in place.  Rows past M are zero-filled by the load.
+        if (lane == 0) {
+          tma_store_wait_read<0>();   // the stores of the previous tile have read the slabs out
+          mbar_expect_tx(gu_bar, 4 * 4096);
+#pragma unroll
+          for (int grp = 0; grp < 2; ++grp) {
+            const int c0 = n0 + half * 128 + grp * 64;
+            tma_load_3d(slabs + (2 * grp) * 4096, &tmAct, gu_bar, c0, m0 + q * 32, 0);
+            tma_load_3d(slabs + (2 * grp + 1) * 4096, &tmAct, gu_bar, F + c0, m0 + q * 32, 0);
+          }
+        }
+        __syncwarp();
+        mbar_wait(&tmem_full[as], aphase);
+        tc_fence_after();
+        mbar_wait(gu_bar, gphase);
+        gphase ^= 1;
+        const uint32_t t_addr = tmem_base + as * BN + (static_cast<uint32_t>(q * 32) << 16);
+#pragma unroll 1
+        for (int grp = 0; grp < 2; ++grp) {
+          const int c0 = n0 + half * 128 + grp * 64;   // first hidden unit of this group of 64
+          uint8_t* row_g = slabs + (2 * grp) * 4096 + lane * 128;
+          uint8_t* row_u = row_g + 4096;
+#pragma unroll
+          for (int cc = 0; cc < 2; ++cc) {
+            uint32_t r[32];
+            tmem_ld32(t_addr + half * 128 + grp * 64 + cc * 32, r);
+            uint4 gq[4], uq[4];
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+              const int idx = ((cc * 4 + i) ^ (lane & 7)) << 4;   // 128B swizzle of the slab row
+              gq[i] = *reinterpret_cast<const uint4*>(row_g + idx);
+              uq[i] = *reinterpret_cast<const uint4*>(row_u + idx);
+            }
+            tmem_ld_wait();
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+              const uint32_t gw[4] = {gq[i].x, gq[i].y, gq[i].z, gq[i].w}, uw[4] = {uq[i].x, uq[i].y, uq[i].z, uq[i].w};
+              uint32_t og[4], ou[4];
+#pragma unroll
+              for (int k = 0; k < 4; ++k) {
+                const float2 g = unpack_bf16(gw[k]), u = unpack_bf16(uw[k]);
+                // dact goes through bf16 like the stand-alone path (GEMM output rounded, then the SwiGLU backward)
+                const float2 d = unpack_bf16(pack_bf16(__uint_as_float(r[8 * i + 2 * k]),
+                                                       __uint_as_float(r[8 * i + 2 * k + 1])));
+                float t0, t1;
+                asm("tanh.approx.f32 %0, %1;" : "=f"(t0) : "f"(0.5f * g.x));
+                asm("tanh.approx.f32 %0, %1;" : "=f"(t1) : "f"(0.5f * g.y));
+                const float s0 = fmaf(0.5f, t0, 0.5f), s1 = fmaf(0.5f, t1, 0.5f);
+                og[k] = pack_bf16(d.x * u.x * s0 * (1.f + g.x * (1.f - s0)), d.y * u.y * s1 * (1.f + g.y * (1.f - s1)));
+                ou[k] = pack_bf16(d.x * g.x * s0, d.y * g.y * s1);
+              }
+              const int idx = ((cc * 4 + i) ^ (lane & 7)) << 4;
+              *reinterpret_cast<uint4*>(row_g + idx) = make_uint4(og[0], og[1], og[2], og[3]);
+              *reinterpret_cast<uint4*>(row_u + idx) = make_uint4(ou[0], ou[1], ou[2], ou[3]);
+            }
+          }
+          __syncwarp();
+          // column sums of the two finished slabs (what is stored, bf16-rounded): lane = (8-column unit, 8-row group)
+          {
+            const int unit = lane & 7, rg = lane >> 3;
+            float* dst = args.colsum +
+                         (static_cast<long long>(t / tiles_n) * 8 + cta * 4 + q) * 2 * F + c0 + unit * 8;
+#pragma unroll
+            for (int which = 0; which < 2; ++which) {
+              const uint8_t* slab = slabs + (2 * grp + which) * 4096;
+              float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+              for (int rr = 0; rr < 8; ++rr) {
+                const int srow = rg * 8 + rr;
+                const uint4 v = *reinterpret_cast<const uint4*>(slab + srow * 128 + ((unit ^ (srow & 7)) << 4));
+                const uint32_t vw[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                  const float2 f = unpack_bf16(vw[k]);
+                  acc[2 * k] += f.x;
+                  acc[2 * k + 1] += f.y;
+                }
+              }
+#pragma unroll
+              for (int e = 0; e < 8; ++e) {   // fixed order: row groups 0+1, 2+3, then the pairs
+                acc[e] += __shfl_xor_sync(0xffffffffu, acc[e], 8);
+                acc[e] += __shfl_xor_sync(0xffffffffu, acc[e], 16);
+              }
+              if (rg == 0) {
+                *reinterpret_cast<float4*>(dst + which * F) = make_float4(acc[0], acc[1], acc[2], acc[3]);
+                *reinterpret_cast<float4*>(dst + which * F + 4) = make_float4(acc[4], acc[5], acc[6], acc[7]);
+              }
+            }
+          }
+          fence_proxy_async_smem();
+          __syncwarp();
+          if (lane == 0) {
+            tma_store_3d(&tmOut, slabs + (2 * grp) * 4096, c0, m0 + q * 32, 0);
+            tma_store_3d(&tmOut, slabs + (2 * grp + 1) * 4096, F + c0, m0 + q * 32, 0);
+            tma_store_commit();
+          }
+          __syncwarp();
+        }
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive_leader(&tmem_empty[as]);
+        if (++as == 2) {
+          as = 0;
+          aphase ^= 1;
+        }
+      }
+      if (lane == 0) tma_store_wait<0>();
+    } else if constexpr (SWIGLU) {
       // warps 2-5: hidden-unit chunks 0, 1 of the tile (gate columns [0, 64) + up columns [128, 192));
       // warps 6-9: chunks 2, 3.  Three slabs per warp: gate, up, act (32 rows x 64 bf16 columns each).
       const int half = (warp - 2) >> 2;
@@ -710,12 +850,65 @@ extern "C" int dpfs_gemm2sm_swiglu_bf16(const void* A, long long lda, const void
   args.residual = nullptr;
   args.ldr = 0;
   args.F = F;
+  args.gu = nullptr;
+  args.colsum = nullptr;
   const int work = ((M + 2 * BM - 1) / (2 * BM)) * (F / BNH);
   int clusters = num_sms() / 2;
   if (work < clusters) clusters = work;
-  auto kfn = gemm2sm_kernel<false, false, __nv_bfloat16, 8, true>;
-  DPFS_ENSURE_DYN_SMEM(kfn, (Cfg<8, true>::kSmem));
-  kfn<<<(DPFS_COUNT(), 2 * clusters), Cfg<8, true>::kThreads, Cfg<8, true>::kSmem, stream>>>(tmA, tmB, tmOut, args,
+  auto kfn = gemm2sm_kernel<false, false, __nv_bfloat16, 8, 1>;
+  DPFS_ENSURE_DYN_SMEM(kfn, (Cfg<8, 1>::kSmem));
+  kfn<<<(DPFS_COUNT(), 2 * clusters), Cfg<8, 1>::kThreads, Cfg<8, 1>::kSmem, stream>>>(tmA, tmB, tmOut, args,
                                                                                               tmAct);
   return static_cast<int>(cudaGetLastError());
+}
+
+namespace dpfs { int reduce_partials_rows(const float* partial, float* out, int nrows, int D, cudaStream_t stream); }
+
+// rows of the column-sum scratch of dpfs_gemm2sm_swiglu_bwd_bf16 ([rows][2F] floats)
+extern "C" int dpfs_gemm2sm_swiglu_bwd_rows(int M) { return ((M + 255) / 256) * 8; }
+
+// Fused down_proj dgrad + SwiGLU backward: dgu[M][2F] = swiglu'(dy W_down, gu) (bf16) and bias_grad[2F] = column sums
+// of dgu.  dy: bf16 [M][ldy] (K = d contiguous), W: bf16 [d][ldw] (the down_proj weight as stored: [odim = d][F]),
+// gu: the saved gate|up activation [M][2F].  F % 256 == 0.  scratch: dpfs_gemm2sm_swiglu_bwd_rows(M) x 2F floats.
+extern "C" int dpfs_gemm2sm_swiglu_bwd_bf16(const void* dy, long long ldy, const void* W, long long ldw, const void* gu,
+                                            void* dgu, float* bias_grad, float* scratch, int M, int F, int K,
+                                            cudaStream_t stream) {
+  using namespace dpfs::sm2;
+  if (M <= 0 || F <= 0 || K <= 0) return 0;
+  if (F % BN != 0 || (ldy % 8) != 0 || (ldw % 8) != 0 || !gu || !scratch) return -10;
+  CUtensorMap tmA, tmB, tmOut;
+  int rc = make_tmap_bf16_2d(&tmA, dy, K, M, ldy, 64, BM);
+  if (rc) return rc;
+  rc = make_tmap_bf16_2d(&tmB, W, F, K, ldw, 64, BK);   // MN-major B: [K][N] with N contiguous
+  if (rc) return rc;
+  rc = make_out_tmap(&tmOut, dgu, false, M, 2 * F, 2LL * F, 1, 0);
+  if (rc) return rc;
+  CUtensorMap tmGu;   // same geometry over the saved gate|up activation: its slabs are loaded, not stored
+  rc = make_out_tmap(&tmGu, const_cast<void*>(gu), false, M, 2 * F, 2LL * F, 1, 0);
+  if (rc) return rc;
+  Args args;
+  args.M = M;
+  args.N = F;
+  args.K = K;
+  args.splits = 1;
+  args.kb_per_split = (K + BK - 1) / BK;
+  args.out = dgu;
+  args.ldo = 2LL * F;
+  args.split_stride = 0;
+  args.bias = nullptr;
+  args.residual = nullptr;
+  args.ldr = 0;
+  args.F = F;
+  args.gu = static_cast<const __nv_bfloat16*>(gu);
+  args.colsum = scratch;
+  const int work = ((M + 2 * BM - 1) / (2 * BM)) * (F / BN);
+  int clusters = num_sms() / 2;
+  if (work < clusters) clusters = work;
+  auto kfn = gemm2sm_kernel<false, true, __nv_bfloat16, 8, 2>;
+  DPFS_ENSURE_DYN_SMEM(kfn, (Cfg<8, 2>::kSmem));
+  kfn<<<(DPFS_COUNT(), 2 * clusters), Cfg<8, 2>::kThreads, Cfg<8, 2>::kSmem, stream>>>(tmA, tmB, tmOut, args, tmGu);
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return static_cast<int>(e);
+  if (!bias_grad) return 0;
+  return reduce_partials_rows(scratch, bias_grad, dpfs_gemm2sm_swiglu_bwd_rows(M), 2 * F, stream);
 }

@@ -30,7 +30,7 @@ import torch
 
 from ..ops import fused
 from ..ops.attention import attn_bwd, attn_fwd
-from ..ops.gemm import gemm_nt, gemm_swiglu
+from ..ops.gemm import gemm_nt, gemm_swiglu, gemm_swiglu_bwd
 from ..parallel import comm_ops
 from ..parallel import process_manager as pm
 from ..utils.logging import nvtx_range
@@ -276,10 +276,9 @@ class FusedLayerFn(torch.autograd.Function):
             dx3_b = fused.cast_to_bf16(dx3)
             fused.colsum(dx3_b, out=pack.g_bd)
         # ---- FFN
-        dact = gemm_nt(dx3_b, pack.wd, b_mn_major=True, out_dtype=BF16)            # [M, Fl]
         _wgrad(dx3_b, act, pack.g_wd)
-        dgu = fused.swiglu_bwd_bias(dact, gu, pack.g_bgu)   # + gate|up bias grads from the same pass
-        del dact
+        # down_proj dgrad with the SwiGLU backward (+ gate|up bias grads) in its epilogue: dact never reaches memory
+        dgu = gemm_swiglu_bwd(dx3_b, pack.wd, gu, pack.g_bgu)
         dh2 = _colpar_dgrad(dgu, pack.wgu)                                            # [M, d]
         _wgrad(dgu, h2, pack.g_wgu)
         del dgu
@@ -665,12 +664,10 @@ class FusedLayerSPFn(torch.autograd.Function):
             dx3 = fused.cast_to_bf16_push(dx3_l, push)                                   # [M, d] bf16 (landing zone)
         else:
             dx3 = _all_gather_rows(fused.cast_to_bf16(dx3_l))                            # [M, d] bf16
-        dact = gemm_nt(dx3, pack.wd, b_mn_major=True, out_dtype=BF16)
         _wgrad(dx3, act, pack.g_wd)
         Ml, r = dx3_l.shape[0], pm.pgm.tp_rank
         fused.colsum(dx3[r * Ml:(r + 1) * Ml], out=pack.g_bd)    # partial over this rank's rows (see norm_grads)
-        dgu = fused.swiglu_bwd_bias(dact, gu, pack.g_bgu)
-        del dact
+        dgu = gemm_swiglu_bwd(dx3, pack.wd, gu, pack.g_bgu)
         dh2_l = _rowpar_rs(dgu, pack.wgu, b_mn_major=True)                               # [Ml, d]
         _wgrad(dgu, h2, pack.g_wgu)
         del dgu
@@ -858,10 +855,8 @@ class HandoffLayerFn(torch.autograd.Function):
         dx3_l = dx3_l.contiguous()
         dx3 = rt.take_stash(dx3_l)        # gathered bf16 [M, d] from the hand-off that closed the block above
         assert dx3 is not None
-        dact = gemm_nt(dx3, pack.wd, b_mn_major=True, out_dtype=BF16)
         rt.on_side(lambda: _wgrad(dx3, act, pack.g_wd), keep=(dx3, act), reads_bzone=True)
-        dgu = fused.swiglu_bwd_bias(dact, gu, pack.g_bgu)
-        del dact
+        dgu = gemm_swiglu_bwd(dx3, pack.wd, gu, pack.g_bgu)    # dgrad of down_proj + SwiGLU backward in one kernel
         rt.on_side(lambda: _wgrad(dgu, h2, pack.g_wgu), keep=(dgu, h2))
         # dx2 is the output gradient of wo's residual add: its (local) column sums are the wo bias gradient
         dx2_l, dx2 = _handoff_bwd(dgu, pack.wgu, x2_l, rstd2, pack.s2, dx3_l, rt.next_bzone(), pack.g_s2, pack.g_bo)

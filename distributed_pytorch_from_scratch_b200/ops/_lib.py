@@ -28,6 +28,8 @@ SIGS = {
     "dpfs_gemm2sm_bf16": (c_p, c_ll, c_int, c_p, c_ll, c_int, c_p, c_ll, c_int, c_p, c_p, c_ll, c_int, c_int, c_int,
                           c_int, c_p, c_p),
     "dpfs_gemm2sm_swiglu_bf16": (c_p, c_ll, c_p, c_ll, c_p, c_p, c_p, c_int, c_int, c_int, c_p),
+    "dpfs_gemm2sm_swiglu_bwd_bf16": (c_p, c_ll, c_p, c_ll, c_p, c_p, c_p, c_p, c_int, c_int, c_int, c_p),
+    "dpfs_gemm2sm_swiglu_bwd_rows": (c_int,),
     "dpfs_gemm_allreduce_bf16": (c_p, c_ll, c_p, c_ll, c_int, c_p, c_p, c_p, c_ll, c_int, c_int, c_int, c_p, c_int,
                                  c_int, c_int, c_p),
     "dpfs_gemm_reduce_scatter_bf16": (c_p, c_ll, c_p, c_ll, c_int, c_p, c_p, c_p, c_ll, c_p, c_int, c_int, c_int, c_p,

@@ -130,3 +130,29 @@ def gemm_swiglu(x: torch.Tensor, w_gate_up: torch.Tensor, bias: Optional[torch.T
     from . import fused
     gu = gemm_nt(x, w_gate_up, bias=bias, out_dtype=torch.bfloat16)
     return gu, fused.swiglu_fwd(gu)
+
+
+def gemm_swiglu_bwd(dy: torch.Tensor, w_down: torch.Tensor, gu: torch.Tensor, bias_grad: torch.Tensor) -> torch.Tensor:
+    """d(gate|up) = swiglu'(dy @ W_down, gu) (bf16 [M, 2F]) and its column sums into ``bias_grad`` (fp32 [2F]).
+
+    One kernel when the 2-SM GEMM's SwiGLU-backward epilogue applies (F % 256 == 0, M >= 256): the dgrad accumulator
+    dact = dy @ W_down never leaves the SM -- the epilogue reads the saved gate / up values and writes both halves of
+    d(gate|up).  Otherwise dgrad GEMM + swiglu_bwd_bias.  ``w_down``: the down_proj weight as stored, [d, F]."""
+    from . import fused
+    M, K = dy.shape
+    F = w_down.shape[1]
+    assert gu.shape == (M, 2 * F) and gu.dtype == torch.bfloat16 and gu.is_contiguous()
+    assert bias_grad.dtype == torch.float32 and bias_grad.numel() == 2 * F and bias_grad.is_contiguous()
+    if (_FUSE_SWIGLU and _USE_2SM and M >= 256 and F % 256 == 0 and dy.dtype == torch.bfloat16
+            and w_down.dtype == torch.bfloat16 and dy.stride(1) == 1 and w_down.stride(1) == 1
+            and dy.stride(0) % 8 == 0 and w_down.stride(0) % 8 == 0 and w_down.shape[0] == K):
+        lib = _lib.lib()
+        dgu = torch.empty_like(gu)
+        scratch = fused._scratch(dy.device, "swiglu_bwd_epi", lib.dpfs_gemm2sm_swiglu_bwd_rows(M) * 2 * F)
+        rc = lib.dpfs_gemm2sm_swiglu_bwd_bf16(dy.data_ptr(), dy.stride(0), w_down.data_ptr(), w_down.stride(0),
+                                              gu.data_ptr(), dgu.data_ptr(), bias_grad.data_ptr(), scratch.data_ptr(),
+                                              M, F, K, _lib.stream())
+        _lib.check(rc, "dpfs_gemm2sm_swiglu_bwd_bf16")
+        return dgu
+    dact = gemm_nt(dy, w_down, b_mn_major=True, out_dtype=torch.bfloat16)
+    return fused.swiglu_bwd_bias(dact, gu, bias_grad)

@@ -44,6 +44,15 @@ int dpfs_gemm2sm_bf16(const void* A, long long lda, int a_mn_major, const void* 
 int dpfs_gemm2sm_swiglu_bf16(const void* A, long long lda, const void* B, long long ldb, void* gu, void* act,
                              const float* bias, int M, int F, int K, cudaStream_t stream);
 
+/* Fused down_proj dgrad + SwiGLU backward (2-SM kernel, SwiGLU' in the epilogue): dgu[M][2F] = swiglu'(dy W, gu) in
+ * bf16 and bias_grad[2F] = column sums of dgu (nullable).  dy: bf16 [M][ldy]; W: the down_proj weight as stored,
+ * bf16 [K = d][ldw] with F contiguous; gu: the saved gate|up activation [M][2F].  F % 256 == 0.  scratch: fp32
+ * [dpfs_gemm2sm_swiglu_bwd_rows(M)][2F].  dact = dy W is never written to memory.
+ * ref: autograd of FFN.forward, models/model.py:95 (a cuBLAS dgrad GEMM + ~6 ATen kernels in the reference). */
+int dpfs_gemm2sm_swiglu_bwd_bf16(const void* dy, long long ldy, const void* W, long long ldw, const void* gu, void* dgu,
+                                 float* bias_grad, float* scratch, int M, int F, int K, cudaStream_t stream);
+int dpfs_gemm2sm_swiglu_bwd_rows(int M);
+
 /* Fused GEMM -> all-reduce over NVLink (one kernel): every rank computes its partial out = A_r B_r^T (bf16) into
  * its symmetric buffer `out` ([M][N], row stride N) and the ranks sum the tiles through the NVSwitch with
  * multimem.ld_reduce / multimem.st on `mc_out` (the multicast alias of `out`).  flag_ptrs: HOST array of the n ranks'

@@ -66,6 +66,28 @@ def test_gemm_swiglu_epilogue(shape):
     assert (act.float() - act_ref).abs().max().item() < 1e-2 * max(1.0, act_ref.abs().max().item())
 
 
+@pytest.mark.parametrize("shape", [(32000, 2048, 512), (1000, 256, 512), (520, 512, 192), (4096, 1024, 1024)])
+def test_gemm_swiglu_bwd_epilogue(shape):
+    """down_proj dgrad with the SwiGLU backward in the epilogue vs fp32 PyTorch autograd of silu(g) * u."""
+    from distributed_pytorch_from_scratch_b200.ops.gemm import gemm_swiglu_bwd
+    M, F, K = shape
+    torch.manual_seed(0)
+    dy = _bf(torch.randn(M, K, device=DEV))
+    w = _bf(torch.randn(K, F, device=DEV) * K ** -0.5)          # down_proj weight as stored: [d, F]
+    gu = _bf(torch.randn(M, 2 * F, device=DEV))
+    bg = torch.empty(2 * F, device=DEV)
+    dgu = gemm_swiglu_bwd(dy, w, gu, bg)
+    dact = _bf(dy.float() @ w.float()).float()                   # the stand-alone path rounds dact to bf16 too
+    g = gu.float()[:, :F].clone().requires_grad_(True)
+    u = gu.float()[:, F:].clone().requires_grad_(True)
+    (torch.nn.functional.silu(g) * u).backward(dact)
+    ref = torch.cat([g.grad, u.grad], dim=1)
+    sc = max(1.0, ref.abs().max().item())
+    assert (dgu.float() - ref).abs().max().item() < 2e-2 * sc
+    bsum = dgu.float().sum(0)
+    assert (bg - bsum).abs().max().item() < 1e-3 * max(1.0, bsum.abs().max().item()) + 1e-2
+
+
 @pytest.mark.parametrize("B,T,H,HD", [(1, 128, 1, 64), (2, 200, 2, 64), (2, 1000, 2, 64), (2, 333, 2, 128)])
 def test_flash_attention_fwd_bwd(B, T, H, HD):
     from distributed_pytorch_from_scratch_b200.ops import attention as A
