@@ -32,8 +32,24 @@ def test_train_then_test_cli(tmp_path):
     # resume continues from step 6 to step 8
     out = _run(["train.py", "--tp_size", "2", "--synthetic_data", "--save_dir", save, "--max_steps", "8",
                 "--warmup_steps", "2", "--log_interval", "2", "--save_interval", "2", "--batch_size", "2", "--resume",
-                "--backend", "gloo", "--master_port", str(free_port())] + MODEL)
+                "--profile", "--backend", "gloo", "--master_port", str(free_port())] + MODEL)
     assert "Resumed from" in out and "at step 6" in out and "total steps: 8" in out
+    # --profile reports throughput both ways: every padded position, and only positions that carry a target
+    assert "[profile]" in out and "counting every padded position" in out and "is not padding" in out
+    # a resume file that belongs to another step than every checkpoint on disk must be refused, not silently mixed
+    import torch
+    rp = os.path.join(save, "resume-tprank-0.pt")
+    st = torch.load(rp, map_location="cpu", weights_only=False)
+    st["step"] = 5
+    torch.save(st, rp)
+    env = dict(os.environ, DPFS_NO_TQDM="1", PYTHONPATH=REPO)
+    bad = subprocess.run([sys.executable, "train.py", "--tp_size", "2", "--synthetic_data", "--save_dir", save,
+                          "--max_steps", "9", "--warmup_steps", "2", "--batch_size", "2", "--resume", "--backend", "gloo",
+                          "--master_port", str(free_port())] + MODEL, cwd=REPO, env=env, capture_output=True, text=True,
+                         timeout=600)
+    assert bad.returncode != 0 and "refusing to mix them" in (bad.stdout + bad.stderr)
+    st["step"] = 8
+    torch.save(st, rp)
     # evaluation + greedy decode at TP=2
     data = os.path.join(save, "synthetic_tokens.json")
     out = _run(["test.py", "--tp_size", "2", "--ckpt_dir", save, "-d", data, "-t", "tokenizer/tokenizer.json",

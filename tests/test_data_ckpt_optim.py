@@ -30,6 +30,26 @@ def test_collate_layout_and_loader(tmp_path):
         ShakespeareDataset(path, "test", 16)
 
 
+def test_vectorised_collate_matches_row_by_row_restatement():
+    """The flat-scatter collate against a row-by-row restatement of the batch layout (BOS prefix, EOS as the input pad,
+    targets shifted by one with EOS then IGNORE) on random ragged batches, including a batch of one and equal lengths."""
+    import random
+    from dataset import collate_fn
+    rng = random.Random(0)
+    for trial in range(50):
+        B = rng.choice([1, 2, 5, 16])
+        same = rng.random() < 0.2
+        L0 = rng.randint(1, 40)
+        batch = [[rng.randint(3, 1000) for _ in range(L0 if same else rng.randint(1, 40))] for _ in range(B)]
+        out = collate_fn(batch, bos=0, eos=1, ignore_idx=-1)
+        width = max(len(d) for d in batch) + 1
+        for i, doc in enumerate(batch):
+            assert out["input_ids"][i].tolist() == [0] + doc + [1] * (width - 1 - len(doc))
+            assert out["target_ids"][i].tolist() == doc + [1] + [-1] * (width - 1 - len(doc))
+            assert out["position_ids"][i].tolist() == list(range(width))
+        assert all(out[k].dtype == torch.int64 and out[k].is_contiguous() for k in out)
+
+
 def test_shipped_tokenizer():
     from tokenizers import Tokenizer
     tok = Tokenizer.from_file(os.path.join(REPO, "tokenizer", "tokenizer.json"))

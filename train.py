@@ -186,7 +186,7 @@ def train(rank: int, args: Namespace):
     accum_dev = torch.zeros((), dtype=torch.float64, device=device)   # running loss sum stays on the device
     n_step = start_step
     timer = StepTimer(device)
-    tokens_since, steps_since = 0, 0
+    tokens_since, real_since, steps_since = 0, 0, 0     # padded positions / positions with a real target / steps
     timer.start()
 
     if dist.is_initialized():
@@ -212,6 +212,8 @@ def train(rank: int, args: Namespace):
             accum_dev += loss.double()
             n_step += 1
             tokens_since += batch['input_ids'].numel()
+            if args.profile:     # counted on the host copy of the batch: no device sync
+                real_since += int((batch['target_ids'] != IGNORE_INDEX).sum())
             steps_since += 1
             pbar.update(1)
             if n_step % args.log_interval == 0:
@@ -228,11 +230,14 @@ def train(rank: int, args: Namespace):
                 if args.profile:
                     ms = max_over_ranks(timer.stop_ms(), device) / max(steps_since, 1)
                     tps = tokens_since / max(steps_since, 1) / ms * 1e3
+                    tps_real = real_since / max(steps_since, 1) / ms * 1e3
                     if rank == 0:
-                        print(f"[profile] {ms:.2f} ms/step (device-timed, max over ranks), {tps:,.0f} tokens/s "
-                              f"(padded tokens included)")
+                        print(f"[profile] {ms:.2f} ms/step (device-timed, max over ranks), {tps:,.0f} tokens/s counting "
+                              f"every padded position, {tps_real:,.0f} tokens/s counting only positions with a target "
+                              f"({100.0 * real_since / max(tokens_since, 1):.1f}% of the batch is not padding)")
                     summary_writer.add_scalar('train/tokens_per_sec', tps, n_step)
-                    tokens_since, steps_since = 0, 0
+                    summary_writer.add_scalar('train/nonpad_tokens_per_sec', tps_real, n_step)
+                    tokens_since, real_since, steps_since = 0, 0, 0
                     timer.start()
             if n_step % args.save_interval == 0:
                 avg_loss = (accum_loss + accum_dev.item()) / n_step
