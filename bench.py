@@ -380,7 +380,6 @@ def run_reference(args):
                 "h2d_bytes_per_step": int(3 * BATCH * SEQ * 8), "d2h_bytes_per_step": 4},
         "gpu_launches": 0,
         "final_loss": loss_dev,
-        "parity": parity,
         "max_mem_gib": torch.cuda.max_memory_allocated() / 2 ** 30,
     }
     emit(rank, payload)
