@@ -448,7 +448,7 @@ class FusedRuntime:
         ids = input_ids.reshape(-1).contiguous()
         pos = position_ids.reshape(-1).contiguous()
         if self.sp_active(B * T):
-            if self.handoff_ready(B * T):
+            if self.handoff_ready(B * T, B):
                 # ONE kernel per residual-stream hand-off (reduce-scatter -> norm -> all-gather through the switch)
                 x = HandoffEmbedFn.apply(ids, self, self.model.embedding.weight)
                 for pack in self.packs:
@@ -464,7 +464,7 @@ class FusedRuntime:
         return x  # fp32 [M, d]
 
     # ---------------------------------------------------------------------------------------------- SP hand-off path
-    def handoff_ready(self, M: int) -> bool:
+    def handoff_ready(self, M: int, B: Optional[int] = None) -> bool:
         """True when the one-kernel hand-offs (csrc/sp_fused.cu) can run this batch: NVLS multicast available, model
         width within the kernels' register budget, partial matrix fits the symmetric buffer.  Allocates the symmetric
         activation zones on first use (a collective: every rank takes this branch for the same batch shapes)."""
@@ -477,8 +477,12 @@ class FusedRuntime:
             # h1 / h2 of every layer and the final norm's output stay resident for the backward pass (2L + 1 zones);
             # two more zones alternate as the landing buffer of the gathered bf16 residual-stream gradient (two, so a
             # weight-gradient GEMM on the side stream may still read one while the next hand-off fills the other)
-            self._zones = symm.alloc_zones(2 * len(self.packs) + 3, M * self.d * 2)
-            self._zone_rows = M
+            # Sized for the longest sequence the model accepts at this batch size, not for this batch: the loader's
+            # batches differ in length, and a zone set that had to grow would be a second ~GB allocation (the old one
+            # stays alive for the CUDA graphs captured on it).
+            rows = max(M, (B or 0) * int(getattr(self.model, "maxlen", 0) or 0))
+            self._zones = symm.alloc_zones(2 * len(self.packs) + 3, rows * self.d * 2)
+            self._zone_rows = rows
             self._bz = 0
         return True
 
