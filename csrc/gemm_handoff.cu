@@ -71,8 +71,8 @@ struct Args {
 
 // same owner-interleaved tile order as the fused reduce-scatter (gemm_tcgen05.cu): the j-th row-block of owner 0, of
 // owner 1, ... so that every owner's comm warps are fed from the start
-__device__ __forceinline__ int first_blk(int o, int rpr) { return (o * rpr + BM - 1) / BM; }
-__device__ __forceinline__ int block_of(int wb, int n, int rpr) {
+__host__ __device__ __forceinline__ int first_blk(int o, int rpr) { return (o * rpr + BM - 1) / BM; }
+__host__ __device__ __forceinline__ int block_of(int wb, int n, int rpr) {
   int cmin = 0x7fffffff;
   for (int o = 0; o < n; ++o) {
     const int cnt = first_blk(o + 1, rpr) - first_blk(o, rpr);
@@ -484,4 +484,25 @@ extern "C" int dpfs_gemm_handoff_bwd(const void* A, long long lda, const void* B
   gh::reduce_partials2_kernel<<<(DPFS_COUNT(), (2 * N + 31) / 32), 256, 0, stream>>>(scratch, grid, N, dscale_out,
                                                                                      dbias_out);
   return static_cast<int>(cudaGetLastError());
+}
+
+// Host-side view of the kernel's schedule for the CPU tests (same functions the kernel runs): order[i] = row-block
+// computed i-th by every rank; for rank `rank`, item k (16 rows for N <= 512, 8 above) covers local rows
+// [item_lo[k], item_hi[k]) and waits for the tiles of row-blocks [blk_lo[k], blk_hi[k]].  Returns the item count.
+extern "C" int dpfs_debug_gh_schedule(int M, int N, int n, int rank, int* order, int* item_lo, int* item_hi,
+                                      int* blk_lo, int* blk_hi, int cap) {
+  using namespace dpfs::gh;
+  if (n < 1 || M <= 0 || M % n != 0 || M / n < BM || rank < 0 || rank >= n) return -53;
+  const int rpr = M / n, tiles_m = (M + BM - 1) / BM;
+  for (int i = 0; i < tiles_m; ++i) order[i] = block_of(i, n, rpr);
+  const int IR = kCommWarps * ((N + 255) / 256 <= 2 ? 2 : 1);
+  const int n_items = (rpr + IR - 1) / IR;
+  const long long g0 = static_cast<long long>(rank) * rpr;
+  for (int k = 0; k < n_items && k < cap; ++k) {
+    item_lo[k] = k * IR;
+    item_hi[k] = (k + 1) * IR < rpr ? (k + 1) * IR : rpr;
+    blk_lo[k] = static_cast<int>((g0 + item_lo[k]) / BM);
+    blk_hi[k] = static_cast<int>((g0 + item_hi[k] - 1) / BM);
+  }
+  return n_items;
 }

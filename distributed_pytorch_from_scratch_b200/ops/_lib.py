@@ -82,6 +82,7 @@ SIGS = {
     "dpfs_gemm_handoff_bwd": (c_p, c_ll, c_p, c_ll, c_int, c_p, c_p, c_int, c_int, c_int, c_p, c_p, c_p, c_p, c_p, c_p,
                               c_p, c_p, c_p, c_p, c_int, c_int, c_p),
     "dpfs_gemm_handoff_scratch_rows": (),
+    "dpfs_debug_gh_schedule": (c_int, c_int, c_int, c_int, c_p, c_p, c_p, c_p, c_p, c_int),
     "dpfs_sp_blocks": (c_int, c_int),
     "dpfs_sp_debug_config": (c_int, c_int),
     "dpfs_comm_barrier_ex": (c_p, c_int, c_int, c_int, c_int, c_int, c_p),

@@ -121,6 +121,9 @@ int dpfs_gemm_handoff_bwd(const void* A, long long lda, const void* B, long long
                           float* dbias_out, float* scratch, const unsigned long long* flag_ptrs, int rank, int n,
                           cudaStream_t stream);
 int dpfs_gemm_handoff_scratch_rows(void);
+/* host-side view of that kernel's tile order and comm work items, for the CPU tests */
+int dpfs_debug_gh_schedule(int M, int N, int n, int rank, int* order, int* item_lo, int* item_hi, int* blk_lo,
+                           int* blk_hi, int cap);
 /* Tuning hook of the two stand-alone kernels above (tools/bench_handoff.py): grid_cap = most blocks to launch (0 = as many as are
  * resident at once), bar_mode = 0 one rank barrier per block (n remote atomics each), 1 grid-wide barrier with a
  * single n-way exchange per rank (default), 2 no barrier (timing of the data phase only; results are undefined). */

@@ -50,3 +50,39 @@ def test_schedule_is_a_fair_bijection(n, rows_per_rank):
 def test_rejects_unsupported_shapes():
     assert _schedule(1000, 8)[0] == -53      # 125 rows per rank < one tile
     assert _schedule(1001, 2)[0] == -53      # not divisible
+
+
+# ---- GEMM + hand-off in one kernel (csrc/gemm_handoff.cu): same tile order, comm work items of 16 / 8 rows ----------
+def _gh_schedule(M, N, n, rank):
+    tiles = (M + BM - 1) // BM
+    cap = M // n // 8 + 2
+    order = (ctypes.c_int * tiles)()
+    arrs = [(ctypes.c_int * cap)() for _ in range(4)]
+    rc = _lib.lib().dpfs_debug_gh_schedule(M, N, n, rank, ctypes.addressof(order), *[ctypes.addressof(a) for a in arrs],
+                                           cap)
+    return rc, list(order), [list(a)[:max(rc, 0)] for a in arrs]
+
+
+@pytest.mark.parametrize("n", [2, 4, 8])
+@pytest.mark.parametrize("rows_per_rank", [128, 130, 200, 1000, 4000, 4001])
+@pytest.mark.parametrize("N", [256, 512, 1024])
+def test_gemm_handoff_schedule(n, rows_per_rank, N):
+    """Every rank computes every row-block once, in the fused reduce-scatter's order; a rank's comm items tile its rows
+    exactly, and every item only waits for row-blocks whose producers flag this rank (a wait without a matching flag
+    would spin until the watchdog traps)."""
+    M = rows_per_rank * n
+    tiles = (M + BM - 1) // BM
+    rs_order = _schedule(M, n)[1]
+    rows_per_item = 16 if N <= 512 else 8
+    for rank in range(n):
+        rc, order, (ilo, ihi, blo, bhi) = _gh_schedule(M, N, n, rank)
+        assert rc == (rows_per_rank + rows_per_item - 1) // rows_per_item
+        assert order == rs_order and sorted(order) == list(range(tiles))
+        assert ilo[0] == 0 and ihi[-1] == rows_per_rank and all(a == b for a, b in zip(ihi[:-1], ilo[1:]))
+        g0 = rank * rows_per_rank
+        for lo, hi, b0, b1 in zip(ilo, ihi, blo, bhi):
+            assert 0 < hi - lo <= rows_per_item and 0 <= b1 - b0 <= 1
+            assert b0 == (g0 + lo) // BM and b1 == (g0 + hi - 1) // BM
+            for b in range(b0, b1 + 1):     # the producers of block b flag the owners of its first and last row
+                owners = {(b * BM) // rows_per_rank, (min(b * BM + BM, M) - 1) // rows_per_rank}
+                assert rank in owners, (rank, b, owners)
