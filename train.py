@@ -58,6 +58,8 @@ def get_train_args(argv=None):
     group.add_argument("--batch_size", "-b", type=int, default=32)
     group.add_argument("--bf16", action='store_true', help="Whether to use automatic mixed precision or not.")
     group.add_argument("--cuda_graph", action='store_true', help="replay the whole step as a CUDA graph")
+    group.add_argument("--bucket_len", type=int, default=128,
+                       help="with --cuda_graph: pad sequence lengths up to a multiple of this (0 = exact shapes)")
     group.add_argument("--resume", action='store_true',
                        help="continue from the newest checkpoint + resume-tprank-{r}.pt in --save_dir")
     group.add_argument("--profile", action='store_true', help="print device-timed step time / tokens per second")
@@ -175,7 +177,12 @@ def train(rank: int, args: Namespace):
             print(f"[TP rank {rank}]: Resumed from {chosen} at step {start_step}")
 
     if fused_model:
-        step_fn = TrainStep(model, optimizer, scheduler, ignore_index=IGNORE_INDEX, use_graph=args.cuda_graph)
+        # with --cuda_graph, ragged batches are padded up to multiples of --bucket_len so that a handful of captured
+        # graphs cover every batch (no loss / gradient change: padded positions are causal-masked and ignored)
+        bucket = args.bucket_len if args.cuda_graph else 0
+        n_shapes = (model_args.maxlen + bucket - 1) // bucket + 1 if bucket > 0 else 4
+        step_fn = TrainStep(model, optimizer, scheduler, ignore_index=IGNORE_INDEX, use_graph=args.cuda_graph,
+                            bucket=bucket, max_graphs=max(4, min(n_shapes, 32)))
     else:
         step_fn = None
 
