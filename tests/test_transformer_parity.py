@@ -36,8 +36,9 @@ def _compare_weights(para, van, rank, world):
         row(pl.ffn.down_proj, vl.ffn.down_proj)
 
 
-def _worker(rank, world):
+def _worker(rank, world, cfg=None):
     from models.model import Transformer, VallinaTransformer
+    CFG = cfg or globals()["CFG"]
     torch.manual_seed(7)
     state = torch.get_rng_state()
     para = Transformer(*CFG.values())            # positional, like the reference tests do
@@ -74,8 +75,8 @@ def _worker(rank, world):
         op = para.layers[0].attn.wq.odim_partition
         g, gr = para.layers[0].attn.wq.weight.grad, van.layers[0].attn.wq.weight.grad[op * rank:op * (rank + 1)]
         assert torch.allclose(g, gr, atol=1e-6)
-        ip = para.layers[1].ffn.down_proj.idim_partition
-        g, gr = para.layers[1].ffn.down_proj.weight.grad, van.layers[1].ffn.down_proj.weight.grad[:, ip * rank:ip * (rank + 1)]
+        ip = para.layers[-1].ffn.down_proj.idim_partition
+        g, gr = para.layers[-1].ffn.down_proj.weight.grad, van.layers[-1].ffn.down_proj.weight.grad[:, ip * rank:ip * (rank + 1)]
         assert torch.allclose(g, gr, atol=1e-6)
         # replicated parameters get identical grads on every rank
         assert torch.allclose(para.norm.scale.grad, van.norm.scale.grad, atol=1e-6)
@@ -87,6 +88,21 @@ def _worker(rank, world):
 @pytest.mark.parametrize("world", [2, 4])
 def test_transformer_tp_matches_oracle(world):
     run_distributed(_worker, world, free_port())
+
+
+def _grid_worker(rank, world):
+    """A corner of the reference's model grid (tests/test_transformers.py:73-116: widths, head sizes, depths, vocab
+    sizes, maxlens) scaled to CPU speed; the full 144-point grid runs on GPUs in tests/test_gpu_layer_grids.py."""
+    import itertools
+    for attn_dim, head_dim, layers, vocab in itertools.product((64, 128), (16, 32), (1, 3), (256, 1024)):
+        if (attn_dim, head_dim, layers) in ((64, 32, 3), (128, 16, 3)):
+            continue        # keep the CPU suite short: 12 of the 16 corners
+        _worker(rank, world, dict(attn_dim=attn_dim, ffn_dim=2 * attn_dim, num_heads=attn_dim // head_dim,
+                                  num_layers=layers, vocab_size=vocab, maxlen=48 + 16 * layers))
+
+
+def test_transformer_tp_grid_matches_oracle():
+    run_distributed(_grid_worker, 2, free_port())
 
 
 def test_tp1_matches_oracle_and_api():
