@@ -1,5 +1,5 @@
 """Script-style entry point with the reference's CLI (its tests/test_column_parallel_linear.py:1-179 is run as
-`python tests/test_column_parallel_linear.py --tp_size N`): spawns N ranks (gloo on CPU; the multi-GPU NCCL variants live in tests/test_gpu_tp.py) and runs the same
+`python tests/test_column_parallel_linear.py --tp_size N`): spawns N ranks (`--backend gloo`: the CPU-sized grids of the pytest suite; `--backend nccl`: the reference's full grid and 1000-step histories on GPUs, fp32, like the reference's own scripts) and runs the same
 assertions as the pytest suite.  Unlike the reference, a failing assertion makes the process exit non-zero."""
 import argparse
 import os
@@ -17,7 +17,11 @@ if __name__ == "__main__":
     ap.add_argument("--master_port", type=str, default="25555")
     ap.add_argument("--random_seed", type=int, default=42)
     ap.add_argument("--tp_size", type=int, default=2)
-    ap.add_argument("--backend", type=str, default="gloo", choices=["gloo"])
+    ap.add_argument("--backend", type=str, default="gloo", choices=["gloo", "nccl"])
     a = ap.parse_args()
-    run_distributed(_col_worker, a.tp_size, int(a.master_port), backend=a.backend)
+    if a.backend == "nccl":      # one process per GPU, NCCL, the reference's grid at full depth
+        from test_gpu_layer_grids import _linear_worker  # noqa: E402
+        run_distributed(_linear_worker, a.tp_size, int(a.master_port), backend="nccl", args=("col",))
+    else:
+        run_distributed(_col_worker, a.tp_size, int(a.master_port), backend=a.backend)
     print(f"OK: column_parallel_linear at TP={a.tp_size} ({a.backend})")
