@@ -347,6 +347,12 @@ def _model_worker(rank, world, comm, sp=False, poison=False, fused_gemm=False):
     gr = van.layers[1].ffn.down_proj.weight.grad[:, ip * rank:ip * (rank + 1)]
     assert (dn.weight.grad - gr).norm().item() / gr.norm().item() < 0.05
     assert (model.norm.scale.grad - van.norm.scale.grad).norm().item() / van.norm.scale.grad.norm().item() < 0.05
+    # replicated biases of the row-parallel layers: under sequence parallelism their gradients are row-partial sums
+    # completed by the once-per-step all-reduce of the replicated-parameter block
+    for got, want in ((model.layers[0].attn.wo.bias.grad, van.layers[0].attn.wo.bias.grad),
+                      (model.layers[1].ffn.down_proj.bias.grad, van.layers[1].ffn.down_proj.bias.grad),
+                      (model.layers[0].norm2.scale.grad, van.layers[0].norm2.scale.grad)):
+        assert (got - want).norm().item() / want.norm().item() < 0.05
     with torch.no_grad():
         lg = model(ids, pos).float()
     assert lg.shape == (B, 200, 1024) and (lg - ref_logits).abs().max().item() < 0.08
